@@ -1,0 +1,174 @@
+/*
+ * ssad.h -- C ABI of libssad_gen.so: batched artificial-anomaly generation on B200 (sm_100a).
+ *
+ * The reference (gabry1998/Self-Supervised-Anomaly-Detection) has no FFI/plugin boundary: its
+ * generator is plain Python (src/self_supervised/datasets.py:209-394,
+ * src/self_supervised/dataset_generator.py:15-275) calling Pillow/torchvision per image.  This
+ * header is the boundary a binding of that path would use: every entry point names the
+ * reference function(s) it replaces.  INTEGRATION.md shows the ctypes binding.
+ *
+ * Conventions
+ *  - all pointers except SsadBatchDesc* are DEVICE pointers owned by the caller (PyTorch);
+ *    the library never allocates, frees or synchronises, and launches only on `stream`;
+ *  - every random decision of the reference arrives as an explicit per-image parameter
+ *    record (SsadImageParams); there is no RNG in the library;
+ *  - images are uint8, interleaved RGB (HWC), row pitch in bytes;
+ *  - masks are bit-packed: uint32 words, bit (x & 31) of word (x >> 5) of row y, 1 = object;
+ *  - return value 0 = success, negative = SSAD_E* (ssad_strerror() gives the text).
+ */
+#ifndef SSAD_H_
+#define SSAD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSAD_VERSION 100  /* 0.1.0 */
+
+enum {
+    SSAD_OK = 0,
+    SSAD_EINVAL = -1,       /* bad argument (null pointer, non-positive size, bad enum) */
+    SSAD_EALIGN = -2,       /* pointer / pitch not aligned as required */
+    SSAD_EUNSUPPORTED = -3, /* valid request this build cannot serve (e.g. image too large for the fused path) */
+    SSAD_ELAUNCH = -4,      /* CUDA launch / attribute error (cudaGetLastError text via ssad_last_cuda_error) */
+    SSAD_EWORKSPACE = -5    /* workspace too small */
+};
+
+/* mask_mode */
+enum { SSAD_MASK_ALL = 0 /* textures: datasets.py:197-198 */, SSAD_MASK_SHARED = 1 /* fixed-pose classes: one
+       cached mask, datasets.py:199-206 */, SSAD_MASK_PER_IMAGE = 2 /* hazelnut/screw/metal_nut, datasets.py:232-233 */ };
+
+/* out_norm_dtype */
+enum { SSAD_NORM_NONE = 0, SSAD_NORM_F32 = 1, SSAD_NORM_BF16 = 2 };
+
+/* Per-image parameter record: every draw __getitem__ makes, with the
+ * Python-float derivations already done on the host exactly as PIL / torchvision do them.
+ * 192 bytes, 16-byte aligned array on the device. */
+typedef struct SsadImageParams {
+    int32_t  warp_fix[6];      /*   0: RandomAffine(3, scale=(1.05,1.1)) (datasets.py:221-222) as Pillow affine_fixed
+                                       16.16 coefficients a0,a1,a2,a3,a4,a5 (half-pixel term folded into a2,a5) */
+    int32_t  scar_fix[6];      /*  24: scar.rotate(angle, expand=True) (datasets.py:344), same encoding */
+    uint32_t centre_r[6];      /*  48: get_random_coordinate (dataset_generator.py:259-265): index = (r * N) >> 32 */
+    float    bright_f[2];      /*  72: the two ImageEnhance.Brightness factors (datasets.py:298-299), used iff cos > 0.99 */
+    float    jit_f[4];         /*  80: ColorJitter factors brightness, contrast, saturation, (hue: unused) */
+    int16_t  fallback_c[6][2]; /*  96: centre drawn inside the container when the mask is empty (dataset_generator.py:112-114) */
+    int16_t  poly_xy[8][2];    /* 120: rect2poly vertices (dataset_generator.py:63-98), in draw order */
+    int16_t  rect[4];          /* 152: generate_patch rectangle l,t,pw,ph inside the donor window (dataset_generator.py:172-191) */
+    int16_t  scar_size[2];     /* 160: (nw, nh) of the rotated scar */
+    int16_t  donor_off[2];     /* 164: x,y of the donor window (RandomCrop, datasets.py:253) inside the donor image */
+    int16_t  crop_off[2];      /* 168: x,y of the working window inside src and mask (datasets.py:243-252) */
+    int16_t  donor_idx;        /* 172: index into the donor bank (datasets.py:226); -1 = the image itself */
+    uint8_t  label;            /* 174: 0 good, 1 polygon cut-paste, 2 scar (datasets.py:215) */
+    uint8_t  warp_en;          /* 175 */
+    uint8_t  src_variant;      /* 176: 0 cut, 1 average colour, 2 random colour (datasets.py:270-293) */
+    uint8_t  scar_k;           /* 177: number of scar pastes, 2..5 (datasets.py:341) */
+    uint8_t  poly_n;           /* 178: number of polygon vertices, 4..8 */
+    uint8_t  rnd_rgb[3];       /* 179 */
+    uint8_t  jit_order[4];     /* 182: ColorJitter fn_idx permutation (0 b, 1 c, 2 s, 3 hue/no-op) */
+    uint8_t  jit_en;           /* 186: bit0 brightness, bit1 contrast, bit2 saturation; 0 = no jitter */
+    uint8_t  reserved[5];      /* 187 */
+} SsadImageParams;
+
+/* Batch constants (host struct, passed by pointer, copied at call time). */
+typedef struct SsadBatchDesc {
+    int32_t batch;             /* images in this call */
+    int32_t height, width;     /* working image x: imsize, or patch_size x patch_size in patch-level mode */
+    int32_t src_height, src_width;
+    int64_t src_pitch;         /* bytes per source row */
+    int64_t src_stride;        /* bytes per source image */
+    int32_t donor_count;       /* images in the donor bank (0: none) */
+    int32_t donor_height, donor_width;
+    int64_t donor_pitch, donor_stride;
+    int32_t donor_win_h, donor_win_w; /* size of image_for_cutting as generate_patch sees it (== working size) */
+    int32_t mask_mode;         /* SSAD_MASK_* */
+    int32_t mask_pitch_words;  /* uint32 words per mask row */
+    int64_t mask_stride_words; /* words per image (SSAD_MASK_PER_IMAGE) */
+    int32_t mask_height, mask_width;
+    int32_t box_poly[4];       /* Container(imsize, 1.75 | 1) left, top, right, bottom (dataset_generator.py:15-24) */
+    int32_t box_scar[4];       /* Container(imsize, 2 | 1) */
+    int32_t coverage_min3;     /* patch mode: label := 0 iff 3 * popcount(mask window) < coverage_min3 (datasets.py:258-259); 0 = off */
+    int32_t max_patch_w, max_patch_h; /* upper bounds of rect[2], rect[3] over the batch (polygon table sizing) */
+    int32_t out_norm_dtype;    /* SSAD_NORM_* */
+    int64_t out_u8_pitch;      /* bytes per output row (>= 3 * width) */
+    int64_t out_u8_stride;     /* bytes per output image */
+} SsadBatchDesc;
+
+/* Optional per-image trace of the data-dependent decisions, for parity tests. */
+typedef struct SsadDebug {
+    int32_t n_coords;          /* popcount of the mask window (len(coords_map), datasets.py:264) */
+    int32_t sim;               /* check_color_similarity(...) > 0.99 (datasets.py:295) */
+    int32_t paste[5][2];       /* (left, top) of each paste (check_valid_coordinates_by_container) */
+    int32_t contrast_mean;     /* ImageEnhance.Contrast degenerate grey level, -1 if contrast did not run */
+    int32_t label_out;
+    int32_t avg_rgb[3];        /* colour of the 'average' variant */
+    double  cosine;
+    int32_t reserved[2];
+} SsadDebug;
+
+int ssad_version(void);
+const char* ssad_strerror(int code);
+const char* ssad_last_cuda_error(void);
+size_t ssad_sizeof_params(void);
+size_t ssad_sizeof_desc(void);
+size_t ssad_sizeof_debug(void);
+
+/* The hot path: PretextTaskDataset.__getitem__ (datasets.py:209-394) for a whole batch, from the
+ * resident uint8 originals to (x, y):  RandomAffine pre-warp -> patch-mode window -> mask-constrained
+ * centre selection -> polygon cut-paste | rotated scar x k -> ColorJitter -> [ToTensor + Normalize].
+ *   params     [batch] device records
+ *   src        [batch] source images, uint8 HWC
+ *   donor_bank [donor_count] donor images (textures; may be NULL when every donor_idx is -1)
+ *   mask_bits  bit-packed mask(s) per mask_mode (NULL for SSAD_MASK_ALL)
+ *   norm_lut   [3][256] table of Normalize(ToTensor(v)) per channel, element type per out_norm_dtype
+ *              (NULL when out_norm is NULL)
+ *   out_u8     [batch][height][width][3] uint8, nullable
+ *   out_norm   [batch][3][height][width] f32/bf16 = Normalize(ToTensor(x)) (datasets.py:392-393), nullable
+ *   y_out      [batch] int64 labels after the coverage rule, nullable
+ *   debug      [batch] SsadDebug, nullable */
+int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, const uint8_t* src,
+                  const uint8_t* donor_bank, const uint32_t* mask_bits, const void* norm_lut,
+                  uint8_t* out_u8, void* out_norm, int64_t* y_out, SsadDebug* debug,
+                  void* workspace, size_t workspace_bytes, void* stream);
+size_t ssad_generate_workspace(const SsadBatchDesc* desc);
+
+/* obj_mask (dataset_generator.py:27-39) for a batch: canny(sigma 1.5, 5/255, 15/255) -> dilate 3x3 -> close 3x3
+ * -> fill holes -> erode 4x4 -> largest 8-connected component, bit-packed. */
+int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
+                  int64_t src_stride, uint32_t* mask_bits, int32_t mask_pitch_words, int64_t mask_stride_words,
+                  void* workspace, size_t workspace_bytes, void* stream);
+size_t ssad_obj_mask_workspace(int32_t batch, int32_t height, int32_t width);
+
+/* Unit entry points (parity tests of the individual reference routines). */
+
+/* rect2poly mask: ImageDraw.polygon(points, fill='white') on a pw x ph canvas (dataset_generator.py:99-100).
+ * out: [n][max_h][max_w] uint8 0/255 (rows/cols beyond (pw, ph) are zero). */
+int ssad_polygon_mask(int32_t n, const int16_t* poly_xy /* [n][8][2] */, const uint8_t* poly_n /* [n] */,
+                      const int16_t* size /* [n][2] pw, ph */, uint8_t* out, int32_t max_w, int32_t max_h, void* stream);
+
+/* Image.transform(size, AFFINE, NEAREST) with affine_fixed coefficients (Image.rotate(expand=True) at
+ * datasets.py:344, RandomAffine at datasets.py:221): channels in {3,4}; outside -> 0. */
+int ssad_affine_nearest(const uint8_t* src, int32_t src_w, int32_t src_h, int32_t channels,
+                        const int32_t* fix6_host, uint8_t* out, int32_t out_w, int32_t out_h, void* stream);
+
+/* torchvision ColorJitter.forward (datasets.py:44-47,391) with explicit order/factors, in place semantics
+ * on a batch of uint8 HWC images (dense pitch). order/factors are device arrays [n][4]. */
+int ssad_color_jitter(int32_t n, int32_t height, int32_t width, const uint8_t* src, uint8_t* out,
+                      const uint8_t* order, const float* factors, const uint8_t* enable, void* stream);
+
+/* coords_map[k] (datasets.py:263-264 + dataset_generator.py:259-265): (x, y) of the k-th set pixel in row-major
+ * order inside a window of a bit-packed mask; out_xy[i] = (-1,-1) when k >= count.  count_out nullable. */
+int ssad_select_kth(const uint32_t* mask_bits, int32_t mask_pitch_words, int32_t win_x, int32_t win_y,
+                    int32_t win_w, int32_t win_h, int32_t n, const uint32_t* k /* [n] device */,
+                    int32_t* out_xy /* [n][2] device */, int32_t* count_out, void* stream);
+
+/* ToTensor(original) (datasets.py:394): uint8 HWC -> f32 NCHW / 255. */
+int ssad_to_tensor(int32_t n, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
+                   int64_t src_stride, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSAD_H_ */

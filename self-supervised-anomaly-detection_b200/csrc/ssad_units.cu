@@ -1,0 +1,188 @@
+// Unit entry points of the C ABI: each reference routine of the path on its own, for parity tests
+// (rect2poly / ImageDraw.polygon, Image.transform AFFINE NEAREST, ColorJitter, coords_map[k], ToTensor).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ssad_device.cuh"
+
+int ssad_set_cuda_error(cudaError_t e);
+
+namespace ssad {
+
+// ---- rect2poly(patch, regular=False, sides=8) -> alpha of the RGBA mask (dataset_generator.py:63-100)
+__global__ void polygon_mask_kernel(int n, const int16_t* __restrict__ poly_xy, const uint8_t* __restrict__ poly_n,
+                                    const int16_t* __restrict__ size, uint8_t* __restrict__ out, int max_w, int max_h) {
+    extern __shared__ uint32_t rows[];          // blockDim.x rows of pitch words
+    const int i = blockIdx.x;
+    if (i >= n) return;
+    const int pw = size[2 * i], ph = size[2 * i + 1];
+    const int pitch = (max_w + 31) / 32;
+    __shared__ int16_t xy[8][2];
+    if (threadIdx.x < 16) (&xy[0][0])[threadIdx.x] = poly_xy[16 * i + threadIdx.x];
+    __syncthreads();
+    Polygon G;
+    polygon_setup(G, xy, poly_n[i], ph);
+    uint32_t* row = rows + (size_t)threadIdx.x * pitch;
+    uint8_t* o = out + (size_t)i * max_w * max_h;
+    for (int r = threadIdx.x; r < max_h; r += blockDim.x) {
+        for (int j = 0; j < pitch; ++j) row[j] = 0;
+        if (r < ph) polygon_fill_row(G, r, pw, row);
+        for (int x = 0; x < max_w; ++x) o[(size_t)r * max_w + x] = ((row[x >> 5] >> (x & 31)) & 1u) ? 255 : 0;
+    }
+}
+
+// ---- Image.transform(size, AFFINE, coeffs, NEAREST) via affine_fixed (Geometry.c)
+struct Fix6 { int32_t a[6]; };
+__global__ void affine_nearest_kernel(const uint8_t* __restrict__ src, int sw, int sh, int ch, Fix6 f,
+                                      uint8_t* __restrict__ out, int ow, int oh) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ow * oh) return;
+    int y = p / ow, x = p - y * ow;
+    int xin, yin;
+    affine_fixed_map(f.a, x, y, xin, yin);
+    bool ok = xin >= 0 && xin < sw && yin >= 0 && yin < sh;
+    for (int c = 0; c < ch; ++c) out[(size_t)p * ch + c] = ok ? src[((size_t)yin * sw + xin) * ch + c] : 0;
+}
+
+// ---- ColorJitter.forward (torchvision transforms.py:1259-1290) on PIL semantics, one CTA per image
+__global__ void __launch_bounds__(256)
+color_jitter_kernel(int height, int width, const uint8_t* __restrict__ src, uint8_t* __restrict__ out,
+                    const uint8_t* __restrict__ order, const float* __restrict__ factors, const uint8_t* __restrict__ enable) {
+    __shared__ uint32_t red[64];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int npix = height * width;
+    const uint8_t* s = src + (size_t)b * npix * 3;
+    uint8_t* o = out + (size_t)b * npix * 3;
+    for (int i = tid; i < npix * 3; i += blockDim.x) o[i] = s[i];
+    __syncthreads();
+    for (int st = 0; st < 4; ++st) {
+        const int fn = order[4 * b + st];
+        if (fn >= 3 || !((enable[b] >> fn) & 1)) continue;
+        const float f = factors[4 * b + fn];
+        const bool clip = blend_needs_clip(f);
+        int mean = 0;
+        if (fn == 1) {
+            uint32_t ls = 0;
+            for (int p = tid; p < npix; p += blockDim.x) ls += luma_u8(o[3 * p], o[3 * p + 1], o[3 * p + 2]);
+            ls = block_sum_u32<256>(ls, red);
+            mean = (int)((2ull * ls + (uint32_t)npix) / (2ull * (uint32_t)npix));
+        }
+        for (int p = tid; p < npix; p += blockDim.x) {
+            uint32_t L = luma_u8(o[3 * p], o[3 * p + 1], o[3 * p + 2]);
+            for (int c = 0; c < 3; ++c) {
+                float mB = magic_from_u8(o[3 * p + c]);
+                uint32_t A = (fn == 0) ? 0u : (fn == 1 ? (uint32_t)mean : L);
+                float r = clip ? magic_blend<true>(mB, magic_from_u8(A), (float)A, f)
+                               : magic_blend<false>(mB, magic_from_u8(A), (float)A, f);
+                o[3 * p + c] = (uint8_t)magic_to_u8(r);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---- coords_map[k] inside a window of a bit-packed mask (datasets.py:263-264)
+__global__ void __launch_bounds__(256)
+select_kth_kernel(const uint32_t* __restrict__ mask, int pitch, int wx, int wy, int ww, int wh, int n,
+                  const uint32_t* __restrict__ ks, int32_t* __restrict__ out_xy, int32_t* __restrict__ count_out) {
+    extern __shared__ uint32_t pre[];           // wh + 1
+    const int tid = threadIdx.x;
+    for (int r = tid; r < wh; r += blockDim.x) pre[r + 1] = row_window_popc(mask + (size_t)(wy + r) * pitch, wx, ww);
+    __syncthreads();
+    if (tid == 0) {
+        pre[0] = 0;
+        for (int r = 0; r < wh; ++r) pre[r + 1] += pre[r];
+        if (count_out) *count_out = (int32_t)pre[wh];
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) {
+        uint32_t k = ks[i];
+        int x = -1, y = -1;
+        if (k < pre[wh]) {
+            int lo = 0, hi = wh;
+            while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (pre[mid] <= k) lo = mid; else hi = mid; }
+            y = lo;
+            x = row_window_select(mask + (size_t)(wy + y) * pitch, wx, ww, k - pre[lo]);
+        }
+        out_xy[2 * i] = x; out_xy[2 * i + 1] = y;
+    }
+}
+
+// ---- ToTensor(original) (datasets.py:394): HWC u8 -> CHW f32, value / 255 (IEEE division as torch)
+__global__ void to_tensor_kernel(int height, int width, const uint8_t* __restrict__ src, int64_t pitch, int64_t stride,
+                                 float* __restrict__ out) {
+    const int b = blockIdx.y;
+    const int npix = height * width;
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    int y = p / width, x = p - y * width;
+    const uint8_t* q = src + (size_t)b * stride + (size_t)y * pitch + (size_t)x * 3;
+    float* o = out + (size_t)b * 3 * npix;
+    o[p] = __fdiv_rn((float)q[0], 255.0f);
+    o[npix + p] = __fdiv_rn((float)q[1], 255.0f);
+    o[2 * npix + p] = __fdiv_rn((float)q[2], 255.0f);
+}
+
+}  // namespace ssad
+
+#define SSAD_CHECK_LAUNCH()                                   \
+    do {                                                      \
+        cudaError_t e_ = cudaGetLastError();                  \
+        if (e_ != cudaSuccess) return ssad_set_cuda_error(e_); \
+    } while (0)
+
+extern "C" int ssad_polygon_mask(int32_t n, const int16_t* poly_xy, const uint8_t* poly_n, const int16_t* size,
+                                 uint8_t* out, int32_t max_w, int32_t max_h, void* stream) {
+    if (n < 0 || !poly_xy || !poly_n || !size || !out || max_w <= 0 || max_h <= 0) return SSAD_EINVAL;
+    if (n == 0) return SSAD_OK;
+    const int threads = 128;
+    size_t smem = (size_t)threads * ((max_w + 31) / 32) * 4;
+    if (smem > 48 * 1024) return SSAD_EUNSUPPORTED;
+    ssad::polygon_mask_kernel<<<n, threads, smem, (cudaStream_t)stream>>>(n, poly_xy, poly_n, size, out, max_w, max_h);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_affine_nearest(const uint8_t* src, int32_t src_w, int32_t src_h, int32_t channels,
+                                   const int32_t* fix6_host, uint8_t* out, int32_t out_w, int32_t out_h, void* stream) {
+    if (!src || !out || !fix6_host || src_w <= 0 || src_h <= 0 || out_w <= 0 || out_h <= 0) return SSAD_EINVAL;
+    if (channels != 3 && channels != 4) return SSAD_EINVAL;
+    ssad::Fix6 f;
+    for (int i = 0; i < 6; ++i) f.a[i] = fix6_host[i];
+    int n = out_w * out_h;
+    ssad::affine_nearest_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(src, src_w, src_h, channels, f, out, out_w, out_h);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_color_jitter(int32_t n, int32_t height, int32_t width, const uint8_t* src, uint8_t* out,
+                                 const uint8_t* order, const float* factors, const uint8_t* enable, void* stream) {
+    if (n < 0 || height <= 0 || width <= 0 || !src || !out || !order || !factors || !enable) return SSAD_EINVAL;
+    if (n == 0) return SSAD_OK;
+    ssad::color_jitter_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(height, width, src, out, order, factors, enable);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_select_kth(const uint32_t* mask_bits, int32_t mask_pitch_words, int32_t win_x, int32_t win_y,
+                               int32_t win_w, int32_t win_h, int32_t n, const uint32_t* k, int32_t* out_xy,
+                               int32_t* count_out, void* stream) {
+    if (!mask_bits || mask_pitch_words <= 0 || win_x < 0 || win_y < 0 || win_w <= 0 || win_h <= 0 || n < 0) return SSAD_EINVAL;
+    if (n > 0 && (!k || !out_xy)) return SSAD_EINVAL;
+    size_t smem = (size_t)(win_h + 1) * 4;
+    if (smem > 48 * 1024) return SSAD_EUNSUPPORTED;
+    ssad::select_kth_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(mask_bits, mask_pitch_words, win_x, win_y, win_w, win_h,
+                                                                      n, k, out_xy, count_out);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_to_tensor(int32_t n, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
+                              int64_t src_stride, float* out, void* stream) {
+    if (n < 0 || height <= 0 || width <= 0 || !src || !out || src_pitch < 3ll * width) return SSAD_EINVAL;
+    if (n == 0) return SSAD_OK;
+    dim3 grid((height * width + 255) / 256, n);
+    ssad::to_tensor_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(height, width, src, src_pitch, src_stride, out);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}

@@ -1,0 +1,175 @@
+"""Host side of the batched generator: owns the resident device state (cached mask bits, donor
+bank, normalisation table) and turns (source images, ParamBatch) into one ``ssad_generate`` call.
+
+PyTorch is used for device memory and streams only; all pixel work happens in libssad_gen.so."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .config import CPP, GeneratorConfig
+from .params import IMAGE_PARAMS_DTYPE, ParamBatch
+
+DEBUG_DTYPE = np.dtype([
+    ("n_coords", "<i4"), ("sim", "<i4"), ("paste", "<i4", (5, 2)), ("contrast_mean", "<i4"),
+    ("label_out", "<i4"), ("avg_rgb", "<i4", (3,)), ("cosine", "<f8"), ("reserved", "<i4", (2,)),
+], align=True)
+
+
+def pack_mask_bits(mask: np.ndarray) -> np.ndarray:
+    """bool [..., H, W] -> uint32 [..., H, ceil(W/32)], bit (x & 31) of word (x >> 5)."""
+    mask = np.asarray(mask, dtype=bool)
+    W = mask.shape[-1]
+    pad = (-W) % 32
+    if pad:
+        mask = np.concatenate([mask, np.zeros(mask.shape[:-1] + (pad,), dtype=bool)], axis=-1)
+    b = np.packbits(mask, axis=-1, bitorder="little")
+    return np.ascontiguousarray(b).view("<u4")
+
+
+def normalize_lut(dtype: torch.dtype) -> torch.Tensor:
+    """[3, 256] table of Normalize(ToTensor(v)) computed with the very torch ops the reference's
+    transform runs (datasets.py:430-433): v.float().div(255).sub(mean).div(std)."""
+    v = torch.arange(256, dtype=torch.uint8).to(torch.float32).div(255)
+    mean = torch.as_tensor(CPP.normalize_mean, dtype=torch.float32)[:, None]
+    std = torch.as_tensor(CPP.normalize_std, dtype=torch.float32)[:, None]
+    lut = (v[None, :] - mean) / std
+    return lut.to(dtype).contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class BatchGenerator:
+    """Batched replacement of ``PretextTaskDataset.__getitem__`` (reference datasets.py:209-394).
+
+    mask:   None for textures (all-white, datasets.py:197-198); bool [H, W] for fixed-pose classes (the
+            cached ``obj_mask`` of image 000, datasets.py:199-206); per-image masks are passed to
+            ``generate`` (non-fixed classes, datasets.py:232-233).
+    donors: uint8 [D, H, W, 3] bank of ``images_for_cut`` (datasets.py:189-193), textures only.
+    """
+
+    def __init__(self, cfg: GeneratorConfig, device="cuda", mask: Optional[np.ndarray] = None,
+                 donors: Optional[np.ndarray] = None):
+        self.cfg = cfg
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("BatchGenerator needs a CUDA device: there is no CPU fallback")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.lib = N.load()
+        W, H = cfg.imsize
+        self.mask_bits = None
+        if mask is not None:
+            mask = np.asarray(mask, dtype=bool)
+            if mask.shape != (H, W):
+                raise ValueError(f"mask must be [H={H}, W={W}]")
+            self.mask_bits = torch.from_numpy(pack_mask_bits(mask).view(np.int32)).to(self.device)
+        self.donors = None
+        if donors is not None:
+            donors = np.ascontiguousarray(donors, dtype=np.uint8)
+            if donors.ndim != 4 or donors.shape[1:] != (H, W, 3):
+                raise ValueError("donors must be uint8 [D, H, W, 3] at imsize")
+            self.donors = torch.from_numpy(donors).to(self.device)
+        if cfg.is_texture and self.donors is None:
+            raise ValueError("texture classes need the donor bank (datasets.py:189-193,226)")
+        self._luts = {}
+
+    def lut(self, dtype: torch.dtype) -> torch.Tensor:
+        if dtype not in self._luts:
+            self._luts[dtype] = normalize_lut(dtype).to(self.device)
+        return self._luts[dtype]
+
+    # ------------------------------------------------------------------
+    def upload_params(self, params: ParamBatch) -> torch.Tensor:
+        rec = np.ascontiguousarray(params.records)
+        if rec.dtype != IMAGE_PARAMS_DTYPE:
+            raise ValueError("records have the wrong dtype")
+        if np.any(rec["jit_f"] < 0) or np.any(rec["bright_f"] < 0):
+            raise ValueError("enhancement factors must be non-negative")
+        t = torch.from_numpy(rec.view(np.uint8).reshape(len(rec), IMAGE_PARAMS_DTYPE.itemsize))
+        return t.to(self.device, non_blocking=True)
+
+    def describe(self, batch: int, src: torch.Tensor, max_pw: int, max_ph: int, masks, norm_dtype) -> N.SsadBatchDesc:
+        cfg = self.cfg
+        W, H = cfg.work_size
+        d = N.SsadBatchDesc()
+        d.batch = batch
+        d.height, d.width = H, W
+        d.src_height, d.src_width = int(src.shape[1]), int(src.shape[2])
+        d.src_pitch, d.src_stride = int(src.stride(1)), int(src.stride(0))
+        if self.donors is not None:
+            d.donor_count = int(self.donors.shape[0])
+            d.donor_height, d.donor_width = int(self.donors.shape[1]), int(self.donors.shape[2])
+            d.donor_pitch, d.donor_stride = int(self.donors.stride(1)), int(self.donors.stride(0))
+        d.donor_win_w, d.donor_win_h = cfg.donor_window
+        if masks is not None:
+            d.mask_mode = N.SSAD_MASK_PER_IMAGE
+            d.mask_pitch_words, d.mask_stride_words = int(masks.stride(1)), int(masks.stride(0))
+            d.mask_height, d.mask_width = int(masks.shape[1]), cfg.imsize[0]
+        elif self.mask_bits is not None:
+            d.mask_mode = N.SSAD_MASK_SHARED
+            d.mask_pitch_words = int(self.mask_bits.stride(0))
+            d.mask_height, d.mask_width = int(self.mask_bits.shape[0]), cfg.imsize[0]
+        else:
+            d.mask_mode = N.SSAD_MASK_ALL
+        d.box_poly = (C.c_int32 * 4)(*cfg.box_poly)
+        d.box_scar = (C.c_int32 * 4)(*cfg.box_scar)
+        d.coverage_min3 = cfg.coverage_min3
+        d.max_patch_w, d.max_patch_h = max(int(max_pw), 1), max(int(max_ph), 1)
+        d.out_norm_dtype = {None: N.SSAD_NORM_NONE, torch.float32: N.SSAD_NORM_F32, torch.bfloat16: N.SSAD_NORM_BF16}[norm_dtype]
+        d.out_u8_pitch, d.out_u8_stride = 3 * W, 3 * W * H
+        return d
+
+    def generate(self, src: torch.Tensor, params: ParamBatch, *, masks: Optional[torch.Tensor] = None,
+                 want_u8: bool = True, norm_dtype: Optional[torch.dtype] = None, debug: bool = False,
+                 params_dev: Optional[torch.Tensor] = None, out_u8: Optional[torch.Tensor] = None,
+                 out_norm: Optional[torch.Tensor] = None, y_out: Optional[torch.Tensor] = None):
+        """src: uint8 [B, Hs, Ws, 3] on the device (the decoded, resized originals).
+        masks: int32/uint32-packed [B, Hs, ceil(Ws/32)] per-image mask bits (non-fixed classes).
+        Returns dict(x_u8, x, y, debug) -- entries present per the want_* flags."""
+        cfg = self.cfg
+        if src.device != self.device or src.dtype != torch.uint8 or src.dim() != 4 or src.shape[-1] != 3:
+            raise ValueError("src must be a uint8 [B, H, W, 3] tensor on the generator's device")
+        if src.stride(3) != 1 or src.stride(2) != 3:
+            raise ValueError("src pixels must be interleaved RGB with unit channel stride")
+        B = int(src.shape[0])
+        if len(params) != B:
+            raise ValueError("params and src disagree on the batch size")
+        iW, iH = cfg.imsize
+        if (int(src.shape[1]), int(src.shape[2])) != (iH, iW):
+            raise ValueError(f"src images must be at imsize {cfg.imsize}")
+        if cfg.is_non_fixed and masks is None and self.mask_bits is None:
+            raise ValueError("non-fixed classes need per-image masks (obj_mask, datasets.py:232-233)")
+        W, H = cfg.work_size
+        rec = params.records
+        if params_dev is None:
+            params_dev = self.upload_params(params)
+        d = self.describe(B, src, rec["rect"][:, 2].max(initial=1), rec["rect"][:, 3].max(initial=1), masks, norm_dtype)
+        if want_u8 and out_u8 is None:
+            out_u8 = torch.empty((B, H, W, 3), dtype=torch.uint8, device=self.device)
+        if norm_dtype is not None and out_norm is None:
+            out_norm = torch.empty((B, 3, H, W), dtype=norm_dtype, device=self.device)
+        if y_out is None:
+            y_out = torch.empty((B,), dtype=torch.int64, device=self.device)
+        dbg = torch.zeros((B, DEBUG_DTYPE.itemsize), dtype=torch.uint8, device=self.device) if debug else None
+        mask_t = masks if masks is not None else self.mask_bits
+        lut = self.lut(norm_dtype) if norm_dtype is not None else None
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        code = self.lib.ssad_generate(C.byref(d), _ptr(params_dev), _ptr(src), _ptr(self.donors), _ptr(mask_t), _ptr(lut),
+                                      _ptr(out_u8 if want_u8 else None), _ptr(out_norm), _ptr(y_out), _ptr(dbg),
+                                      None, 0, C.c_void_p(stream))
+        N.check(code, "ssad_generate")
+        out = {"y": y_out}
+        if want_u8:
+            out["x_u8"] = out_u8
+        if norm_dtype is not None:
+            out["x"] = out_norm
+        if debug:
+            out["debug"] = dbg.cpu().numpy().view(DEBUG_DTYPE).reshape(B)
+        return out

@@ -1,0 +1,122 @@
+"""GPU parity (run on the B200 box): the CUDA path through the C ABI against the CPU oracle on the
+same seeded inputs and parameters, and against the golden vectors made from the reference's own code.
+
+Bars: labels, mask decisions, paste positions and every pasted / warped / rotated pixel bit-exact;
+jittered pixels bit-exact as well (the contract allows +-1 LSB; the kernels reproduce Pillow's
+float32 sequence, so any deviation is reported); normalised f32 output bit-exact against
+torchvision's ToTensor+Normalize of the oracle image; bf16 = round-to-nearest-even of that."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import scenarios as S
+from golden import make_golden as G
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("name", S.ALL)
+def test_generate_matches_oracle(name):
+    import gpu_utils as U
+    from oracle import generator as og
+    from PIL import Image
+    sc = S.build(name, 12)
+    out = U.run_cuda(sc)
+    x = out["x_u8"].cpu().numpy()
+    y = out["y"].cpu().numpy()
+    xn = out["x"].cpu().numpy()
+    dbg = out["debug"]
+    for i in range(len(sc.params)):
+        ox, oy, info = S.run_oracle(sc, i)
+        assert int(y[i]) == oy, (name, i)
+        if oy > 0:
+            assert int(dbg["n_coords"][i]) == info["n_coords"]
+            assert bool(dbg["sim"][i]) == info["sim"], (name, i, dbg["cosine"][i], info["cos"])
+            assert abs(dbg["cosine"][i] - info["cos"]) < 1e-12
+            got = [tuple(int(v) for v in dbg["paste"][i][k]) for k in range(len(info["paste"]))]
+            assert got == [tuple(int(v) for v in p) for p in info["paste"]], (name, i)
+        diff = np.abs(x[i].astype(np.int16) - ox.astype(np.int16))
+        assert diff.max() == 0, (name, i, int(diff.max()), int((diff > 0).sum()))
+        ref_n = og.to_tensor_normalize(Image.fromarray(ox)).numpy()
+        assert np.array_equal(xn[i], ref_n), (name, i)
+
+
+@pytest.mark.parametrize("name", S.ALL)
+def test_generate_matches_reference_golden(name):
+    import gpu_utils as U
+    g = np.load(os.path.join(GOLD, f"{name}.npz"))
+    sc = S.build(name, G.BATCH[name])
+    assert bytes(g["sha"]).hex() == G.scenario_sha(sc)
+    out = U.run_cuda(sc)
+    assert np.array_equal(out["y"].cpu().numpy(), g["y"])
+    assert np.array_equal(out["x_u8"].cpu().numpy(), g["x"])
+    assert np.array_equal(out["x"].cpu().numpy()[:2], g["xn"])
+
+
+def test_bf16_output_is_rounded_f32():
+    import gpu_utils as U
+    sc = S.build("image_level", 6)
+    a = U.run_cuda(sc, norm_dtype=torch.float32)["x"]
+    b = U.run_cuda(sc, norm_dtype=torch.bfloat16)["x"]
+    assert torch.equal(a.to(torch.bfloat16), b)
+
+
+def test_no_jitter_no_warp_label0_is_identity():
+    import gpu_utils as U
+    sc = S.build("non_fixed", 4)
+    sc.cfg.jitter = False
+    sc.params = S.sample_params(sc.cfg, 4, np.random.default_rng(3), labels=np.zeros(4, dtype=np.int64))
+    out = U.run_cuda(sc, norm_dtype=None)
+    assert np.array_equal(out["x_u8"].cpu().numpy(), sc.images)
+
+
+def test_large_batch_properties_config2_shape():
+    """BASELINE config 2 at full size (512 x 256x256 windows): size-independent properties --
+    label-0 images equal jitter(window) exactly; defect images differ from jitter-only output
+    only inside the paste boxes; y follows the coverage rule."""
+    import gpu_utils as U
+    from ssad_b200 import synth
+    B, S_, ps = 512, 288, 256
+    cfg = S.GeneratorConfig(subject="bottle", imsize=(S_, S_), patch_localization=True, patch_size=ps,
+                            patch_area_ratio=(0.1, 0.2), scar_area_ratio=(0.01, 0.02))
+    base = synth.object_images(8, S_, S_, 5)
+    imgs = base[np.arange(B) % 8]
+    mask = synth.disc_mask(S_, S_, 0.5)
+    params = S.sample_params(cfg, B, np.random.default_rng(9))
+    sc = S.Scenario("cfg2", cfg, imgs, mask, None, params)
+    gen = U.make_generator(sc)
+    out = U.run_cuda(sc, norm_dtype=None, gen=gen)
+    # same parameters with every label forced to 0 -> jitter only
+    draws0 = {k: v.copy() for k, v in params.draws.items()}
+    draws0["label"][:] = 0
+    sc0 = S.Scenario("cfg2_0", cfg, imgs, mask, None, S.ssad_b200.params_from_draws(cfg, draws0))
+    out0 = U.run_cuda(sc0, norm_dtype=None, gen=gen)
+    x, x0 = out["x_u8"].cpu().numpy(), out0["x_u8"].cpu().numpy()
+    y = out["y"].cpu().numpy()
+    dbg = out["debug"]
+    rec = params.records
+    n_def = 0
+    for i in range(B):
+        cov_ok = 3 * int(S.window_mask(sc, i).sum()) >= cfg.coverage_min3
+        assert y[i] == (params.draws["label"][i] if cov_ok else 0)
+        changed = np.argwhere((x[i] != x0[i]).any(axis=2))
+        if y[i] == 0:
+            assert len(changed) == 0
+            continue
+        n_def += 1
+        if len(changed) == 0:
+            continue
+        # jitter is pointwise except contrast (global mean): compare supports only when contrast mean is unchanged
+        if dbg["contrast_mean"][i] != out0["debug"]["contrast_mean"][i]:
+            continue
+        k = 1 if y[i] == 1 else int(rec["scar_k"][i])
+        w, h = (rec["rect"][i][2], rec["rect"][i][3]) if y[i] == 1 else rec["scar_size"][i]
+        inside = np.zeros(len(changed), dtype=bool)
+        for j in range(k):
+            l, t = dbg["paste"][i][j]
+            inside |= (changed[:, 1] >= l) & (changed[:, 1] < l + w) & (changed[:, 0] >= t) & (changed[:, 0] < t + h)
+        assert inside.all()
+    assert n_def > B // 3
