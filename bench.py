@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""Benchmark of the batched anomaly generator (BASELINE.json metric: synthetic-anomaly images/s and
+HBM GB/s, vs the reference CPU path).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config 1|2|3]
+
+A step = one pass of the hot path (ssad_generate) over one batch of synthetic inputs.  Workload at
+N=1 = BASELINE.json configs[1]: patch-level mode, batch 512 of 256x256 windows cut from 320x320
+synthetic object images, big area_ratio [0.1,0.2], scar [0.01,0.02].  Multi-GPU: the batch shards
+by image, every rank runs the same per-GPU batch (weak scaling), no collective on the data path.
+
+Prints ONE JSON line (rank 0).  `value` = images/s with inputs resident in HBM; `e2e` = the same
+through host buffers (pinned H2D of images + parameter records, D2H of the uint8 result + labels
+inside the timed region); `roofline` for the fused kernel; `cpu_baseline` = the CPU oracle
+(the reference's algorithm on the installed Pillow/torchvision) timed on this box's host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+
+# ------------------------------------------------------------------ workloads
+def make_workload(config: int, batch: int, seed: int = 0):
+    """Returns (cfg, images u8 [B,S,S,3], mask bool [S,S] | None, donors | None, params, name, AB)."""
+    import ssad_b200
+    from ssad_b200 import GeneratorConfig, sample_params, synth
+    uniq = 16   # distinct synthetic images; the batch cycles through them (MVTec classes have 60-391)
+    if config == 2:
+        S, ps = 320, 256
+        cfg = GeneratorConfig(subject="bottle", imsize=(S, S), patch_localization=True, patch_size=ps,
+                              patch_area_ratio=(0.1, 0.2), scar_area_ratio=(0.01, 0.02))
+        base = synth.object_images(uniq, S, S, 1234 + config)
+        mask = synth.disc_mask(S, S, 0.5)
+        donors = None
+        name = "patch-level 3-class, 256x256 windows of 320x320 images, area_ratio [0.1,0.2]/[0.01,0.02]"
+        ab = 2 * 3 * ps * ps + ps * ps // 8
+    elif config == 1:
+        S = 256
+        cfg = GeneratorConfig(subject="bottle", imsize=(S, S))
+        base = synth.object_images(uniq, S, S, 1234 + config)
+        mask = synth.disc_mask(S, S, 0.4)
+        donors = None
+        name = "image-level 3-class, 256x256 fixed-pose object, RandomAffine pre-warp"
+        ab = 2 * 3 * S * S
+    elif config == 3:
+        S = 256
+        cfg = GeneratorConfig(subject="carpet", imsize=(S, S), n_donors=15)
+        base = synth.texture_images(uniq, S, S, 1234 + config, tint=(120, 110, 100))
+        donors = np.concatenate([synth.texture_images(1, S, S, 5000 + k, tint=((37 * k) % 200 + 30, (91 * k) % 200 + 30, (53 * k) % 200 + 30))
+                                 for k in range(15)])
+        mask = None
+        name = "texture class, 256x256, cross-class donor bank (15), all-positive mask, RandomAffine pre-warp"
+        ab = 2 * 3 * S * S
+    else:
+        raise SystemExit(f"config {config} is not a bench line yet")
+    images = base[np.arange(batch) % uniq]
+    params = sample_params(cfg, batch, np.random.default_rng(5678 + config + seed))
+    return cfg, images, mask, donors, params, name, ab
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period: float = 0.01):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.sm_max = [], set(), None
+        self._halt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._halt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self._halt.wait(self.period)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------ CPU oracle timing
+_W = {}
+
+
+def _cpu_init(config, batch):
+    import torch
+    torch.set_num_threads(1)
+    import scenarios as S
+    cfg, images, mask, donors, params, _, _ = make_workload(config, batch)
+    _W["sc"] = S.Scenario("bench", cfg, images, mask, donors, params)
+
+
+def _cpu_run(i):
+    import scenarios as S
+    from PIL import Image
+    from oracle import generator as og
+    x, y, _ = S.run_oracle(_W["sc"], i)
+    xn = og.to_tensor_normalize(Image.fromarray(x))      # datasets.py:392-393, part of the path
+    return int(y)
+
+
+def cpu_oracle_images_per_s(config: int, batch: int, sample: int, procs: int):
+    """images/s of the CPU oracle over `sample` images of the workload on `procs` processes."""
+    import multiprocessing as mp
+    ctx = mp.get_context("fork")
+    with ctx.Pool(procs, initializer=_cpu_init, initargs=(config, batch)) as pool:
+        pool.map(_cpu_run, range(min(procs, batch)))          # warm imports / caches
+        t0 = time.perf_counter()
+        pool.map(_cpu_run, [i % batch for i in range(sample)], chunksize=max(1, sample // (procs * 4)))
+        dt = time.perf_counter() - t0
+    return sample / dt, dt
+
+
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ------------------------------------------------------------------ main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=2)
+    ap.add_argument("--batch", type=int, default=None, help="per-GPU batch (default: the config's)")
+    ap.add_argument("--out", default="u8", choices=["u8", "f32", "bf16"], help="output variant timed for `value`")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--e2e-steps", type=int, default=20)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    batch = args.batch or {1: 96, 2: 512, 3: 1024}[args.config]
+    metric, unit = "synthetic_anomaly_images_per_sec", "images/s"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cores = host_cores()
+        _, _, _, _, _, name, _ = make_workload(args.config, 8)
+        # bound the run: ~90 images/s/core expected; keep (steps + warmup) * sample under ~2 min
+        per_core = 60.0
+        sample = int(max(8, min(batch, 120.0 * per_core * cores / max(1, args.steps + args.warmup))))
+        import multiprocessing as mp
+        ctx = mp.get_context("fork")
+        with ctx.Pool(cores, initializer=_cpu_init, initargs=(args.config, batch)) as pool:
+            idx = [i % batch for i in range(sample)]
+            for _ in range(args.warmup):
+                pool.map(_cpu_run, idx, chunksize=max(1, sample // (cores * 4)))
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                pool.map(_cpu_run, idx, chunksize=max(1, sample // (cores * 4)))
+            dt = time.perf_counter() - t0
+        v = sample * args.steps / dt
+        line = {"impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": name, "batch_per_step_sample": sample},
+                "cpu_baseline": {"value": v, "unit": unit, "cores": cores, "kind": "port",
+                                 "sample": f"{sample} images/step of the workload, {cores} processes x 1 thread; the reference is "
+                                           "pure Python and cannot travel to this box, so its algorithm runs as oracle/generator.py "
+                                           "on the installed Pillow/torchvision"},
+                "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import torch.distributed as dist
+    from ssad_b200.generator import BatchGenerator
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    cfg, images, mask, donors, params, name, ab = make_workload(args.config, batch, seed=rank)
+    gen = BatchGenerator(cfg, dev, mask=mask, donors=donors)
+    W, H = cfg.work_size
+    norm_dtype = {"u8": None, "f32": torch.float32, "bf16": torch.bfloat16}[args.out]
+    want_u8 = args.out == "u8"
+    if args.out == "f32":
+        ab = ab - 3 * H * W + 12 * H * W
+    elif args.out == "bf16":
+        ab = ab - 3 * H * W + 6 * H * W
+    # two resident input sets, alternated, so consecutive steps never touch the same lines
+    # (one step already moves > L2: e.g. config 2 = 157 MB in + 100 MB out vs 126 MB L2)
+    srcs = [torch.from_numpy(images).to(dev), torch.from_numpy(np.roll(images, 1, axis=0).copy()).to(dev)]
+    pdev = gen.upload_params(params)
+    outs_u8 = [torch.empty((batch, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)] if want_u8 else [None, None]
+    outs_n = [torch.empty((batch, 3, H, W), dtype=norm_dtype, device=dev) for _ in range(2)] if norm_dtype else [None, None]
+    y_out = torch.empty((batch,), dtype=torch.int64, device=dev)
+
+    plans = [gen.plan(srcs[j], params, want_u8=want_u8, norm_dtype=norm_dtype, params_dev=pdev,
+                      out_u8=outs_u8[j], out_norm=outs_n[j], y_out=y_out) for j in range(2)]
+
+    def step(i):
+        gen.run(plans[i & 1])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = world * batch / (ms_per_step * 1e-3)
+
+    # ---- e2e: host buffers in, host buffers out, copies inside the timed region
+    h_src = [torch.from_numpy(images).pin_memory(), torch.from_numpy(np.roll(images, 1, axis=0).copy()).pin_memory()]
+    h_out = torch.empty((batch, H, W, 3), dtype=torch.uint8).pin_memory()
+    h_y = torch.empty((batch,), dtype=torch.int64).pin_memory()
+    d_src = torch.empty_like(srcs[0])
+    d_out = torch.empty((batch, H, W, 3), dtype=torch.uint8, device=dev)
+    rec_bytes = params.records.nbytes
+
+    def e2e_step(i):
+        d_src.copy_(h_src[i & 1], non_blocking=True)
+        p = gen.upload_params(params)
+        gen.generate(d_src, params, want_u8=True, norm_dtype=None, params_dev=p, out_u8=d_out, y_out=y_out)
+        h_out.copy_(d_out, non_blocking=True)
+        h_y.copy_(y_out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the caller owns the result when the call returns
+
+    for i in range(3):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.e2e_steps):
+        e2e_step(i)
+    barrier()
+    e2e_dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_dt], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_dt = float(t.item())
+    e2e_value = world * batch * args.e2e_steps / e2e_dt
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = batch * ab / (ms_per_step * 1e-3) / 1e9      # per GPU: one launch = one batch
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"config{args.config}_{args.out}")
+    except Exception:
+        pass
+    line = {
+        "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": name, "batch_per_gpu": batch, "global_batch": batch * world, "output": args.out,
+                   "l2": "two alternating resident input/output sets; one step moves more than the 126 MB L2",
+                   "parallelism": f"image-sharded x{world}, no collective"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "kernel": "generate_fused_kernel", "algorithmic_bytes_per_image": ab,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s"},
+        "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(images.nbytes + rec_bytes),
+                "d2h_bytes_per_step": int(h_out.numel() + h_y.numel() * 8), "steps": args.e2e_steps},
+        "gpu_launches": args.steps,
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu:
+        cores = host_cores()
+        sample = int(min(batch, max(64, 8 * cores)))
+        v, dt = cpu_oracle_images_per_s(args.config, batch, sample, cores)
+        v1, dt1 = cpu_oracle_images_per_s(args.config, batch, min(sample, 48), 1)
+        line["cpu_baseline"] = {"value": v, "unit": unit, "cores": cores, "kind": "port",
+                                "sample": f"{sample} images of the same batch, {cores} processes x 1 torch thread ({dt:.1f} s); "
+                                          f"1 process: {v1:.1f} images/s",
+                                "value_1core": v1}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

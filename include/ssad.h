@@ -92,6 +92,7 @@ typedef struct SsadBatchDesc {
     int32_t coverage_min3;     /* patch mode: label := 0 iff 3 * popcount(mask window) < coverage_min3 (datasets.py:258-259); 0 = off */
     int32_t max_patch_w, max_patch_h; /* upper bounds of rect[2], rect[3] over the batch (polygon table sizing) */
     int32_t out_norm_dtype;    /* SSAD_NORM_* */
+    int32_t crop_align16;      /* 1: caller guarantees (3 * crop_off.x) % 16 == 0 for every image (lets TMA land the window dense) */
     int64_t out_u8_pitch;      /* bytes per output row (>= 3 * width) */
     int64_t out_u8_stride;     /* bytes per output image */
 } SsadBatchDesc;

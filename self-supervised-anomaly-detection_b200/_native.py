@@ -25,7 +25,7 @@ class SsadBatchDesc(C.Structure):
         ("mask_height", C.c_int32), ("mask_width", C.c_int32),
         ("box_poly", C.c_int32 * 4), ("box_scar", C.c_int32 * 4),
         ("coverage_min3", C.c_int32), ("max_patch_w", C.c_int32), ("max_patch_h", C.c_int32),
-        ("out_norm_dtype", C.c_int32),
+        ("out_norm_dtype", C.c_int32), ("crop_align16", C.c_int32),
         ("out_u8_pitch", C.c_int64), ("out_u8_stride", C.c_int64),
     ]
 

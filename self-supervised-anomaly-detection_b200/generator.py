@@ -45,6 +45,10 @@ def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
+class Plan:
+    """Frozen arguments of one ssad_generate call (keeps the tensors alive)."""
+
+
 class BatchGenerator:
     """Batched replacement of ``PretextTaskDataset.__getitem__`` (reference datasets.py:209-394).
 
@@ -95,7 +99,7 @@ class BatchGenerator:
         t = torch.from_numpy(rec.view(np.uint8).reshape(len(rec), IMAGE_PARAMS_DTYPE.itemsize))
         return t.to(self.device, non_blocking=True)
 
-    def describe(self, batch: int, src: torch.Tensor, max_pw: int, max_ph: int, masks, norm_dtype) -> N.SsadBatchDesc:
+    def describe(self, batch: int, src: torch.Tensor, max_pw: int, max_ph: int, masks, norm_dtype, crop_aligned=False) -> N.SsadBatchDesc:
         cfg = self.cfg
         W, H = cfg.work_size
         d = N.SsadBatchDesc()
@@ -124,7 +128,41 @@ class BatchGenerator:
         d.max_patch_w, d.max_patch_h = max(int(max_pw), 1), max(int(max_ph), 1)
         d.out_norm_dtype = {None: N.SSAD_NORM_NONE, torch.float32: N.SSAD_NORM_F32, torch.bfloat16: N.SSAD_NORM_BF16}[norm_dtype]
         d.out_u8_pitch, d.out_u8_stride = 3 * W, 3 * W * H
+        d.crop_align16 = int(crop_aligned)
         return d
+
+    def plan(self, src: torch.Tensor, params: ParamBatch, *, masks=None, want_u8=True, norm_dtype=None, debug=False,
+             params_dev=None, out_u8=None, out_norm=None, y_out=None) -> "Plan":
+        """Validate once and freeze descriptor + device pointers of one ssad_generate call; ``run(plan)``
+        then costs one FFI call (steady-state loops, CUDA-graph capture)."""
+        cfg = self.cfg
+        B = int(src.shape[0])
+        W, H = cfg.work_size
+        rec = params.records
+        if params_dev is None:
+            params_dev = self.upload_params(params)
+        crop_aligned = bool(np.all((rec["crop_off"][:, 0].astype(np.int64) * 3) % 16 == 0))
+        d = self.describe(B, src, rec["rect"][:, 2].max(initial=1), rec["rect"][:, 3].max(initial=1), masks, norm_dtype,
+                          crop_aligned)
+        if want_u8 and out_u8 is None:
+            out_u8 = torch.empty((B, H, W, 3), dtype=torch.uint8, device=self.device)
+        if norm_dtype is not None and out_norm is None:
+            out_norm = torch.empty((B, 3, H, W), dtype=norm_dtype, device=self.device)
+        if y_out is None:
+            y_out = torch.empty((B,), dtype=torch.int64, device=self.device)
+        dbg = torch.zeros((B, DEBUG_DTYPE.itemsize), dtype=torch.uint8, device=self.device) if debug else None
+        mask_t = masks if masks is not None else self.mask_bits
+        lut = self.lut(norm_dtype) if norm_dtype is not None else None
+        pl = Plan()
+        pl.desc, pl.params_dev, pl.src, pl.mask_t, pl.lut = d, params_dev, src, mask_t, lut
+        pl.out_u8, pl.out_norm, pl.y_out, pl.dbg = (out_u8 if want_u8 else None), out_norm, y_out, dbg
+        pl.args = (C.byref(d), _ptr(params_dev), _ptr(src), _ptr(self.donors), _ptr(mask_t), _ptr(lut),
+                   _ptr(pl.out_u8), _ptr(out_norm), _ptr(y_out), _ptr(dbg), None, 0)
+        return pl
+
+    def run(self, plan: "Plan") -> None:
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.lib.ssad_generate(*plan.args, C.c_void_p(stream)), "ssad_generate")
 
     def generate(self, src: torch.Tensor, params: ParamBatch, *, masks: Optional[torch.Tensor] = None,
                  want_u8: bool = True, norm_dtype: Optional[torch.dtype] = None, debug: bool = False,
@@ -146,25 +184,10 @@ class BatchGenerator:
             raise ValueError(f"src images must be at imsize {cfg.imsize}")
         if cfg.is_non_fixed and masks is None and self.mask_bits is None:
             raise ValueError("non-fixed classes need per-image masks (obj_mask, datasets.py:232-233)")
-        W, H = cfg.work_size
-        rec = params.records
-        if params_dev is None:
-            params_dev = self.upload_params(params)
-        d = self.describe(B, src, rec["rect"][:, 2].max(initial=1), rec["rect"][:, 3].max(initial=1), masks, norm_dtype)
-        if want_u8 and out_u8 is None:
-            out_u8 = torch.empty((B, H, W, 3), dtype=torch.uint8, device=self.device)
-        if norm_dtype is not None and out_norm is None:
-            out_norm = torch.empty((B, 3, H, W), dtype=norm_dtype, device=self.device)
-        if y_out is None:
-            y_out = torch.empty((B,), dtype=torch.int64, device=self.device)
-        dbg = torch.zeros((B, DEBUG_DTYPE.itemsize), dtype=torch.uint8, device=self.device) if debug else None
-        mask_t = masks if masks is not None else self.mask_bits
-        lut = self.lut(norm_dtype) if norm_dtype is not None else None
-        stream = torch.cuda.current_stream(self.device).cuda_stream
-        code = self.lib.ssad_generate(C.byref(d), _ptr(params_dev), _ptr(src), _ptr(self.donors), _ptr(mask_t), _ptr(lut),
-                                      _ptr(out_u8 if want_u8 else None), _ptr(out_norm), _ptr(y_out), _ptr(dbg),
-                                      None, 0, C.c_void_p(stream))
-        N.check(code, "ssad_generate")
+        plan = self.plan(src, params, masks=masks, want_u8=want_u8, norm_dtype=norm_dtype, debug=debug,
+                         params_dev=params_dev, out_u8=out_u8, out_norm=out_norm, y_out=y_out)
+        self.run(plan)
+        out_u8, out_norm, y_out, dbg = plan.out_u8, plan.out_norm, plan.y_out, plan.dbg
         out = {"y": y_out}
         if want_u8:
             out["x_u8"] = out_u8
