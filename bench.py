@@ -124,11 +124,19 @@ _W = {}
 
 
 def _cpu_init(config, batch):
+    """Worker start-up: one torch / BLAS thread per process (as DataLoader workers run),
+    the workload, and one untimed item so that imports (sklearn, torchvision) are outside the timed region."""
     import torch
     torch.set_num_threads(1)
+    try:
+        from threadpoolctl import threadpool_limits
+        _W["tp"] = threadpool_limits(1)
+    except Exception:
+        pass
     import scenarios as S
     cfg, images, mask, donors, params, _, _ = make_workload(config, batch)
     _W["sc"] = S.Scenario("bench", cfg, images, mask, donors, params)
+    _cpu_run(0)
 
 
 def _cpu_run(i):
@@ -140,16 +148,22 @@ def _cpu_run(i):
     return int(y)
 
 
-def cpu_oracle_images_per_s(config: int, batch: int, sample: int, procs: int):
-    """images/s of the CPU oracle over `sample` images of the workload on `procs` processes."""
+def cpu_oracle_images_per_s(config: int, batch: int, sample: int, procs: int, target_s: float = 0.0):
+    """images/s of the CPU oracle over `sample` images of the workload on `procs` processes (each worker is
+    warmed by its initializer).  With target_s > 0 the sample is re-sized from a pilot run so that the timed
+    region lasts about target_s seconds.  Returns (images/s, seconds, images)."""
     import multiprocessing as mp
     ctx = mp.get_context("fork")
     with ctx.Pool(procs, initializer=_cpu_init, initargs=(config, batch)) as pool:
-        pool.map(_cpu_run, range(min(procs, batch)))          # warm imports / caches
-        t0 = time.perf_counter()
-        pool.map(_cpu_run, [i % batch for i in range(sample)], chunksize=max(1, sample // (procs * 4)))
-        dt = time.perf_counter() - t0
-    return sample / dt, dt
+        def run(n):
+            t0 = time.perf_counter()
+            pool.map(_cpu_run, [i % batch for i in range(n)], chunksize=max(1, n // (procs * 8)))
+            return time.perf_counter() - t0
+        dt = run(sample)
+        if target_s > 0:
+            sample = int(max(sample, min(20000, target_s * sample / dt)))
+            dt = run(sample)
+    return sample / dt, dt, sample
 
 
 def host_cores() -> int:
@@ -330,12 +344,11 @@ def main():
     }
     if world == 1 and not args.no_cpu:
         cores = host_cores()
-        sample = int(min(batch, max(64, 8 * cores)))
-        v, dt = cpu_oracle_images_per_s(args.config, batch, sample, cores)
-        v1, dt1 = cpu_oracle_images_per_s(args.config, batch, min(sample, 48), 1)
+        v, dt, sample = cpu_oracle_images_per_s(args.config, batch, 4 * cores, cores, target_s=12.0)
+        v1, dt1, s1 = cpu_oracle_images_per_s(args.config, batch, 16, 1, target_s=4.0)
         line["cpu_baseline"] = {"value": v, "unit": unit, "cores": cores, "kind": "port",
-                                "sample": f"{sample} images of the same batch, {cores} processes x 1 torch thread ({dt:.1f} s); "
-                                          f"1 process: {v1:.1f} images/s",
+                                "sample": f"{sample} images cycling through the same batch, {cores} processes x 1 torch/BLAS thread "
+                                          f"({dt:.1f} s); 1 process: {v1:.1f} images/s over {s1} images",
                                 "value_1core": v1}
     print(json.dumps(line))
     if world > 1:
