@@ -135,11 +135,23 @@ int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, cons
                   void* workspace, size_t workspace_bytes, void* stream);
 size_t ssad_generate_workspace(const SsadBatchDesc* desc);
 
-/* obj_mask (dataset_generator.py:27-39) for a batch: canny(sigma 1.5, 5/255, 15/255) -> dilate 3x3 -> close 3x3
- * -> fill holes -> erode 4x4 -> largest 8-connected component, bit-packed. */
+/* Host-computed constants of skimage.feature.canny(image, sigma=1.5, low_threshold=5, high_threshold=15) as
+ * obj_mask calls it (dataset_generator.py:30).  They are inputs (not computed by the library) because the Gaussian
+ * taps come from numpy's exp on the caller's machine -- scipy.ndimage._filters._gaussian_kernel1d(1.5, 0, 6) -- and
+ * the masks must be bit-identical with the CPU libraries running there. */
+typedef struct SsadCannyConsts {
+    double gauss_w[13];        /* normalised taps exp(-x^2 / (2 sigma^2)), x = -6..6 */
+    double low, high;          /* 5 / 255, 15 / 255 (uint8 input: thresholds are divided by the dtype max) */
+    double eps;                /* numpy.finfo(float64).eps, added to the bleed-over divisor */
+} SsadCannyConsts;
+
+/* obj_mask (dataset_generator.py:27-39) for a batch: convert('L') -> canny(sigma 1.5, 5/255, 15/255) -> dilate 3x3
+ * -> close 3x3 -> fill holes -> erode 4x4 -> largest 8-connected component, bit-packed (1 = object).
+ * 13 <= width <= 1024, height >= 13.  workspace: ssad_obj_mask_workspace() bytes, 16-byte aligned. */
 int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
-                  int64_t src_stride, uint32_t* mask_bits, int32_t mask_pitch_words, int64_t mask_stride_words,
-                  void* workspace, size_t workspace_bytes, void* stream);
+                  int64_t src_stride, const SsadCannyConsts* consts /* host */, uint32_t* mask_bits,
+                  int32_t mask_pitch_words, int64_t mask_stride_words, void* workspace, size_t workspace_bytes,
+                  void* stream);
 size_t ssad_obj_mask_workspace(int32_t batch, int32_t height, int32_t width);
 
 /* Unit entry points (parity tests of the individual reference routines). */

@@ -30,6 +30,10 @@ class SsadBatchDesc(C.Structure):
     ]
 
 
+class SsadCannyConsts(C.Structure):
+    _fields_ = [("gauss_w", C.c_double * 13), ("low", C.c_double), ("high", C.c_double), ("eps", C.c_double)]
+
+
 EXPORTS = {
     # name: (restype, argtypes)
     "ssad_version": (C.c_int, []),
@@ -40,7 +44,7 @@ EXPORTS = {
     "ssad_sizeof_debug": (C.c_size_t, []),
     "ssad_generate": (C.c_int, [C.POINTER(SsadBatchDesc)] + [C.c_void_p] * 10 + [C.c_size_t, C.c_void_p]),
     "ssad_generate_workspace": (C.c_size_t, [C.POINTER(SsadBatchDesc)]),
-    "ssad_obj_mask": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+    "ssad_obj_mask": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                 C.c_int32, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
     "ssad_obj_mask_workspace": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "ssad_polygon_mask": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),

@@ -196,3 +196,54 @@ class BatchGenerator:
         if debug:
             out["debug"] = dbg.cpu().numpy().view(DEBUG_DTYPE).reshape(B)
         return out
+
+
+# ---------------------------------------------------------------------- obj_mask on device
+def canny_consts(sigma: float = 1.5, low_threshold: float = 5, high_threshold: float = 15) -> "N.SsadCannyConsts":
+    """Constants of ``canny(gray, sigma=1.5, low_threshold=5, high_threshold=15)`` (dataset_generator.py:30) for a
+    uint8 image, computed as the CPU libraries compute them: taps as ``scipy.ndimage._filters._gaussian_kernel1d``
+    (truncate 4.0 -> radius 6), thresholds divided by the dtype max."""
+    radius = int(4.0 * float(sigma) + 0.5)
+    if radius != 6:
+        raise ValueError("the device kernel is built for radius 6 (sigma = 1.5)")
+    sigma2 = sigma * sigma
+    x = np.arange(-radius, radius + 1)
+    phi = np.exp(-0.5 / sigma2 * x ** 2)
+    phi = (phi / phi.sum())[::-1]
+    k = N.SsadCannyConsts()
+    k.gauss_w = (C.c_double * 13)(*[float(v) for v in phi])
+    k.low, k.high = low_threshold / 255.0, high_threshold / 255.0
+    k.eps = float(np.finfo(np.float64).eps)
+    return k
+
+
+def unpack_mask_bits(bits: np.ndarray, width: int) -> np.ndarray:
+    """uint32/int32 [..., H, nw] -> bool [..., H, width] (inverse of ``pack_mask_bits``)."""
+    b = np.ascontiguousarray(bits).view(np.uint8)
+    return np.unpackbits(b, axis=-1, bitorder="little")[..., :width].astype(bool)
+
+
+def obj_mask_batch(src: torch.Tensor, out: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``obj_mask`` (dataset_generator.py:27-39) for every image of ``src`` (uint8 [B, H, W, 3] on a CUDA device)
+    -> bit-packed masks int32 [B, H, ceil(W/32)] on the same device (the layout ``BatchGenerator.generate(masks=...)``
+    takes).  Runs on the current stream; no host synchronisation."""
+    if src.device.type != "cuda" or src.dtype != torch.uint8 or src.dim() != 4 or src.shape[-1] != 3:
+        raise ValueError("src must be a uint8 [B, H, W, 3] CUDA tensor")
+    if src.stride(3) != 1 or src.stride(2) != 3:
+        raise ValueError("src pixels must be interleaved RGB with unit channel stride")
+    lib = N.load()
+    B, H, W = int(src.shape[0]), int(src.shape[1]), int(src.shape[2])
+    nw = (W + 31) // 32
+    if out is None:
+        out = torch.empty((B, H, nw), dtype=torch.int32, device=src.device)
+    need = int(lib.ssad_obj_mask_workspace(B, H, W))
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty((max(need, 16),), dtype=torch.uint8, device=src.device)
+    k = canny_consts()
+    with torch.cuda.device(src.device):
+        stream = torch.cuda.current_stream(src.device).cuda_stream
+        N.check(lib.ssad_obj_mask(B, H, W, C.c_void_p(src.data_ptr()), int(src.stride(1)), int(src.stride(0)), C.byref(k),
+                                  C.c_void_p(out.data_ptr()), int(out.stride(1)), int(out.stride(0)),
+                                  C.c_void_p(workspace.data_ptr()), workspace.numel() * workspace.element_size(),
+                                  C.c_void_p(stream)), "ssad_obj_mask")
+    return out

@@ -1,0 +1,71 @@
+"""-m gpu: ssad_obj_mask (canny -> morphology -> fill -> erosion -> largest component on device) against the CPU
+restatement oracle/objmask.py (dataset_generator.py:27-39).  Bar: masks bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from ssad_b200 import synth
+from ssad_b200.generator import obj_mask_batch, unpack_mask_bits
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(images: np.ndarray) -> np.ndarray:
+    src = torch.from_numpy(np.ascontiguousarray(images)).cuda()
+    bits = obj_mask_batch(src)
+    torch.cuda.synchronize()
+    return unpack_mask_bits(bits.cpu().numpy(), images.shape[2])
+
+
+def _oracle(images: np.ndarray) -> np.ndarray:
+    from oracle import objmask
+    return np.stack([objmask.obj_mask_array(im) for im in images])
+
+
+def _check(images, what):
+    got, want = _run(images), _oracle(images)
+    for i in range(len(images)):
+        diff = int(np.count_nonzero(got[i] != want[i]))
+        assert diff == 0, f"{what}: image {i}: {diff} mask pixels differ (oracle area {int(want[i].sum())}, device {int(got[i].sum())})"
+
+
+@pytest.mark.parametrize("size", [(128, 128), (256, 256), (96, 160), (100, 77), (64, 1024)])
+def test_screw_like(size):
+    H, W = size
+    _check(synth.screw_images(6, H, W, 31 + H + W), f"screw {H}x{W}")
+
+
+def test_object_and_texture_images():
+    _check(synth.object_images(4, 192, 192, 5), "object")
+    _check(synth.texture_images(4, 160, 224, 6), "texture")          # many edge fragments / components
+
+
+def test_noise_many_components():
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, (3, 120, 150, 3), dtype=np.uint8)
+    _check(img, "iid noise")
+    blocks = np.kron(rng.integers(0, 2, (3, 12, 15, 1), dtype=np.uint8), np.ones((1, 10, 10, 3), np.uint8)) * 200 + 20
+    _check(blocks.astype(np.uint8), "checker blocks")
+
+
+def test_flat_image_degenerate_all_true():
+    img = np.full((2, 64, 96, 3), 128, dtype=np.uint8)
+    got = _run(img)
+    assert got.all()                                                   # no edges -> label 0 wins -> all True
+    _check(img, "flat")
+
+
+def test_spiral_needs_many_sweeps():
+    # a long spiral corridor: reachability has to reverse direction many times
+    H = W = 128
+    img = np.full((1, H, W, 3), 200, dtype=np.uint8)
+    yy, xx = np.mgrid[0:H, 0:W]
+    r = np.hypot(yy - 64, xx - 64)
+    th = np.arctan2(yy - 64, xx - 64)
+    spiral = (np.abs(((r - 6 * th / np.pi) % 12) - 6) < 1.5) & (r < 60)
+    img[0][spiral] = 30
+    _check(img, "spiral")
+
+
+def test_1024_single():
+    _check(synth.screw_images(1, 1024, 1024, 77), "screw 1024")
