@@ -256,7 +256,7 @@ __device__ __forceinline__ uint32_t block_sum_u32(uint32_t v, uint32_t* scratch 
 
 // cosine of the mean colours as check_color_similarity + sklearn compute it (float64):
 // mean = (sum / n) / 255 per channel; rows L2-normalised; dot.
-__device__ inline double cosine_of_means(const uint32_t* s1, double n1, const uint32_t* s2, double n2) {
+__device__ __forceinline__ double cosine_of_means(const uint32_t* s1, double n1, const uint32_t* s2, double n2) {
     double a[3], b[3];
     for (int c = 0; c < 3; ++c) {
         a[c] = __ddiv_rn(__ddiv_rn((double)s1[c], n1), 255.0);

@@ -512,6 +512,10 @@ int ssad_launch_cluster(const SsadBatchDesc& d, const SsadImageParams* params, c
                         const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
                         SsadDebug* debug, cudaStream_t stream);
 
+int ssad_launch_v3(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
+                   const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
+                   SsadDebug* debug, cudaStream_t stream);
+
 int ssad_set_cuda_error(cudaError_t e) {
     strncpy(g_cuda_err, cudaGetErrorString(e), sizeof(g_cuda_err) - 1);
     return SSAD_ELAUNCH;
@@ -541,14 +545,21 @@ extern "C" int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* p
         return SSAD_EALIGN;
     if (out_u8 && (d.out_u8_pitch != 3ll * d.width || d.out_u8_stride != 3ll * d.width * d.height)) return SSAD_EUNSUPPORTED;
     if (((long long)d.height * d.width) % ssad::kUnitPix != 0) return SSAD_EUNSUPPORTED;
-    // B200 path: persistent 2-CTA clusters + TMA double buffering (ssad_generate_cluster.cu); the generic
-    // one-CTA-per-image kernel below serves shapes / alignments the tensor map cannot express.
+    // B200 paths, in order of preference: v3 (clusters of 1-8 CTAs, resident or streaming rows, ssad_generate_v3.cu),
+    // the 2-CTA cluster kernel (ssad_generate_cluster.cu), and the generic one-CTA-per-image kernel below for
+    // shapes / alignments the tensor maps cannot express.  SSAD_KERNEL=v3|cluster|generic pins one (tests, profiling).
     const char* force = getenv("SSAD_KERNEL");
-    if (!(force && strcmp(force, "generic") == 0)) {
+    const bool only_v3 = force && strcmp(force, "v3") == 0, only_cluster = force && strcmp(force, "cluster") == 0;
+    const bool only_generic = force && strcmp(force, "generic") == 0;
+    if (!only_cluster && !only_generic) {
+        int rc = ssad_launch_v3(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug,
+                                static_cast<cudaStream_t>(stream));
+        if (rc != SSAD_EUNSUPPORTED || only_v3) return rc;
+    }
+    if (!only_generic) {
         int rc = ssad_launch_cluster(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug,
                                      static_cast<cudaStream_t>(stream));
-        if (rc != SSAD_EUNSUPPORTED) return rc;
-        if (force && strcmp(force, "cluster") == 0) return rc;
+        if (rc != SSAD_EUNSUPPORTED || only_cluster) return rc;
     }
     const ssad::SmemLayout L = ssad::smem_layout(d);
     int dev = 0, max_smem = 0;

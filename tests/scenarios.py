@@ -96,6 +96,25 @@ def build(name: str, batch: int = 12, seed: int = 0) -> Scenario:
         imgs = np.clip(rng.normal(128, 20, (batch, S, S, 1)).repeat(3, axis=3), 0, 255).astype(np.uint8)
         mask = synth.disc_mask(S, S)
         donors = None
+    elif name == "big_fixed_768":      # rows stream through chunk buffers (does not fit shared memory), warp gather
+        S = 768
+        cfg = GeneratorConfig(subject="bottle", imsize=(S, S))
+        imgs = synth.object_images(batch, S, S, 19 + seed)
+        mask = synth.disc_mask(S, S)
+        donors = None
+    elif name == "big_non_fixed_1024":  # config 4 shape: 1024x1024, per-image obj_mask, no warp -> TMA streaming
+        S = 1024
+        cfg = GeneratorConfig(subject="screw", imsize=(S, S))
+        imgs = synth.screw_images(batch, S, S, 20 + seed)
+        mask = "per_image"
+        donors = None
+    elif name == "mid_texture_512":     # 512x512: eight CTAs per image, rows resident
+        S = 512
+        cfg = GeneratorConfig(subject="carpet", imsize=(S, S), n_donors=15)
+        imgs = synth.texture_images(batch, S, S, 21 + seed, tint=(120, 110, 100))
+        donors = np.concatenate([synth.texture_images(1, S, S, 300 + k, tint=rng.integers(40, 220, 3))
+                                 for k in range(15)])
+        mask = None
     else:
         raise KeyError(name)
     if isinstance(mask, str):
@@ -105,6 +124,8 @@ def build(name: str, batch: int = 12, seed: int = 0) -> Scenario:
     params = sample_params(cfg, batch, np.random.default_rng(2000 + seed), labels=labels)
     return Scenario(name, cfg, imgs, mask, donors, params)
 
+
+BIG = ["big_fixed_768", "big_non_fixed_1024", "mid_texture_512"]      # no golden vectors (size); oracle parity only
 
 ALL = ["image_level", "image_level_256", "patch_level", "patch_level_32", "texture", "non_fixed",
        "empty_mask", "single_pixel_mask", "flat_grey"]

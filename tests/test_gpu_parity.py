@@ -18,12 +18,14 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
-@pytest.mark.parametrize("name", S.ALL)
-def test_generate_matches_oracle(name):
+def _check_against_oracle(name, batch, monkeypatch=None, env=None):
     import gpu_utils as U
     from oracle import generator as og
     from PIL import Image
-    sc = S.build(name, 12)
+    sc = S.build(name, batch)
+    if env:
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
     out = U.run_cuda(sc)
     x = out["x_u8"].cpu().numpy()
     y = out["y"].cpu().numpy()
@@ -42,6 +44,30 @@ def test_generate_matches_oracle(name):
         assert diff.max() == 0, (name, i, int(diff.max()), int((diff > 0).sum()))
         ref_n = og.to_tensor_normalize(Image.fromarray(ox)).numpy()
         assert np.array_equal(xn[i], ref_n), (name, i)
+
+
+@pytest.mark.parametrize("name", S.ALL)
+def test_generate_matches_oracle(name):
+    _check_against_oracle(name, 12)
+
+
+@pytest.mark.parametrize("name", S.BIG)
+def test_generate_big_images_match_oracle(name):
+    """Images whose rows do not fit one CTA's shared memory: clusters of eight CTAs, rows resident (512) or
+    streamed through TMA chunk buffers once per pass (768, 1024)."""
+    _check_against_oracle(name, 5)
+
+
+@pytest.mark.parametrize("kernel", ["v3", "cluster", "generic"])
+@pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture"])
+def test_every_kernel_variant_matches_oracle(name, kernel, monkeypatch):
+    _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": kernel})
+
+
+@pytest.mark.parametrize("csize", ["1", "2", "4", "8"])
+@pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed"])
+def test_v3_cluster_sizes_match_oracle(name, csize, monkeypatch):
+    _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v3", "SSAD_V3_C": csize})
 
 
 @pytest.mark.parametrize("name", S.ALL)
