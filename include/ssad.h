@@ -95,6 +95,8 @@ typedef struct SsadBatchDesc {
     int32_t crop_align16;      /* 1: caller guarantees (3 * crop_off.x) % 16 == 0 for every image (lets TMA land the window dense) */
     int64_t out_u8_pitch;      /* bytes per output row (>= 3 * width) */
     int64_t out_u8_stride;     /* bytes per output image */
+    int32_t any_warp;          /* 1: some records have warp_en set (sizes the workspace: x is materialised once per batch) */
+    int32_t reserved0;
 } SsadBatchDesc;
 
 /* Optional per-image trace of the data-dependent decisions, for parity tests. */
@@ -128,7 +130,9 @@ size_t ssad_sizeof_debug(void);
  *   out_u8     [batch][height][width][3] uint8, nullable
  *   out_norm   [batch][3][height][width] f32/bf16 = Normalize(ToTensor(x)) (datasets.py:392-393), nullable
  *   y_out      [batch] int64 labels after the coverage rule, nullable
- *   debug      [batch] SsadDebug, nullable */
+ *   debug      [batch] SsadDebug, nullable
+ *   workspace  ssad_generate_workspace(desc) bytes, 256-byte aligned: per-image decisions and accumulators,
+ *              polygon bit rows, and (any_warp) the warped images */
 int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, const uint8_t* src,
                   const uint8_t* donor_bank, const uint32_t* mask_bits, const void* norm_lut,
                   uint8_t* out_u8, void* out_norm, int64_t* y_out, SsadDebug* debug,

@@ -516,21 +516,25 @@ int ssad_launch_v3(const SsadBatchDesc& d, const SsadImageParams* params, const 
                    const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
                    SsadDebug* debug, cudaStream_t stream);
 
+int ssad_launch_v4(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
+                   const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
+                   SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+size_t ssad_v4_workspace(const SsadBatchDesc& d);
+
 int ssad_set_cuda_error(cudaError_t e) {
     strncpy(g_cuda_err, cudaGetErrorString(e), sizeof(g_cuda_err) - 1);
     return SSAD_ELAUNCH;
 }
 
 extern "C" size_t ssad_generate_workspace(const SsadBatchDesc* desc) {
-    (void)desc;
-    return 0;   // the fused path keeps every intermediate on chip
+    if (!desc || desc->batch <= 0) return 0;
+    return ssad_v4_workspace(*desc);   // 0 for shapes only the on-chip kernels serve (they need no workspace)
 }
 
 extern "C" int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, const uint8_t* src,
                              const uint8_t* donor_bank, const uint32_t* mask_bits, const void* norm_lut,
                              uint8_t* out_u8, void* out_norm, int64_t* y_out, SsadDebug* debug,
                              void* workspace, size_t workspace_bytes, void* stream) {
-    (void)workspace; (void)workspace_bytes;
     if (!desc || !params || !src) return SSAD_EINVAL;
     const SsadBatchDesc& d = *desc;
     if (d.batch < 0 || d.height <= 0 || d.width <= 0 || d.src_pitch < 3ll * d.width) return SSAD_EINVAL;
@@ -545,12 +549,20 @@ extern "C" int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* p
         return SSAD_EALIGN;
     if (out_u8 && (d.out_u8_pitch != 3ll * d.width || d.out_u8_stride != 3ll * d.width * d.height)) return SSAD_EUNSUPPORTED;
     if (((long long)d.height * d.width) % ssad::kUnitPix != 0) return SSAD_EUNSUPPORTED;
-    // B200 paths, in order of preference: v3 (clusters of 1-8 CTAs, resident or streaming rows, ssad_generate_v3.cu),
-    // the 2-CTA cluster kernel (ssad_generate_cluster.cu), and the generic one-CTA-per-image kernel below for
-    // shapes / alignments the tensor maps cannot express.  SSAD_KERNEL=v3|cluster|generic pins one (tests, profiling).
+    // B200 paths, in order of preference: v4 (pipeline of barrier-free streaming kernels, ssad_generate_v4.cu), v3
+    // (clusters of 1-8 CTAs, rows resident or streamed, ssad_generate_v3.cu), the 2-CTA cluster kernel
+    // (ssad_generate_cluster.cu) and the generic one-CTA-per-image kernel below for shapes the others cannot express.
+    // SSAD_KERNEL=v4|v3|cluster|generic pins one (tests, profiling).
     const char* force = getenv("SSAD_KERNEL");
+    const bool only_v4 = force && strcmp(force, "v4") == 0;
     const bool only_v3 = force && strcmp(force, "v3") == 0, only_cluster = force && strcmp(force, "cluster") == 0;
     const bool only_generic = force && strcmp(force, "generic") == 0;
+    if (d.batch > 65535) return SSAD_EUNSUPPORTED;
+    if (!only_v3 && !only_cluster && !only_generic) {
+        int rc = ssad_launch_v4(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug, workspace,
+                                workspace_bytes, static_cast<cudaStream_t>(stream));
+        if (rc != SSAD_EUNSUPPORTED || only_v4) return rc;
+    }
     if (!only_cluster && !only_generic) {
         int rc = ssad_launch_v3(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug,
                                 static_cast<cudaStream_t>(stream));

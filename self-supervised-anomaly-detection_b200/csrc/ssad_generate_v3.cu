@@ -20,11 +20,14 @@
 
 #include "ssad_device.cuh"
 #include "ssad_sm100.cuh"
+#include "ssad_unit8.cuh"
 
 int ssad_set_cuda_error(cudaError_t e);
 
 namespace ssad {
 namespace v3 {
+
+using namespace u8x;
 
 constexpr int NT = 256;
 constexpr int NWARP = NT / 32;
@@ -54,122 +57,6 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, u
         ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
 
-// ---------------------------------------------------------------- 8-pixel unit, packed pairs
-// v[c][k] = (pixel 2k, pixel 2k+1) of channel c in magic form (2^23 + value)
-struct Unit8 {
-    f32x2 v[3][4];
-};
-
-__device__ __forceinline__ void unit_unpack(Unit8& u, const uint2& a, const uint2& b, const uint2& c) {
-    const uint32_t w[6] = {a.x, a.y, b.x, b.y, c.x, c.y};
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            const int b0 = 6 * k + ch, b1 = 6 * k + 3 + ch;
-            u.v[ch][k] = pack2(magic_from_byte(w[b0 >> 2], b0 & 3), magic_from_byte(w[b1 >> 2], b1 & 3));
-        }
-    }
-}
-__device__ __forceinline__ void unit_scalars(const Unit8& u, float (&m)[24]) {
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) unpack2(u.v[ch][k], m[6 * k + ch], m[6 * k + 3 + ch]);
-    }
-}
-__device__ __forceinline__ void unit_pack(const Unit8& u, uint2& a, uint2& b, uint2& c) {
-    float m[24];
-    unit_scalars(u, m);
-    uint32_t w[6];
-    #pragma unroll
-    for (int i = 0; i < 6; ++i) w[i] = magic_pack4(m[4 * i], m[4 * i + 1], m[4 * i + 2], m[4 * i + 3]);
-    a = make_uint2(w[0], w[1]);
-    b = make_uint2(w[2], w[3]);
-    c = make_uint2(w[4], w[5]);
-}
-
-template <bool CLAMP>
-__device__ __forceinline__ f32x2 quantize2(f32x2 t) {
-    if (CLAMP) {
-        float lo, hi;
-        unpack2(t, lo, hi);
-        t = pack2(fminf(fmaxf(lo, 0.0f), 255.0f), fminf(fmaxf(hi, 0.0f), 255.0f));
-    }
-    return add2_rz(t, pack2(kMagic, kMagic));
-}
-template <bool CLAMP>
-__device__ __forceinline__ void unit_brightness(Unit8& u, float f) {
-    const f32x2 F = pack2(f, f), NEG = pack2(-kMagic, -kMagic), MAG = pack2(kMagic, kMagic);
-    #pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-        #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            f32x2 t = mul2_rn(F, add2_rn(u.v[ch][k], NEG));
-            if (CLAMP) {                                   // values >= 0: only the upper clip can bind
-                float lo, hi;
-                unpack2(t, lo, hi);
-                t = pack2(fminf(lo, 255.0f), fminf(hi, 255.0f));
-            }
-            u.v[ch][k] = add2_rz(t, MAG);
-        }
-    }
-}
-template <bool CLAMP>
-__device__ __forceinline__ void unit_contrast(Unit8& u, float f, int mean) {
-    const float nm = -(kMagic + (float)mean), af = (float)mean;
-    const f32x2 F = pack2(f, f), NMA = pack2(nm, nm), AF = pack2(af, af);
-    #pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-        #pragma unroll
-        for (int k = 0; k < 4; ++k)
-            u.v[ch][k] = quantize2<CLAMP>(add2_rn(AF, mul2_rn(F, add2_rn(u.v[ch][k], NMA))));
-    }
-}
-__device__ __forceinline__ uint32_t luma_bits(uint32_t r, uint32_t g, uint32_t b) {
-    return 19595u * r + 38470u * g + 7471u * b + 0x8000u;     // on magic bit patterns: the 0x4B000000 offsets cancel mod 2^32
-}
-template <bool CLAMP>
-__device__ __forceinline__ void unit_saturation(Unit8& u, float f) {
-    const f32x2 F = pack2(f, f), MAG = pack2(kMagic, kMagic);
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        float r0, r1, g0, g1, b0, b1;
-        unpack2(u.v[0][k], r0, r1); unpack2(u.v[1][k], g0, g1); unpack2(u.v[2][k], b0, b1);
-        const uint32_t a0 = luma_bits(__float_as_uint(r0), __float_as_uint(g0), __float_as_uint(b0));
-        const uint32_t a1 = luma_bits(__float_as_uint(r1), __float_as_uint(g1), __float_as_uint(b1));
-        // -(2^23 + L): bit pattern 0xCB0000LL
-        const f32x2 NML = pack2(__uint_as_float(__byte_perm(a0, 0xCB000000u, 0x7542)),
-                                __uint_as_float(__byte_perm(a1, 0xCB000000u, 0x7542)));
-        const f32x2 NLF = add2_rn(NML, MAG);                // -(float)L, exact
-        #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            f32x2 p = mul2_rn(F, add2_rn(u.v[ch][k], NML)); // alpha * (v - L)
-            f32x2 t;
-            asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(p), "l"(NLF));   // L + p (same rounding as Pillow's A + p)
-            u.v[ch][k] = quantize2<CLAMP>(t);
-        }
-    }
-}
-__device__ __forceinline__ uint32_t unit_luma_sum(const Unit8& u) {
-    uint32_t s = 0;
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        float r0, r1, g0, g1, b0, b1;
-        unpack2(u.v[0][k], r0, r1); unpack2(u.v[1][k], g0, g1); unpack2(u.v[2][k], b0, b1);
-        s += luma_bits(__float_as_uint(r0), __float_as_uint(g0), __float_as_uint(b0)) >> 16;
-        s += luma_bits(__float_as_uint(r1), __float_as_uint(g1), __float_as_uint(b1)) >> 16;
-    }
-    return s;
-}
-__device__ __forceinline__ void unit_apply(Unit8& u, int op, float f) {
-    if (op == 0) {
-        if (f > 1.0f) unit_brightness<true>(u, f); else unit_brightness<false>(u, f);
-    } else {
-        if (blend_needs_clip(f)) unit_saturation<true>(u, f); else unit_saturation<false>(u, f);
-    }
-}
-
 // sum NV values over the CTA; result valid in every thread
 template <int NV>
 __device__ __forceinline__ void block_sum_vec(uint32_t (&v)[NV], uint32_t* red /* NWARP * 8 words */) {
@@ -189,19 +76,6 @@ __device__ __forceinline__ void block_sum_vec(uint32_t (&v)[NV], uint32_t* red /
         for (int w = 0; w < NWARP; ++w) t += red[w * 8 + i];
         v[i] = t;
     }
-}
-
-// check_color_similarity(...) > 0.99 from exact integer channel sums (dataset_generator.py:147-159): the cheap
-// cosine <s1,s2>/sqrt(<s1,s1><s2,s2>) decides unless it is within 1e-9 of the threshold; then the reference's own
-// operation order (mean / 255, normalise, dot) is evaluated.
-__device__ __forceinline__ bool similarity_branch(const uint32_t* s1, double n1, const uint32_t* s2, double n2, double& cosv) {
-    const double a0 = s1[0], a1 = s1[1], a2 = s1[2], b0 = s2[0], b1 = s2[1], b2 = s2[2];
-    const double dot = a0 * b0 + a1 * b1 + a2 * b2;
-    const double nn = (a0 * a0 + a1 * a1 + a2 * a2) * (b0 * b0 + b1 * b1 + b2 * b2);
-    double c = (nn > 0.0) ? dot * rsqrt(nn) : 0.0;
-    if (fabs(c - 0.99) < 1e-9 || nn == 0.0) c = cosine_of_means(s1, n1, s2, n2);
-    cosv = c;
-    return c > 0.99;
 }
 
 // shift rows that TMA landed at pitch RB + 16 (16-byte aligned superset of the window) down to the dense layout

@@ -129,10 +129,11 @@ class BatchGenerator:
         d.out_norm_dtype = {None: N.SSAD_NORM_NONE, torch.float32: N.SSAD_NORM_F32, torch.bfloat16: N.SSAD_NORM_BF16}[norm_dtype]
         d.out_u8_pitch, d.out_u8_stride = 3 * W, 3 * W * H
         d.crop_align16 = int(crop_aligned)
+        d.any_warp = int(cfg.warp)
         return d
 
     def plan(self, src: torch.Tensor, params: ParamBatch, *, masks=None, want_u8=True, norm_dtype=None, debug=False,
-             params_dev=None, out_u8=None, out_norm=None, y_out=None) -> "Plan":
+             params_dev=None, out_u8=None, out_norm=None, y_out=None, workspace=None) -> "Plan":
         """Validate once and freeze descriptor + device pointers of one ssad_generate call; ``run(plan)``
         then costs one FFI call (steady-state loops, CUDA-graph capture)."""
         cfg = self.cfg
@@ -153,11 +154,16 @@ class BatchGenerator:
         dbg = torch.zeros((B, DEBUG_DTYPE.itemsize), dtype=torch.uint8, device=self.device) if debug else None
         mask_t = masks if masks is not None else self.mask_bits
         lut = self.lut(norm_dtype) if norm_dtype is not None else None
+        need = int(self.lib.ssad_generate_workspace(C.byref(d)))
+        if workspace is None or workspace.numel() * workspace.element_size() < need:
+            workspace = torch.empty((max(need, 256),), dtype=torch.uint8, device=self.device)
         pl = Plan()
+        pl.workspace = workspace
         pl.desc, pl.params_dev, pl.src, pl.mask_t, pl.lut = d, params_dev, src, mask_t, lut
         pl.out_u8, pl.out_norm, pl.y_out, pl.dbg = (out_u8 if want_u8 else None), out_norm, y_out, dbg
         pl.args = (C.byref(d), _ptr(params_dev), _ptr(src), _ptr(self.donors), _ptr(mask_t), _ptr(lut),
-                   _ptr(pl.out_u8), _ptr(out_norm), _ptr(y_out), _ptr(dbg), None, 0)
+                   _ptr(pl.out_u8), _ptr(out_norm), _ptr(y_out), _ptr(dbg), _ptr(workspace),
+                   workspace.numel() * workspace.element_size())
         return pl
 
     def run(self, plan: "Plan") -> None:

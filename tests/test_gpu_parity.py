@@ -58,7 +58,7 @@ def test_generate_big_images_match_oracle(name):
     _check_against_oracle(name, 5)
 
 
-@pytest.mark.parametrize("kernel", ["v3", "cluster", "generic"])
+@pytest.mark.parametrize("kernel", ["v4", "v3", "cluster", "generic"])
 @pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture"])
 def test_every_kernel_variant_matches_oracle(name, kernel, monkeypatch):
     _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": kernel})
