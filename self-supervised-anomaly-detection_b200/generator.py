@@ -143,8 +143,10 @@ class BatchGenerator:
         if params_dev is None:
             params_dev = self.upload_params(params)
         crop_aligned = bool(np.all((rec["crop_off"][:, 0].astype(np.int64) * 3) % 16 == 0))
-        d = self.describe(B, src, rec["rect"][:, 2].max(initial=1), rec["rect"][:, 3].max(initial=1), masks, norm_dtype,
-                          crop_aligned)
+        # canvas bounds: the polygon lives on pw x ph, the rotated scar on scar_size (datasets.py:344)
+        max_w = max(int(rec["rect"][:, 2].max(initial=1)), int(rec["scar_size"][:, 0].max(initial=1)))
+        max_h = max(int(rec["rect"][:, 3].max(initial=1)), int(rec["scar_size"][:, 1].max(initial=1)))
+        d = self.describe(B, src, max_w, max_h, masks, norm_dtype, crop_aligned)
         if want_u8 and out_u8 is None:
             out_u8 = torch.empty((B, H, W, 3), dtype=torch.uint8, device=self.device)
         if norm_dtype is not None and out_norm is None:
