@@ -96,7 +96,8 @@ typedef struct SsadBatchDesc {
     int64_t out_u8_pitch;      /* bytes per output row (>= 3 * width) */
     int64_t out_u8_stride;     /* bytes per output image */
     int32_t any_warp;          /* 1: some records have warp_en set (sizes the workspace: x is materialised once per batch) */
-    int32_t reserved0;
+    float   sat_factor_max;    /* upper bound of the enabled ColorJitter saturation factors jit_f[2] over the batch (the table-driven
+                                  kernel serves factors <= 1.25; larger ones take the arithmetic kernels) */
 } SsadBatchDesc;
 
 /* Optional per-image trace of the data-dependent decisions, for parity tests. */

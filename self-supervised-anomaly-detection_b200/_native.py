@@ -27,7 +27,7 @@ class SsadBatchDesc(C.Structure):
         ("coverage_min3", C.c_int32), ("max_patch_w", C.c_int32), ("max_patch_h", C.c_int32),
         ("out_norm_dtype", C.c_int32), ("crop_align16", C.c_int32),
         ("out_u8_pitch", C.c_int64), ("out_u8_stride", C.c_int64),
-        ("any_warp", C.c_int32), ("reserved0", C.c_int32),
+        ("any_warp", C.c_int32), ("sat_factor_max", C.c_float),
     ]
 
 

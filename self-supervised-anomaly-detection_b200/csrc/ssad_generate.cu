@@ -526,6 +526,11 @@ int ssad_launch_v5(const SsadBatchDesc& d, const SsadImageParams* params, const 
                    SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 size_t ssad_v5_workspace(const SsadBatchDesc& d);
 
+int ssad_launch_v6(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
+                   const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
+                   SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+size_t ssad_v6_workspace(const SsadBatchDesc& d);
+
 int ssad_set_cuda_error(cudaError_t e) {
     strncpy(g_cuda_err, cudaGetErrorString(e), sizeof(g_cuda_err) - 1);
     return SSAD_ELAUNCH;
@@ -533,8 +538,9 @@ int ssad_set_cuda_error(cudaError_t e) {
 
 extern "C" size_t ssad_generate_workspace(const SsadBatchDesc* desc) {
     if (!desc || desc->batch <= 0) return 0;
-    const size_t a = ssad_v5_workspace(*desc), b = ssad_v4_workspace(*desc);
-    return a > b ? a : b;               // 0 for shapes only the on-chip kernels serve (they need no workspace)
+    size_t a = ssad_v5_workspace(*desc), b = ssad_v4_workspace(*desc), c = ssad_v6_workspace(*desc);
+    if (b > a) a = b;
+    return c > a ? c : a;               // 0 for shapes only the on-chip kernels serve (they need no workspace)
 }
 
 extern "C" int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, const uint8_t* src,
@@ -561,6 +567,12 @@ extern "C" int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* p
     // SSAD_KERNEL=v4|v3|cluster|generic pins one (tests, profiling).
     const char* force = getenv("SSAD_KERNEL");
     const bool only_v4 = force && strcmp(force, "v4") == 0, only_v5 = force && strcmp(force, "v5") == 0;
+    const bool only_v6 = force && strcmp(force, "v6") == 0;
+    if (!force || only_v6) {
+        int rc = ssad_launch_v6(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug, workspace,
+                                workspace_bytes, static_cast<cudaStream_t>(stream));
+        if (rc != SSAD_EUNSUPPORTED || only_v6) return rc;
+    }
     if (!force || only_v5) {
         int rc = ssad_launch_v5(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug, workspace,
                                 workspace_bytes, static_cast<cudaStream_t>(stream));

@@ -147,6 +147,8 @@ class BatchGenerator:
         max_w = max(int(rec["rect"][:, 2].max(initial=1)), int(rec["scar_size"][:, 0].max(initial=1)))
         max_h = max(int(rec["rect"][:, 3].max(initial=1)), int(rec["scar_size"][:, 1].max(initial=1)))
         d = self.describe(B, src, max_w, max_h, masks, norm_dtype, crop_aligned)
+        sat_on = (rec["jit_en"] & 4) != 0
+        d.sat_factor_max = float(rec["jit_f"][:, 2][sat_on].max(initial=0.0))
         if want_u8 and out_u8 is None:
             out_u8 = torch.empty((B, H, W, 3), dtype=torch.uint8, device=self.device)
         if norm_dtype is not None and out_norm is None:

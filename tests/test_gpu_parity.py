@@ -58,7 +58,7 @@ def test_generate_big_images_match_oracle(name):
     _check_against_oracle(name, 5)
 
 
-@pytest.mark.parametrize("kernel", ["v5", "v4", "v3", "cluster", "generic"])
+@pytest.mark.parametrize("kernel", ["v6", "v5", "v4", "v3", "cluster", "generic"])
 @pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture"])
 def test_every_kernel_variant_matches_oracle(name, kernel, monkeypatch):
     _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": kernel})
@@ -74,6 +74,12 @@ def test_v3_cluster_sizes_match_oracle(name, csize, monkeypatch):
 @pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
 def test_v5_cluster_sizes_match_oracle(name, csize, monkeypatch):
     _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v5", "SSAD_V5_C": csize})
+
+
+@pytest.mark.parametrize("csize", ["1", "2", "4", "8"])
+@pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
+def test_v6_cluster_sizes_match_oracle(name, csize, monkeypatch):
+    _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v6", "SSAD_V6_C": csize})
 
 
 @pytest.mark.parametrize("name", S.ALL)
