@@ -44,15 +44,17 @@ constexpr int NT = 256;
 constexpr int NWARP = NT / 32;
 constexpr int MAXC = 8;
 // table after Saturation: index = bits(2^23 + t, rounded toward zero) - 0x4B000000 + TB_OFF.  t < 0 lands in the
-// binade below 2^23 (half steps): offsets down to -2 * 64; t < 512 above.  Valid for Saturation factors <= kSatMax.
+// binade below 2^23 (half steps): offsets down to -2 * 64; t < 255 * kSatMax above.  Valid for Saturation factors <= kSatMax.
 constexpr int TB_OFF = 128;
-constexpr int TB_SIZE = TB_OFF + 512;
+constexpr int TB_SIZE = TB_OFF + 320;                  // t < 255 * kSatMax
 constexpr float kSatMax = 1.25f;
 
 struct Geom {
     int H, W, C, rows_cta;
     int upr, upr_shift;                 // units per row (log2 when a power of two, else -1)
     uint32_t cov_pitch, cov_rows;       // coverage canvas: words per row, rows
+    uint32_t canvas_pitch;              // colour canvas (global): words per row
+    size_t canvas_stride, o_canvas, ws_total;   // words per image; workspace offsets / size in bytes
     uint32_t o_rowpre, o_cov, o_flags, o_lut, total;
 };
 
@@ -198,20 +200,32 @@ __device__ __forceinline__ uint32_t dp2a_hi(uint32_t a16x2, uint32_t b8x4, uint3
     asm("dp2a.hi.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a16x2), "r"(b8x4), "r"(c));
     return d;
 }
-__device__ __forceinline__ uint32_t luma_sum_words(const uint32_t (&w)[6]) {
+__device__ __forceinline__ void luma_words(const uint32_t (&w)[6], uint32_t (&L)[8]) {
     constexpr uint32_t kRG = (38470u << 16) | 19595u, kB0 = 7471u;          // pixel at bytes 0,1,2 of a word
     constexpr uint32_t k0R = (19595u << 16), kGB = (7471u << 16) | 38470u;  // pixel at bytes 1,2,3 of a word
-    uint32_t s = 0;
     #pragma unroll
     for (int q = 0; q < 2; ++q) {
         const uint32_t w0 = w[3 * q], w1 = w[3 * q + 1], w2 = w[3 * q + 2];
         const uint32_t p1 = __byte_perm(w0, w1, 0x0543);     // pixel 1: byte 3 of w0, bytes 0,1 of w1
         const uint32_t p2 = __byte_perm(w1, w2, 0x0432);     // pixel 2: bytes 2,3 of w1, byte 0 of w2
-        s += dp2a_hi(kB0, w0, dp2a_lo(kRG, w0, 0x8000u)) >> 16;
-        s += dp2a_hi(kB0, p1, dp2a_lo(kRG, p1, 0x8000u)) >> 16;
-        s += dp2a_hi(kB0, p2, dp2a_lo(kRG, p2, 0x8000u)) >> 16;
-        s += dp2a_hi(kGB, w2, dp2a_lo(k0R, w2, 0x8000u)) >> 16;
+        L[4 * q + 0] = dp2a_hi(kB0, w0, dp2a_lo(kRG, w0, 0x8000u)) >> 16;
+        L[4 * q + 1] = dp2a_hi(kB0, p1, dp2a_lo(kRG, p1, 0x8000u)) >> 16;
+        L[4 * q + 2] = dp2a_hi(kB0, p2, dp2a_lo(kRG, p2, 0x8000u)) >> 16;
+        L[4 * q + 3] = dp2a_hi(kGB, w2, dp2a_lo(k0R, w2, 0x8000u)) >> 16;
     }
+}
+__device__ __forceinline__ uint32_t luma_sum_words(const uint32_t (&w)[6]) {
+    uint32_t L[8];
+    luma_words(w, L);
+    return ((L[0] + L[1]) + (L[2] + L[3])) + ((L[4] + L[5]) + (L[6] + L[7]));
+}
+// ... leaving out the pixels whose bit is set in `skip`
+__device__ __forceinline__ uint32_t luma_sum_words_skip(const uint32_t (&w)[6], uint32_t skip) {
+    uint32_t L[8];
+    luma_words(w, L);
+    uint32_t s = 0;
+    #pragma unroll
+    for (int p = 0; p < 8; ++p) s += ((skip >> p) & 1u) ? 0u : L[p];
     return s;
 }
 
@@ -433,48 +447,61 @@ __device__ __forceinline__ void unit_prog(const Prog& G, uint32_t (&w)[6], uint3
 }
 
 struct Boxes {                 // paste geometry of one image, in registers inside the unit loops
-    const uint32_t* cov;
-    int pitch, bw, bh, npaste;
+    const uint32_t* cov;       // coverage bit rows of the canvas (shared memory)
+    const uint32_t* canvas;    // packed (r, g, b, L) per canvas pixel (global, written by this CTA)
+    int pitch, cpitch, bw, bh, npaste;
 };
 
-// paste_patch / scar pastes (dataset_generator.py:268-275, datasets.py:340-355) applied to the 8 pixels of a unit.
-// PRE: the unit holds pixels that already went through the `pre` program (Saturation ahead of Contrast), so do the
-// pasted colours.
-__device__ __forceinline__ void paste_unit(const Plan& D, const SsadImageParams& P, const Boxes& B, const Colour& K,
-                                           const Donor& dn, const Tables& TP, uint32_t rowflag, int yy, int x0,
-                                           uint32_t (&w)[6]) {
-    const bool pre = D.s_in_pre != 0;
-    if (D.y == 1) {
-        const int pl = D.paste[0][0], v = yy - D.paste[0][1];
-        const int u0 = x0 - pl;
-        if (u0 + 8 <= 0 || u0 >= B.bw) return;
-        const uint32_t bits = cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
-        if (!bits) return;
-        #define SSAD_PASTE1(PIX)                                                                              \
-            if (bits & (1u << PIX)) { uint32_t r, g, bl; patch_colour(K, dn, u0 + PIX, v, r, g, bl);          \
-                                      if (pre) pixel_prog(D.pre, TP, r, g, bl); put_pixel<PIX>(w, r, g, bl); }
-        SSAD_PASTE1(0) SSAD_PASTE1(1) SSAD_PASTE1(2) SSAD_PASTE1(3) SSAD_PASTE1(4) SSAD_PASTE1(5) SSAD_PASTE1(6) SSAD_PASTE1(7)
-        #undef SSAD_PASTE1
-    } else {
-        const int32_t a0 = P.scar_fix[0], a1 = P.scar_fix[1], a2 = P.scar_fix[2];
-        const int32_t a3 = P.scar_fix[3], a4 = P.scar_fix[4], a5 = P.scar_fix[5];
-        for (int k = 0; k < B.npaste; ++k) {                 // in order: later pastes overwrite earlier ones
-            if (!((rowflag >> k) & 1u)) continue;
-            const int pl = D.paste[k][0], v = yy - D.paste[k][1];
-            const int u0 = x0 - pl;
-            if (u0 + 8 <= 0 || u0 >= B.bw) continue;
-            const uint32_t bits = cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
-            if (!bits) continue;
-            const int xr = a2 + v * a1 + u0 * a0, yr = a5 + v * a4 + u0 * a3;
-            #define SSAD_PASTE2(PIX)                                                                          \
-                if (bits & (1u << PIX)) {                                                                     \
-                    const int xin = (xr + PIX * a0) >> 16, yin = (yr + PIX * a3) >> 16;                       \
-                    uint32_t r, g, bl; patch_colour(K, dn, xin, yin, r, g, bl);                               \
-                    if (pre) pixel_prog(D.pre, TP, r, g, bl); put_pixel<PIX>(w, r, g, bl); }
-            SSAD_PASTE2(0) SSAD_PASTE2(1) SSAD_PASTE2(2) SSAD_PASTE2(3) SSAD_PASTE2(4) SSAD_PASTE2(5) SSAD_PASTE2(6) SSAD_PASTE2(7)
-            #undef SSAD_PASTE2
-        }
+// union of the coverage of all pastes over the 8 pixels of a unit (pass 1: those pixels are replaced later)
+__device__ __forceinline__ uint32_t covered_bits8(const Plan& D, const Boxes& B, uint32_t rowflag, int yy, int x0) {
+    uint32_t m = 0;
+    for (int k = 0; k < B.npaste; ++k) {
+        if (!((rowflag >> k) & 1u)) continue;
+        const int u0 = x0 - D.paste[k][0], v = yy - D.paste[k][1];
+        if (u0 + 8 <= 0 || u0 >= B.bw) continue;
+        m |= cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
     }
+    return m;
+}
+
+// replace pixel PIX of the unit by the (r, g, b) bytes of a packed canvas word
+template <int PIX>
+__device__ __forceinline__ void put_pixel_c(uint32_t (&w)[6], uint32_t c) {
+    constexpr int b0 = 3 * PIX, b1 = b0 + 1, b2 = b0 + 2;
+    constexpr uint32_t keep = 0x3210u;
+    w[b0 >> 2] = __byte_perm(w[b0 >> 2], c, (keep & ~(0xFu << (4 * (b0 & 3)))) | (4u << (4 * (b0 & 3))));
+    w[b1 >> 2] = __byte_perm(w[b1 >> 2], c, (keep & ~(0xFu << (4 * (b1 & 3)))) | (5u << (4 * (b1 & 3))));
+    w[b2 >> 2] = __byte_perm(w[b2 >> 2], c, (keep & ~(0xFu << (4 * (b2 & 3)))) | (6u << (4 * (b2 & 3))));
+}
+
+// paste_patch / scar pastes (dataset_generator.py:268-275, datasets.py:340-355) applied to the 8 pixels of a unit:
+// covered pixels take the canvas colour; pastes in order, later ones overwrite earlier ones
+__device__ __forceinline__ void paste_unit(const Plan& D, const Boxes& B, uint32_t rowflag, int yy, int x0, uint32_t (&w)[6]) {
+    for (int k = 0; k < B.npaste; ++k) {
+        if (!((rowflag >> k) & 1u)) continue;
+        const int u0 = x0 - D.paste[k][0], v = yy - D.paste[k][1];
+        if (u0 + 8 <= 0 || u0 >= B.bw) continue;
+        const uint32_t bits = cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
+        if (!bits) continue;
+        const uint32_t* crow = B.canvas + (ptrdiff_t)v * B.cpitch + u0;
+        #define SSAD_PASTE(PIX) if (bits & (1u << PIX)) put_pixel_c<PIX>(w, crow[PIX]);
+        SSAD_PASTE(0) SSAD_PASTE(1) SSAD_PASTE(2) SSAD_PASTE(3) SSAD_PASTE(4) SSAD_PASTE(5) SSAD_PASTE(6) SSAD_PASTE(7)
+        #undef SSAD_PASTE
+    }
+}
+
+// u in [0, n) with 0 <= base + u * step < limit (int64: no wrap) -> [lo, hi] inclusive (empty: lo > hi)
+__device__ __forceinline__ long long floor_div(long long a, long long b) {     // b > 0
+    long long q = a / b;
+    return (a % b < 0) ? q - 1 : q;
+}
+__device__ __forceinline__ void affine_span(long long base, long long step, long long limit, int& lo, int& hi) {
+    if (step == 0) { if (!(base >= 0 && base < limit)) { lo = 1; hi = 0; } return; }
+    long long l, h;
+    if (step > 0) { l = -floor_div(base, step); h = floor_div(limit - 1 - base, step); }      // ceil(-base / step)
+    else { const long long sp = -step; h = floor_div(base, sp); l = floor_div(base - limit, sp) + 1; }
+    if (l > lo) lo = (int)min(l, (long long)0x3FFFFFFF);
+    if (h < hi) hi = (int)max(h, (long long)-1);
 }
 
 // ------------------------------------------------------------------ the kernel
@@ -483,7 +510,7 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
                    const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
                    const uint8_t* __restrict__ donor_bank, const uint32_t* __restrict__ mask_bits,
                    const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8, void* __restrict__ out_norm,
-                   int64_t* __restrict__ y_out, SsadDebug* __restrict__ debug, uint8_t* xbuf) {
+                   int64_t* __restrict__ y_out, SsadDebug* __restrict__ debug, uint8_t* xbuf, uint32_t* canvas_all) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ SsadImageParams P;
     __shared__ Plan D;
@@ -604,18 +631,14 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
         }
     } else if (y == 2) {
         // alpha of scar.rotate(angle, expand=True) (datasets.py:344): canvas pixel (u, v) is opaque iff its inverse
-        // map lands inside the pw x ph scar
-        const int nwords = bh * pitchw;
-        for (int i = tid; i < nwords; i += NT) {
-            const int v = i / pitchw, j = i - v * pitchw;
-            uint32_t m = 0;
-            for (int t = 0; t < 32; ++t) {
-                const int u = j * 32 + t;
-                int xin, yin;
-                affine_fixed_map(P.scar_fix, u, v, xin, yin);
-                if (u < bw && (unsigned)xin < (unsigned)pw && (unsigned)yin < (unsigned)ph) m |= 1u << t;
-            }
-            cov[i] = m;
+        // map (affine_fixed, 16.16) lands inside the pw x ph scar -- per canvas row one span of u, in closed form
+        for (int v = tid; v < bh; v += NT) {
+            uint32_t* row = cov + (size_t)v * pitchw;
+            for (int j = 0; j < pitchw; ++j) row[j] = 0;
+            int lo = 0, hi = bw - 1;
+            affine_span((long long)P.scar_fix[2] + (long long)v * P.scar_fix[1], P.scar_fix[0], (long long)pw << 16, lo, hi);
+            affine_span((long long)P.scar_fix[5] + (long long)v * P.scar_fix[4], P.scar_fix[3], (long long)ph << 16, lo, hi);
+            if (lo <= hi) row_set_bits(row, lo, hi);
         }
     }
     for (int r = r0 + tid; r < r1; r += NT) {
@@ -638,6 +661,10 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
     const int xpitch = W * 3;
     const Donor dn = donor_of(d, src, donor_bank, b, P);
     const uint32_t tp_a = smem_u32(TP.a), tp_ab = smem_u32(TP.ab), tp_bc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
+
+    uint32_t* const canvas = canvas_all + (size_t)b * g.canvas_stride;
+    Boxes BX;
+    BX.cov = cov; BX.canvas = canvas; BX.pitch = pitchw; BX.cpitch = (int)g.canvas_pitch; BX.bw = bw; BX.bh = bh; BX.npaste = npaste;
 
     uint32_t acc[7] = {0, 0, 0, 0, 0, 0, 0};          // 0-2 RGB of x, 3 sum of L, 4-6 RGB of the cut
     if (y != 0 || cpos >= 0 || stored) {
@@ -676,7 +703,10 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
             }
             if (cpos >= 0) {
                 unit_prog(pre, w, tp_a, tp_ab, tp_bc);
-                acc[3] += luma_sum_words(w);
+                // sum of L of what Contrast will see, minus the pixels a paste replaces (their L comes from the canvas)
+                const uint32_t rf = (y != 0) ? (uint32_t)flags[rr] : 0u;
+                const uint32_t skip = rf ? covered_bits8(D, BX, rf, yy, x0) : 0u;
+                acc[3] += skip ? luma_sum_words_skip(w, skip) : luma_sum_words(w);
             }
             if (s_in_pre) {                     // the x buffer keeps pre(x): pass 2 starts from there
                 o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
@@ -747,11 +777,45 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
     K.flat = D.flat; K.sim = D.sim; K.bf1 = D.bf1; K.bf2 = D.bf2;
     K.frgb[0] = D.flat_rgb[0]; K.frgb[1] = D.flat_rgb[1]; K.frgb[2] = D.flat_rgb[2];
 
-    // ================================================================ D: Contrast mean = sum of L of the PASTED image
+    // ================================================================ D: patch canvas, Contrast mean
+    // canvas pixel (u, v) -> packed (r, g, b, L): the colour pass 2 pastes (after the `pre` program when pass 1 stored
+    // pre(x)) and the L of that colour after the ops ahead of Contrast.  Each CTA fills the canvas rows its slab meets.
+    if (y != 0) {
+        int cv_lo = bh, cv_hi = 0;
+        for (int k = 0; k < npaste; ++k) {
+            const int pt = D.paste[k][1];
+            const int v_lo = max(0, r0 - pt), v_hi = min(bh, r1 - pt);
+            if (v_lo < v_hi) { cv_lo = min(cv_lo, v_lo); cv_hi = max(cv_hi, v_hi); }
+        }
+        const int total = max(cv_hi - cv_lo, 0) * bw;
+        const int cpitch = (int)g.canvas_pitch;
+        for (int idx = tid; idx < total; idx += NT) {
+            const int vv = idx / bw, u = idx - vv * bw;
+            const int v = cv_lo + vv;
+            if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
+            uint32_t r, gg, bl;
+            if (y == 1) patch_colour(K, dn, u, v, r, gg, bl);
+            else {
+                int xin, yin;
+                affine_fixed_map(P.scar_fix, u, v, xin, yin);
+                patch_colour(K, dn, xin, yin, r, gg, bl);
+            }
+            uint32_t L = 0;
+            if (cpos >= 0) {
+                uint32_t pr = r, pg = gg, pb = bl;
+                pixel_prog(D.pre, TP, pr, pg, pb);
+                L = luma_u8(pr, pg, pb);
+                if (s_in_pre) { r = pr; gg = pg; bl = pb; }
+            }
+            canvas[(size_t)v * cpitch + u] = r | (gg << 8) | (bl << 16) | (L << 24);
+        }
+        __syncthreads();
+    }
     int cmean = -1;
     if (cpos >= 0) {
-        uint32_t delta = 0;                      // sum over covered pixels of L(new) - L(old), modulo 2^32
+        uint32_t lnew = 0;                       // sum of L over the pixels the pastes leave visible
         if (y != 0) {
+            const int cpitch = (int)g.canvas_pitch;
             for (int k = 0; k < npaste; ++k) {
                 const int pl = D.paste[k][0], pt = D.paste[k][1];
                 const int v_lo = max(0, r0 - pt), v_hi = min(bh, r1 - pt);
@@ -768,38 +832,21 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
                         if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) later = true;
                     }
                     if (later) continue;
-                    uint32_t r, gg, bl;
-                    if (stored) {
-                        const uint8_t* q = xb + (size_t)Y * xpitch + (size_t)X * 3;
-                        r = q[0]; gg = q[1]; bl = q[2];
-                    } else {
-                        const uint8_t* q = sbase + (size_t)Y * spitch + (size_t)X * 3;
-                        r = __ldg(q); gg = __ldg(q + 1); bl = __ldg(q + 2);
-                    }
-                    if (!s_in_pre) pixel_prog(D.pre, TP, r, gg, bl);       // (the x buffer already holds pre(x) otherwise)
-                    uint32_t nr, ng, nb;
-                    if (y == 1) patch_colour(K, dn, u, v, nr, ng, nb);
-                    else {
-                        int xin, yin;
-                        affine_fixed_map(P.scar_fix, u, v, xin, yin);
-                        patch_colour(K, dn, xin, yin, nr, ng, nb);
-                    }
-                    pixel_prog(D.pre, TP, nr, ng, nb);
-                    delta += luma_u8(nr, ng, nb) - luma_u8(r, gg, bl);
+                    lnew += canvas[(size_t)v * cpitch + u] >> 24;
                 }
             }
-            uint32_t v1[1] = {delta};
+            uint32_t v1[1] = {lnew};
             block_sum_vec<1>(v1, red);
-            delta = v1[0];
+            lnew = v1[0];
             if (C > 1) {
-                if (tid < C) st_cluster_u32(&xchg[rank][7], (uint32_t)tid, delta);
+                if (tid < C) st_cluster_u32(&xchg[rank][7], (uint32_t)tid, lnew);
                 cluster_arrive(); cluster_wait();
-                delta = 0;
-                for (int r = 0; r < C; ++r) delta += xchg[r][7];
+                lnew = 0;
+                for (int r = 0; r < C; ++r) lnew += xchg[r][7];
             }
         }
         // int(mean + 0.5) with mean = sum / count in float64 (ImageEnhance.py Contrast) == integer rounding
-        const uint32_t lsum = tot[3] + delta;
+        const uint32_t lsum = tot[3] + lnew;
         cmean = (int)((2ull * lsum + (uint32_t)npix) / (2ull * (uint32_t)npix));
     }
     // what pass 2 still has to do: Contrast and the ops after it on pre(x), or the whole chain on x
@@ -808,8 +855,6 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
 
     // ================================================================ E: pass 2 -- paste, rest of the chain, stores
     {
-        Boxes BX;
-        BX.cov = cov; BX.pitch = pitchw; BX.bw = bw; BX.bh = bh; BX.npaste = npaste;
         const Prog fin = D.fin;
         const uint32_t tf_a = smem_u32(TF.a), tf_ab = smem_u32(TF.ab), tf_bc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
         uint8_t* const obase = out_u8 ? out_u8 + (size_t)b * d.out_u8_stride : nullptr;
@@ -823,7 +868,7 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
             else load24<true>(sbase + (size_t)yy * spitch + (size_t)x0 * 3, w);
             if (y != 0) {
                 const uint32_t rf = flags[rr];
-                if (rf) paste_unit(D, P, BX, K, dn, TP, rf, yy, x0, w);
+                if (rf) paste_unit(D, BX, rf, yy, x0, w);
             }
             unit_prog(fin, w, tf_a, tf_ab, tf_bc);
             const size_t p0 = (size_t)yy * W + x0;
@@ -919,6 +964,10 @@ static bool make_geom(const SsadBatchDesc& d, Geom& g) {
     g.o_flags = o;  o += ((uint32_t)g.rows_cta + 15u) & ~15u;
     g.o_lut = o;    o += (d.out_norm_dtype == SSAD_NORM_F32) ? 3072u : (d.out_norm_dtype == SSAD_NORM_BF16 ? 1536u : 0u);
     g.total = o;
+    g.canvas_pitch = (uint32_t)d.max_patch_w;
+    g.canvas_stride = (size_t)d.max_patch_w * (size_t)d.max_patch_h;
+    g.o_canvas = ((size_t)d.batch * d.height * d.width * 3 + 255) / 256 * 256;       // after the x buffer
+    g.ws_total = g.o_canvas + ((size_t)d.batch * g.canvas_stride * 4 + 255) / 256 * 256;
     return true;
 }
 
@@ -928,7 +977,7 @@ static bool make_geom(const SsadBatchDesc& d, Geom& g) {
 size_t ssad_v6_workspace(const SsadBatchDesc& d) {
     ssad::v6::Geom g;
     if (!ssad::v6::make_geom(d, g)) return 0;
-    return ((size_t)d.batch * d.height * d.width * 3 + 255) / 256 * 256;     // the x buffer
+    return g.ws_total;       // the x buffer + the patch canvases
 }
 
 // returns SSAD_OK when launched, SSAD_EUNSUPPORTED when the caller should use another kernel
@@ -944,6 +993,7 @@ int ssad_launch_v6(const SsadBatchDesc& d, const SsadImageParams* params, const 
     if (!workspace || workspace_bytes < need) return SSAD_EWORKSPACE;
     if (reinterpret_cast<uintptr_t>(workspace) & 255) return SSAD_EALIGN;
     uint8_t* xbuf = static_cast<uint8_t*>(workspace);
+    uint32_t* canvas = reinterpret_cast<uint32_t*>(xbuf + g.o_canvas);
     static int attr_smem = -1;
     cudaError_t e;
     if ((int)g.total > attr_smem) {
@@ -963,7 +1013,7 @@ int ssad_launch_v6(const SsadBatchDesc& d, const SsadImageParams* params, const 
     cfg.attrs = attr;
     cfg.numAttrs = (g.C > 1) ? 1 : 0;
     e = cudaLaunchKernelEx(&cfg, generate_v6_kernel, d, g, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm,
-                           y_out, debug, xbuf);
+                           y_out, debug, xbuf, canvas);
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     return SSAD_OK;
 }
