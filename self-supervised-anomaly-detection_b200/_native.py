@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libssad_gen.so")
+LIB_PATH = os.environ.get("SSAD_LIB") or os.path.join(HERE, "lib", "libssad_gen.so")   # SSAD_LIB: experiments only
 
 SSAD_MASK_ALL, SSAD_MASK_SHARED, SSAD_MASK_PER_IMAGE = 0, 1, 2
 SSAD_NORM_NONE, SSAD_NORM_F32, SSAD_NORM_BF16 = 0, 1, 2

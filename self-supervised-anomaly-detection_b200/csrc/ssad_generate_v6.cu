@@ -26,6 +26,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -116,7 +117,7 @@ __device__ inline void build_prog(Prog& G, Tables& T, const int32_t* ops, const 
     }
     const float fs = fac[is];
     const int sa = (is > i0) ? SA_LUT : SA_UNPACK;
-    const int sb = (is + 1 < i1) ? SB_LUT : (blend_needs_clip(fs) ? SB_CLAMP : SB_PACK);
+    const int sb = (is + 1 < i1) ? SB_LUT : SB_CLAMP;          // (the clamp form also serves factors <= 1)
     if (tid == 0) { G.kind = PK_SAT; G.sa = sa; G.sb = sb; G.fs = fs; }
     if (sa == SA_LUT)
         for (int v = tid; v < 256; v += NT) T.a[v] = kMagicBits | run_ops((uint32_t)v, ops, fac, i0, is, mean);
@@ -164,6 +165,29 @@ __device__ __forceinline__ void load24(const uint8_t* __restrict__ p, uint32_t (
         } else {
             w[0] = __funnelshift_r(A.y, B.x, sh); w[1] = __funnelshift_r(B.x, B.y, sh); w[2] = __funnelshift_r(B.y, C.x, sh);
             w[3] = __funnelshift_r(C.x, C.y, sh); w[4] = __funnelshift_r(C.y, D.x, sh); w[5] = __funnelshift_r(D.x, D.y, sh);
+        }
+    }
+}
+
+// the same load split in two for software pipelining: raw 8-byte-aligned loads now, the byte shift later
+struct Raw { uint2 a, b, c, d; };
+__device__ __forceinline__ void ld_raw(const uint8_t* q /* 8-byte aligned */, bool four, bool nc, Raw& r) {
+    const uint2* p = reinterpret_cast<const uint2*>(q);
+    r.d = make_uint2(0u, 0u);
+    (void)nc;        // one flavour of load: the x buffer is written by this kernel, so no ld.global.nc
+    r.a = p[0]; r.b = p[1]; r.c = p[2]; if (four) r.d = p[3];
+}
+__device__ __forceinline__ void raw_to_words(const Raw& r, uint32_t mis, uint32_t (&w)[6]) {
+    if (mis == 0) {
+        w[0] = r.a.x; w[1] = r.a.y; w[2] = r.b.x; w[3] = r.b.y; w[4] = r.c.x; w[5] = r.c.y;
+    } else {
+        const uint32_t sh = (mis & 3u) * 8u;
+        if (mis < 4) {
+            w[0] = __funnelshift_r(r.a.x, r.a.y, sh); w[1] = __funnelshift_r(r.a.y, r.b.x, sh); w[2] = __funnelshift_r(r.b.x, r.b.y, sh);
+            w[3] = __funnelshift_r(r.b.y, r.c.x, sh); w[4] = __funnelshift_r(r.c.x, r.c.y, sh); w[5] = __funnelshift_r(r.c.y, r.d.x, sh);
+        } else {
+            w[0] = __funnelshift_r(r.a.y, r.b.x, sh); w[1] = __funnelshift_r(r.b.x, r.b.y, sh); w[2] = __funnelshift_r(r.b.y, r.c.x, sh);
+            w[3] = __funnelshift_r(r.c.x, r.c.y, sh); w[4] = __funnelshift_r(r.c.y, r.d.x, sh); w[5] = __funnelshift_r(r.d.x, r.d.y, sh);
         }
     }
 }
@@ -231,7 +255,7 @@ __device__ __forceinline__ uint32_t luma_sum_words_skip(const uint32_t (&w)[6], 
 
 // sum NV values over the CTA; result valid in every thread
 template <int NV>
-__device__ __forceinline__ void block_sum_vec(uint32_t (&v)[NV], uint32_t* red /* NWARP * 8 words */) {
+__device__ __forceinline__ void block_sum_vec(uint32_t (&v)[NV], uint32_t* red /* NWARP * 8 + 8 words */) {
     #pragma unroll
     for (int i = 0; i < NV; ++i)
         for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xFFFFFFFFu, v[i], o);
@@ -241,13 +265,15 @@ __device__ __forceinline__ void block_sum_vec(uint32_t (&v)[NV], uint32_t* red /
         for (int i = 0; i < NV; ++i) red[(threadIdx.x >> 5) * 8 + i] = v[i];
     }
     __syncthreads();
-    #pragma unroll
-    for (int i = 0; i < NV; ++i) {
+    if (threadIdx.x < NV) {
         uint32_t t = 0;
         #pragma unroll
-        for (int w = 0; w < NWARP; ++w) t += red[w * 8 + i];
-        v[i] = t;
+        for (int w = 0; w < NWARP; ++w) t += red[w * 8 + threadIdx.x];
+        red[NWARP * 8 + threadIdx.x] = t;
     }
+    __syncthreads();
+    #pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = red[NWARP * 8 + i];
 }
 
 // ------------------------------------------------------------------ donor / cut source, patch colours
@@ -430,20 +456,25 @@ __device__ __forceinline__ void pixel_prog(const Prog& G, const Tables& T, uint3
     r = q[0]; g = q[1]; b = q[2];
 }
 
-// apply a program to the 8 pixels of a unit (uniform switch: the program is per image)
-__device__ __forceinline__ void unit_prog(const Prog& G, uint32_t (&w)[6], uint32_t ta, uint32_t tab, uint32_t tbc) {
-    if (G.kind == PK_COPY) return;
-    if (G.kind == PK_BYTELUT) { unit_bytelut(w, tab); return; }
-    const float fs = G.fs;
-    if (G.sa == SA_UNPACK) {
-        if (G.sb == SB_PACK) unit_sat_prog<SA_UNPACK, SB_PACK>(w, fs, ta, tbc);
-        else if (G.sb == SB_CLAMP) unit_sat_prog<SA_UNPACK, SB_CLAMP>(w, fs, ta, tbc);
-        else unit_sat_prog<SA_UNPACK, SB_LUT>(w, fs, ta, tbc);
-    } else {
-        if (G.sb == SB_PACK) unit_sat_prog<SA_LUT, SB_PACK>(w, fs, ta, tbc);
-        else if (G.sb == SB_CLAMP) unit_sat_prog<SA_LUT, SB_CLAMP>(w, fs, ta, tbc);
-        else unit_sat_prog<SA_LUT, SB_LUT>(w, fs, ta, tbc);
-    }
+// program kinds the unit loops are specialised for
+enum { LK_COPY = 0, LK_BYTELUT = 1, LK_SAT_UC = 2, LK_SAT_UL = 3, LK_SAT_LC = 4, LK_SAT_LL = 5 };
+__device__ __forceinline__ int loop_kind(const Prog& G) {
+    if (G.kind == PK_COPY) return LK_COPY;
+    if (G.kind == PK_BYTELUT) return LK_BYTELUT;
+    return LK_SAT_UC + (G.sa == SA_LUT ? 2 : 0) + (G.sb == SB_LUT ? 1 : 0);
+}
+struct ProgRegs {              // a program's constants in registers
+    float fs;
+    uint32_t ta, tab, tbc;     // shared-memory addresses: Tables::a, Tables::ab, Tables::b + TB_OFF - 0x4B000000
+};
+template <int LK>
+__device__ __forceinline__ void apply_prog(uint32_t (&w)[6], const ProgRegs& R) {
+    if (LK == LK_COPY) return;
+    if (LK == LK_BYTELUT) { unit_bytelut(w, R.tab); return; }
+    if (LK == LK_SAT_UC) unit_sat_prog<SA_UNPACK, SB_CLAMP>(w, R.fs, R.ta, R.tbc);
+    if (LK == LK_SAT_UL) unit_sat_prog<SA_UNPACK, SB_LUT>(w, R.fs, R.ta, R.tbc);
+    if (LK == LK_SAT_LC) unit_sat_prog<SA_LUT, SB_CLAMP>(w, R.fs, R.ta, R.tbc);
+    if (LK == LK_SAT_LL) unit_sat_prog<SA_LUT, SB_LUT>(w, R.fs, R.ta, R.tbc);
 }
 
 struct Boxes {                 // paste geometry of one image, in registers inside the unit loops
@@ -504,19 +535,150 @@ __device__ __forceinline__ void affine_span(long long base, long long step, long
     if (h < hi) hi = (int)max(h, (long long)-1);
 }
 
+// ------------------------------------------------------------------ the unit loops
+// A CTA's slab = rows [r0, r0 + nrows) x upr units; thread t takes units t, t + NT, ... (row-major).
+struct Slab {
+    int r0, nunits, upr, tid;
+    int dr, dc;                // NT units further = dr rows and dc units (with one carry at most)
+    int rr0, cu0;              // this thread's first unit
+};
+__device__ __forceinline__ Slab make_slab(int r0, int nunits, int upr, int tid) {
+    Slab S;
+    S.r0 = r0; S.nunits = nunits; S.upr = upr; S.tid = tid;
+    S.dr = NT / upr; S.dc = NT - S.dr * upr;
+    S.rr0 = tid / upr; S.cu0 = tid - S.rr0 * upr;
+    return S;
+}
+// rr / cu = row / unit-in-row of the current unit; lin = its dense index (rr * upr + cu = t, t + NT, ...)
+#define SSAD_SLAB_LOOP(S)                                                                                     \
+    for (int lin = (S).tid, rr = (S).rr0, cu = (S).cu0; lin < (S).nunits;                                     \
+         lin += NT, rr += (S).dr, cu += (S).dc, rr += (cu >= (S).upr) ? 1 : 0, cu -= (cu >= (S).upr) ? (S).upr : 0)
+
+// Software-pipelined walk over a thread's units: the loads of the next unit are issued before the current one is
+// processed.  Inside the body: w[6] = the unit's bytes, lin = its dense index in the slab, rr = its row in the slab,
+// yy / x0 = its image row / first pixel.  (Rows are 8-byte periodic: pitch % 8 == 0, so `mis` is one value per slab.)
+#define SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc)                                                          \
+    const uint32_t mis_ = (uint32_t)(reinterpret_cast<uintptr_t>(in0) & 7u);                                  \
+    const uint8_t* const in0a_ = (in0) - mis_;                                                                \
+    Raw nx_;                                                                                                  \
+    int nlin_ = (S).tid, nrr_ = (S).rr0, ncu_ = (S).cu0;                                                      \
+    if (nlin_ < (S).nunits) ld_raw(in0a_ + nrr_ * (in_pitch) + ncu_ * 24, mis_ != 0, in_nc, nx_);             \
+    while (nlin_ < (S).nunits)
+#define SSAD_PIPELINED_STEP(S, in_pitch, in_nc)                                                               \
+    const Raw cur_ = nx_;                                                                                     \
+    const int lin = nlin_, rr = nrr_, yy = (S).r0 + nrr_, x0 = ncu_ * 8;                                      \
+    nlin_ += NT; nrr_ += (S).dr; ncu_ += (S).dc;                                                              \
+    if (ncu_ >= (S).upr) { ncu_ -= (S).upr; ++nrr_; }                                                         \
+    if (nlin_ < (S).nunits) ld_raw(in0a_ + nrr_ * (in_pitch) + ncu_ * 24, mis_ != 0, in_nc, nx_);             \
+    uint32_t w[6];                                                                                            \
+    raw_to_words(cur_, mis_, w);
+
+// pass 1: RGB sums of x; the program ahead of Contrast; sum of L over the pixels no paste replaces; keep the bytes
+template <int LK>
+__device__ __forceinline__ void pass1_loop(const Slab& S, const uint8_t* in, int in_pitch, bool in_nc, uint8_t* xb, int xpitch,
+                                           bool store, bool need_rgb, bool need_luma, const ProgRegs& R, const Plan& D,
+                                           const Boxes& BX, const uint8_t* flags, uint32_t (&acc)[7]) {
+    uint32_t s0 = 0, s1 = 0, s2 = 0, sl = 0;
+    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
+    uint8_t* const xb0 = xb + (size_t)S.r0 * xpitch;           // dense rows: unit `lin` of the slab sits at lin * 24
+    SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc) {
+        SSAD_PIPELINED_STEP(S, in_pitch, in_nc)
+        if (need_rgb) {
+            uint32_t s[3] = {s0, s1, s2};
+            rgb_sums(w, s);
+            s0 = s[0]; s1 = s[1]; s2 = s[2];
+        }
+        if (need_luma) {
+            apply_prog<LK>(w, R);
+            // sum of L of what Contrast will see, minus the pixels a paste replaces (their L comes from the canvas)
+            const uint32_t rf = D.y != 0 ? (uint32_t)flags[rr] : 0u;
+            const uint32_t skip = rf ? covered_bits8(D, BX, rf, yy, x0) : 0u;
+            sl += skip ? luma_sum_words_skip(w, skip) : luma_sum_words(w);
+            if (store) {                        // the x buffer keeps pre(x): pass 2 starts from there
+                uint2* const o = reinterpret_cast<uint2*>(xb0 + lin * 24);
+                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+            }
+        }
+    }
+    acc[0] += s0; acc[1] += s1; acc[2] += s2; acc[3] += sl;
+}
+
+// pass 2: paste on the fly, the rest of the chain, stores
+template <int LK>
+__device__ __forceinline__ void pass2_loop(const Slab& S, const uint8_t* in, int in_pitch, bool in_nc, const ProgRegs& R,
+                                           const Plan& D, const Boxes& BX, const uint8_t* flags, int W, int npix,
+                                           uint8_t* obase, void* onorm, int norm_dtype, const uint8_t* lutbase) {
+    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
+    const size_t pbase = (size_t)S.r0 * W;                     // dense outputs: unit `lin` starts at pixel pbase + lin * 8
+    SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc) {
+        SSAD_PIPELINED_STEP(S, in_pitch, in_nc)
+        if (D.y != 0) {
+            const uint32_t rf = flags[rr];
+            if (rf) paste_unit(D, BX, rf, yy, x0, w);
+        }
+        apply_prog<LK>(w, R);
+        const size_t p0 = pbase + (size_t)lin * 8;
+        if (obase) {
+            uint2* o = reinterpret_cast<uint2*>(obase + p0 * 3);
+            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+        }
+        if (onorm) {
+            // ToTensor + Normalize (datasets.py:392-393): exact table per channel, NCHW planes
+            uint32_t e[24];
+            #pragma unroll
+            for (int i = 0; i < 24; ++i) e[i] = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;      // byte i = pixel i / 3, channel i % 3
+            if (norm_dtype == SSAD_NORM_F32) {
+                const float* lut = reinterpret_cast<const float*>(lutbase);
+                float* ob = reinterpret_cast<float*>(onorm);
+                #pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    float4* o = reinterpret_cast<float4*>(ob + (size_t)ch * npix + p0);
+                    #pragma unroll
+                    for (int qq = 0; qq < 2; ++qq) {
+                        float4 v;
+                        v.x = lut[ch * 256 + e[3 * (4 * qq + 0) + ch]];
+                        v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
+                        v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
+                        v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
+                        o[qq] = v;
+                    }
+                }
+            } else {
+                const uint16_t* lut = reinterpret_cast<const uint16_t*>(lutbase);
+                uint16_t* ob = reinterpret_cast<uint16_t*>(onorm);
+                #pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    uint32_t wv[4];
+                    #pragma unroll
+                    for (int qq = 0; qq < 4; ++qq) {
+                        uint32_t lo = lut[ch * 256 + e[3 * (2 * qq) + ch]];
+                        uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
+                        wv[qq] = lo | (hi << 16);
+                    }
+                    *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+                }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------ the kernel
-__global__ void __launch_bounds__(NT, 4)
+#ifndef SSAD_V6_MINB
+#define SSAD_V6_MINB 4
+#endif
+__global__ void __launch_bounds__(NT, SSAD_V6_MINB)
 generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geom g,
                    const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
                    const uint8_t* __restrict__ donor_bank, const uint32_t* __restrict__ mask_bits,
                    const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8, void* __restrict__ out_norm,
-                   int64_t* __restrict__ y_out, SsadDebug* __restrict__ debug, uint8_t* xbuf, uint32_t* canvas_all) {
+                   int64_t* __restrict__ y_out, SsadDebug* __restrict__ debug, uint8_t* xbuf, uint32_t* canvas_all,
+                   unsigned long long* prof) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ SsadImageParams P;
     __shared__ Plan D;
     __shared__ Polygon G;
     __shared__ Tables TP, TF;                    // tables of the `pre` and `fin` programs
-    __shared__ uint32_t red[NWARP * 8];
+    __shared__ uint32_t red[NWARP * 8 + 8];
     __shared__ uint32_t xchg[MAXC][8];
     __shared__ uint32_t stage[8];
     uint32_t* const rowpre = reinterpret_cast<uint32_t*>(smem + g.o_rowpre);
@@ -530,6 +692,8 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
     const int H = g.H, W = g.W;
     const int npix = H * W;
     if (C > 1) cluster_arrive();                 // #0: "this CTA runs" (waited for before the first remote store)
+    long long tprev = prof ? clock64() : 0;
+    #define SSAD_MARK(i) if (prof && tid == 0) { const long long tn = clock64(); atomicAdd(prof + (i), (unsigned long long)(tn - tprev)); tprev = tn; }
 
     // ================================================================ A: geometry (no pixel is read)
     if (tid < (int)(sizeof(SsadImageParams) / 4))
@@ -651,6 +815,7 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
     }
     __syncthreads();
 
+    SSAD_MARK(0)
     // ================================================================ B: pass 1
     const bool warped = P.warp_en != 0;
     const bool stored = warped || s_in_pre;      // pass 1 leaves its bytes in the x buffer
@@ -660,57 +825,46 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
     uint8_t* const xb = xbuf + (size_t)b * npix * 3;
     const int xpitch = W * 3;
     const Donor dn = donor_of(d, src, donor_bank, b, P);
-    const uint32_t tp_a = smem_u32(TP.a), tp_ab = smem_u32(TP.ab), tp_bc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
 
     uint32_t* const canvas = canvas_all + (size_t)b * g.canvas_stride;
     Boxes BX;
     BX.cov = cov; BX.canvas = canvas; BX.pitch = pitchw; BX.cpitch = (int)g.canvas_pitch; BX.bw = bw; BX.bh = bh; BX.npaste = npaste;
 
     uint32_t acc[7] = {0, 0, 0, 0, 0, 0, 0};          // 0-2 RGB of x, 3 sum of L, 4-6 RGB of the cut
-    if (y != 0 || cpos >= 0 || stored) {
-        const Prog pre = D.pre;
+    const Slab SL = make_slab(r0, nunits, g.upr, tid);
+    if (warped) {
+        // RandomAffine(3, scale=(1.05, 1.1)) NEAREST, fill 0 (datasets.py:220-222): x gathered once into the x buffer
         const int32_t a0 = P.warp_fix[0], a1 = P.warp_fix[1], a2 = P.warp_fix[2];
         const int32_t a3 = P.warp_fix[3], a4 = P.warp_fix[4], a5 = P.warp_fix[5];
-        for (int ui = tid; ui < nunits; ui += NT) {
-            int rr, cu;
-            if (g.upr_shift >= 0) { rr = ui >> g.upr_shift; cu = ui & (g.upr - 1); }
-            else { rr = ui / g.upr; cu = ui - rr * g.upr; }
+        SSAD_SLAB_LOOP(SL) {
             const int yy = r0 + rr, x0 = cu * 8;
-            uint32_t w[6];
-            if (warped) {
-                // RandomAffine(3, scale=(1.05, 1.1)) NEAREST, fill 0 (datasets.py:220-222): gathered once
-                const int xr = a2 + yy * a1 + x0 * a0, yr = a5 + yy * a4 + x0 * a3;
-                #pragma unroll
-                for (int i = 0; i < 6; ++i) w[i] = 0;
-                #define SSAD_GATHER(PIX)                                                                      \
-                    { const int xin = (xr + PIX * a0) >> 16, yin = (yr + PIX * a3) >> 16;                     \
-                      if ((unsigned)xin < (unsigned)W && (unsigned)yin < (unsigned)H) {                       \
-                          const uint8_t* q = sbase + yin * spitch + xin * 3;                                  \
-                          put_pixel<PIX>(w, __ldg(q), __ldg(q + 1), __ldg(q + 2)); } }
-                SSAD_GATHER(0) SSAD_GATHER(1) SSAD_GATHER(2) SSAD_GATHER(3) SSAD_GATHER(4) SSAD_GATHER(5) SSAD_GATHER(6) SSAD_GATHER(7)
-                #undef SSAD_GATHER
-            } else {
-                load24<true>(sbase + (size_t)yy * spitch + (size_t)x0 * 3, w);
-            }
-            if (y != 0) {
-                uint32_t s[3] = {acc[0], acc[1], acc[2]};
-                rgb_sums(w, s);
-                acc[0] = s[0]; acc[1] = s[1]; acc[2] = s[2];
-            }
-            uint2* const o = reinterpret_cast<uint2*>(xb + (size_t)yy * xpitch + (size_t)x0 * 3);
-            if (warped && !s_in_pre) {          // the x buffer keeps x itself: pass 2 runs the whole chain
-                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
-            }
-            if (cpos >= 0) {
-                unit_prog(pre, w, tp_a, tp_ab, tp_bc);
-                // sum of L of what Contrast will see, minus the pixels a paste replaces (their L comes from the canvas)
-                const uint32_t rf = (y != 0) ? (uint32_t)flags[rr] : 0u;
-                const uint32_t skip = rf ? covered_bits8(D, BX, rf, yy, x0) : 0u;
-                acc[3] += skip ? luma_sum_words_skip(w, skip) : luma_sum_words(w);
-            }
-            if (s_in_pre) {                     // the x buffer keeps pre(x): pass 2 starts from there
-                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
-            }
+            const int xr = a2 + yy * a1 + x0 * a0, yr = a5 + yy * a4 + x0 * a3;
+            uint32_t w[6] = {0, 0, 0, 0, 0, 0};
+            #define SSAD_GATHER(PIX)                                                                      \
+                { const int xin = (xr + PIX * a0) >> 16, yin = (yr + PIX * a3) >> 16;                     \
+                  if ((unsigned)xin < (unsigned)W && (unsigned)yin < (unsigned)H) {                       \
+                      const uint8_t* q = sbase + yin * spitch + xin * 3;                                  \
+                      put_pixel<PIX>(w, __ldg(q), __ldg(q + 1), __ldg(q + 2)); } }
+            SSAD_GATHER(0) SSAD_GATHER(1) SSAD_GATHER(2) SSAD_GATHER(3) SSAD_GATHER(4) SSAD_GATHER(5) SSAD_GATHER(6) SSAD_GATHER(7)
+            #undef SSAD_GATHER
+            uint2* const o = reinterpret_cast<uint2*>(xb + (size_t)r0 * xpitch + (size_t)lin * 24);
+            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+        }
+    }
+    // x as the passes read it (each thread re-reads only what it wrote itself)
+    const uint8_t* const xin_base = warped ? xb : sbase;
+    const int xin_pitch = warped ? xpitch : spitch;
+    if (y != 0 || cpos >= 0) {
+        ProgRegs R;
+        R.fs = D.pre.fs; R.ta = smem_u32(TP.a); R.tab = smem_u32(TP.ab); R.tbc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
+        const bool need_rgb = y != 0, need_luma = cpos >= 0;
+        switch (loop_kind(D.pre)) {
+            case LK_COPY:    pass1_loop<LK_COPY>(SL, xin_base, xin_pitch, !warped, xb, xpitch, false, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_BYTELUT: pass1_loop<LK_BYTELUT>(SL, xin_base, xin_pitch, !warped, xb, xpitch, false, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_SAT_UC:  pass1_loop<LK_SAT_UC>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_SAT_UL:  pass1_loop<LK_SAT_UL>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_SAT_LC:  pass1_loop<LK_SAT_LC>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            default:         pass1_loop<LK_SAT_LL>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
         }
         // RGB sums of the would-be cut (dataset_generator.py:202-207 / 147-159): rows dealt over the cluster's warps
         if (y != 0 && P.src_variant != 2) {
@@ -723,6 +877,7 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
         }
     }
 
+    SSAD_MARK(1)
     // ---------------------------------------------------------------- exchange 1: whole-image sums
     // every CTA leaves its partials in slot [rank] of every CTA of the cluster, then all add the C slots
     if (C > 1) cluster_wait();                   // #0: every CTA of the cluster has started
@@ -749,6 +904,7 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
         }
     }
 
+    SSAD_MARK(2)
     // ================================================================ C: check_color_similarity + variant colours
     if (y != 0) {
         if (tid == 0) {
@@ -779,60 +935,82 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
 
     // ================================================================ D: patch canvas, Contrast mean
     // canvas pixel (u, v) -> packed (r, g, b, L): the colour pass 2 pastes (after the `pre` program when pass 1 stored
-    // pre(x)) and the L of that colour after the ops ahead of Contrast.  Each CTA fills the canvas rows its slab meets.
+    // pre(x)) and the L of that colour after the ops ahead of Contrast.  Each CTA fills the canvas rows its slab meets,
+    // one warp per row.  The double Brightness of the similarity branch (datasets.py:298-299) is a per-channel map: a
+    // 256-entry table (TF.ab is free until the final tables are built).
+    uint32_t lnew = 0;                           // sum of L over the pixels the pastes leave visible
     if (y != 0) {
+        const bool cut_sim = !K.flat && K.sim;
+        if (cut_sim) {
+            for (int v = tid; v < 256; v += NT) TF.ab[v] = (uint8_t)brightness_u8(brightness_u8((uint32_t)v, K.bf1), K.bf2);
+            __syncthreads();
+        }
         int cv_lo = bh, cv_hi = 0;
         for (int k = 0; k < npaste; ++k) {
             const int pt = D.paste[k][1];
             const int v_lo = max(0, r0 - pt), v_hi = min(bh, r1 - pt);
             if (v_lo < v_hi) { cv_lo = min(cv_lo, v_lo); cv_hi = max(cv_hi, v_hi); }
         }
-        const int total = max(cv_hi - cv_lo, 0) * bw;
         const int cpitch = (int)g.canvas_pitch;
-        for (int idx = tid; idx < total; idx += NT) {
-            const int vv = idx / bw, u = idx - vv * bw;
-            const int v = cv_lo + vv;
-            if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
-            uint32_t r, gg, bl;
-            if (y == 1) patch_colour(K, dn, u, v, r, gg, bl);
-            else {
-                int xin, yin;
-                affine_fixed_map(P.scar_fix, u, v, xin, yin);
-                patch_colour(K, dn, xin, yin, r, gg, bl);
+        const int pl0 = D.paste[0][0];
+        const bool want_l = cpos >= 0;
+        for (int v = cv_lo + warp; v < cv_hi; v += NWARP) {
+            const uint32_t* crow = cov + (size_t)v * pitchw;
+            uint32_t* out = canvas + (size_t)v * cpitch;
+            const int xr = P.scar_fix[2] + v * P.scar_fix[1], yr = P.scar_fix[5] + v * P.scar_fix[4];
+            for (int u = lane; u < bw; u += 32) {
+                if (!((crow[u >> 5] >> (u & 31)) & 1u)) continue;
+                uint32_t r, gg, bl;
+                if (K.flat) { r = K.frgb[0]; gg = K.frgb[1]; bl = K.frgb[2]; }
+                else {
+                    int su = u, sv = v;          // source pixel of the cut: itself (polygon) | inverse rotation (scar)
+                    if (y == 2) { su = (xr + u * P.scar_fix[0]) >> 16; sv = (yr + u * P.scar_fix[3]) >> 16; }
+                    r = gg = bl = 0;
+                    if (su < dn.u_hi && sv < dn.v_hi) {
+                        const uint8_t* q = dn.base + (size_t)sv * dn.pitch + 3 * su;
+                        r = __ldg(q); gg = __ldg(q + 1); bl = __ldg(q + 2);
+                    }
+                    if (cut_sim) { r = TF.ab[r]; gg = TF.ab[gg]; bl = TF.ab[bl]; }
+                }
+                uint32_t L = 0;
+                if (want_l) {
+                    uint32_t pr = r, pg = gg, pb = bl;
+                    pixel_prog(D.pre, TP, pr, pg, pb);
+                    L = luma_u8(pr, pg, pb);
+                    if (s_in_pre) { r = pr; gg = pg; bl = pb; }
+                    // a polygon is pasted once: visible wherever it lands inside the image (rows: this slab by construction)
+                    if (y == 1 && (unsigned)(pl0 + u) < (unsigned)W) lnew += L;
+                }
+                out[u] = r | (gg << 8) | (bl << 16) | (L << 24);
             }
-            uint32_t L = 0;
-            if (cpos >= 0) {
-                uint32_t pr = r, pg = gg, pb = bl;
-                pixel_prog(D.pre, TP, pr, pg, pb);
-                L = luma_u8(pr, pg, pb);
-                if (s_in_pre) { r = pr; gg = pg; bl = pb; }
-            }
-            canvas[(size_t)v * cpitch + u] = r | (gg << 8) | (bl << 16) | (L << 24);
         }
         __syncthreads();
     }
+    SSAD_MARK(3)
     int cmean = -1;
     if (cpos >= 0) {
-        uint32_t lnew = 0;                       // sum of L over the pixels the pastes leave visible
         if (y != 0) {
-            const int cpitch = (int)g.canvas_pitch;
-            for (int k = 0; k < npaste; ++k) {
-                const int pl = D.paste[k][0], pt = D.paste[k][1];
-                const int v_lo = max(0, r0 - pt), v_hi = min(bh, r1 - pt);
-                const int total = (v_hi - v_lo) * bw;
-                for (int idx = tid; idx < total; idx += NT) {
-                    const int vv = idx / bw, u = idx - vv * bw;
-                    const int v = v_lo + vv;
-                    const int X = pl + u, Y = pt + v;
-                    if (X < 0 || X >= W) continue;
-                    if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
-                    bool later = false;          // a later paste overwrites this pixel: it is counted there
-                    for (int j = k + 1; j < npaste; ++j) {
-                        const int uj = X - D.paste[j][0], vj = Y - D.paste[j][1];
-                        if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) later = true;
+            if (y == 2) {
+                // scars: k pastes of the same canvas, later ones overwrite earlier ones
+                const int cpitch = (int)g.canvas_pitch;
+                for (int k = 0; k < npaste; ++k) {
+                    const int pl = D.paste[k][0], pt = D.paste[k][1];
+                    const int v_lo = max(0, r0 - pt), v_hi = min(bh, r1 - pt);
+                    for (int v = v_lo + warp; v < v_hi; v += NWARP) {
+                        const int Y = pt + v;
+                        for (int u = lane; u < bw; u += 32) {
+                            const int X = pl + u;
+                            if (X < 0 || X >= W) continue;
+                            if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
+                            bool later = false;          // a later paste overwrites this pixel: it is counted there
+                            for (int j = k + 1; j < npaste; ++j) {
+                                const int uj = X - D.paste[j][0], vj = Y - D.paste[j][1];
+                                if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) later = true;
+                            }
+                            if (later) continue;
+                            lnew += canvas[(size_t)v * cpitch + u] >> 24;
+                        }
                     }
-                    if (later) continue;
-                    lnew += canvas[(size_t)v * cpitch + u] >> 24;
                 }
             }
             uint32_t v1[1] = {lnew};
@@ -853,69 +1031,30 @@ generate_v6_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constan
     build_prog(D.fin, TF, D.ops, D.fac, s_in_pre ? cpos : 0, nops, cmean, tid);
     __syncthreads();
 
+    SSAD_MARK(4)
     // ================================================================ E: pass 2 -- paste, rest of the chain, stores
     {
-        const Prog fin = D.fin;
-        const uint32_t tf_a = smem_u32(TF.a), tf_ab = smem_u32(TF.ab), tf_bc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
+        ProgRegs R;
+        R.fs = D.fin.fs; R.ta = smem_u32(TF.a); R.tab = smem_u32(TF.ab); R.tbc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
+        const uint8_t* const in2 = stored ? xb : sbase;
+        const int in2_pitch = stored ? xpitch : spitch;
         uint8_t* const obase = out_u8 ? out_u8 + (size_t)b * d.out_u8_stride : nullptr;
-        for (int ui = tid; ui < nunits; ui += NT) {
-            int rr, cu;
-            if (g.upr_shift >= 0) { rr = ui >> g.upr_shift; cu = ui & (g.upr - 1); }
-            else { rr = ui / g.upr; cu = ui - rr * g.upr; }
-            const int yy = r0 + rr, x0 = cu * 8;
-            uint32_t w[6];
-            if (stored) load24<false>(xb + (size_t)yy * xpitch + (size_t)x0 * 3, w);
-            else load24<true>(sbase + (size_t)yy * spitch + (size_t)x0 * 3, w);
-            if (y != 0) {
-                const uint32_t rf = flags[rr];
-                if (rf) paste_unit(D, BX, rf, yy, x0, w);
-            }
-            unit_prog(fin, w, tf_a, tf_ab, tf_bc);
-            const size_t p0 = (size_t)yy * W + x0;
-            if (obase) {
-                uint2* o = reinterpret_cast<uint2*>(obase + p0 * 3);
-                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
-            }
-            if (out_norm) {
-                // ToTensor + Normalize (datasets.py:392-393): exact table per channel, NCHW planes
-                uint32_t e[24];
-                #pragma unroll
-                for (int i = 0; i < 24; ++i) e[i] = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;      // byte i = pixel i / 3, channel i % 3
-                if (d.out_norm_dtype == SSAD_NORM_F32) {
-                    const float* lut = reinterpret_cast<const float*>(smem + g.o_lut);
-                    float* ob = reinterpret_cast<float*>(out_norm) + (size_t)b * 3 * npix;
-                    #pragma unroll
-                    for (int ch = 0; ch < 3; ++ch) {
-                        float4* o = reinterpret_cast<float4*>(ob + (size_t)ch * npix + p0);
-                        #pragma unroll
-                        for (int qq = 0; qq < 2; ++qq) {
-                            float4 v;
-                            v.x = lut[ch * 256 + e[3 * (4 * qq + 0) + ch]];
-                            v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
-                            v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
-                            v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
-                            o[qq] = v;
-                        }
-                    }
-                } else {
-                    const uint16_t* lut = reinterpret_cast<const uint16_t*>(smem + g.o_lut);
-                    uint16_t* ob = reinterpret_cast<uint16_t*>(out_norm) + (size_t)b * 3 * npix;
-                    #pragma unroll
-                    for (int ch = 0; ch < 3; ++ch) {
-                        uint32_t wv[4];
-                        #pragma unroll
-                        for (int qq = 0; qq < 4; ++qq) {
-                            uint32_t lo = lut[ch * 256 + e[3 * (2 * qq) + ch]];
-                            uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
-                            wv[qq] = lo | (hi << 16);
-                        }
-                        *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
-                    }
-                }
-            }
+        void* onorm = nullptr;
+        if (out_norm) onorm = (d.out_norm_dtype == SSAD_NORM_F32) ? (void*)(reinterpret_cast<float*>(out_norm) + (size_t)b * 3 * npix)
+                                                                   : (void*)(reinterpret_cast<uint16_t*>(out_norm) + (size_t)b * 3 * npix);
+        const uint8_t* lutbase = smem + g.o_lut;
+        switch (loop_kind(D.fin)) {
+            case LK_COPY:    pass2_loop<LK_COPY>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lutbase); break;
+            case LK_BYTELUT: pass2_loop<LK_BYTELUT>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lutbase); break;
+            case LK_SAT_UC:  pass2_loop<LK_SAT_UC>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lutbase); break;
+            case LK_SAT_UL:  pass2_loop<LK_SAT_UL>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lutbase); break;
+            case LK_SAT_LC:  pass2_loop<LK_SAT_LC>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lutbase); break;
+            default:         pass2_loop<LK_SAT_LL>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lutbase); break;
         }
     }
 
+    SSAD_MARK(5)
+    #undef SSAD_MARK
     if (rank == 0 && tid == 0) {
         if (y_out) y_out[b] = y;
         if (debug) {
@@ -952,6 +1091,9 @@ static bool make_geom(const SsadBatchDesc& d, Geom& g) {
     // cluster size: about 2048 units (8 per thread) per CTA, at most 8 CTAs (portable cluster size)
     int C = 1;
     while (C < MAXC && units / (2 * C) >= 2048 && g.H / (2 * C) >= 8) C *= 2;
+    // ... but no more CTAs per image than it takes to give every SM several waves of work: the geometry phase is
+    // repeated by every CTA of a cluster.  (148 SMs x 4 resident CTAs; a wave and a half.)
+    while (C > 2 && (long long)d.batch * (C / 2) >= 3 * 148 * 2) C /= 2;
     if (const char* f = getenv("SSAD_V6_C")) { int v = atoi(f); if (v == 1 || v == 2 || v == 4 || v == 8) C = v; }
     g.C = C;
     g.rows_cta = (g.H + C - 1) / C;
@@ -1012,8 +1154,21 @@ int ssad_launch_v6(const SsadBatchDesc& d, const SsadImageParams* params, const 
     attr[0].val.clusterDim.x = (unsigned)g.C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = (g.C > 1) ? 1 : 0;
+    // SSAD_V6_PROF=1 (debugging aid): per-phase CTA clock sums, printed after a synchronising copy
+    static unsigned long long* prof = nullptr;
+    static const bool want_prof = getenv("SSAD_V6_PROF") != nullptr;
+    if (want_prof && !prof) { cudaMalloc(&prof, 8 * sizeof(unsigned long long)); }
+    if (want_prof) cudaMemsetAsync(prof, 0, 8 * sizeof(unsigned long long), stream);
     e = cudaLaunchKernelEx(&cfg, generate_v6_kernel, d, g, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm,
-                           y_out, debug, xbuf, canvas);
+                           y_out, debug, xbuf, canvas, want_prof ? prof : nullptr);
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
+    if (want_prof) {
+        unsigned long long h[8];
+        cudaMemcpyAsync(h, prof, sizeof(h), cudaMemcpyDeviceToHost, stream);
+        cudaStreamSynchronize(stream);
+        const double n = (double)d.batch * g.C;
+        fprintf(stderr, "v6 phases (cycles per CTA): geometry %.0f  pass1 %.0f  exchange1 %.0f  decide+canvas %.0f  mean+tables %.0f  pass2 %.0f\n",
+                h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n);
+    }
     return SSAD_OK;
 }
