@@ -182,6 +182,13 @@ int ssad_select_kth(const uint32_t* mask_bits, int32_t mask_pitch_words, int32_t
                     int32_t win_w, int32_t win_h, int32_t n, const uint32_t* k /* [n] device */,
                     int32_t* out_xy /* [n][2] device */, int32_t* count_out, void* stream);
 
+/* paste_patch: image.paste(patch, (left, top), mask) (dataset_generator.py:268-275), in place on one dense uint8 RGB image.
+ * patch [ph][pw][channels], channels in {3, 4}; mask [ph][pw] uint8 (0 keeps the image, non-zero takes the patch) or NULL:
+ * then the alpha band of a 4-channel patch (the rotated scar pasted with itself as mask, datasets.py:354), else opaque.
+ * The box is clipped to the image as Pillow does. */
+int ssad_paste(uint8_t* image, int32_t width, int32_t height, const uint8_t* patch, int32_t pw, int32_t ph, int32_t channels,
+               const uint8_t* mask, int32_t left, int32_t top, void* stream);
+
 /* ToTensor(original) (datasets.py:394): uint8 HWC -> f32 NCHW / 255. */
 int ssad_to_tensor(int32_t n, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
                    int64_t src_stride, float* out, void* stream);

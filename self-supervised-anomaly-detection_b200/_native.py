@@ -53,6 +53,8 @@ EXPORTS = {
                                       C.c_int32, C.c_int32, C.c_void_p]),
     "ssad_color_jitter": (C.c_int, [C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 6),
     "ssad_select_kth": (C.c_int, [C.c_void_p] + [C.c_int32] * 6 + [C.c_void_p] * 4),
+    "ssad_paste": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
+                             C.c_int32, C.c_int32, C.c_void_p]),
     "ssad_to_tensor": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
 }
 

@@ -57,6 +57,10 @@ class GeneratorConfig:
     scar_area_ratio: Optional[Tuple[float, float]] = None
     rectangle_aspect_ratio: Tuple[Tuple[float, float], Tuple[float, float]] = CPP.rectangle_aspect_ratio
     scar_aspect_ratio: Tuple[Tuple[float, float], Tuple[float, float]] = CPP.scar_aspect_ratio
+    # function-level entry points (do_patch / do_scar, test_artificial_transformations.py:20-122) run the image-level
+    # geometry without the pre-warp and, with patch_loc=True, with container factor 1
+    force_warp: Optional[bool] = None
+    force_container_factor: Optional[float] = None
 
     def __post_init__(self):
         if self.patch_area_ratio is None:   # datasets.py:184-185
@@ -78,6 +82,8 @@ class GeneratorConfig:
 
     @property
     def warp(self) -> bool:
+        if self.force_warp is not None:
+            return bool(self.force_warp)
         return (not self.patch_localization) and (not self.is_non_fixed)
 
     # -- geometry
@@ -110,10 +116,14 @@ class GeneratorConfig:
 
     @property
     def box_poly(self):
+        if self.force_container_factor is not None:
+            return self.container(self.force_container_factor)
         return self.container(1 if self.patch_localization else CPP.container_scaling_factor_patch)
 
     @property
     def box_scar(self):
+        if self.force_container_factor is not None:
+            return self.container(self.force_container_factor)
         return self.container(1 if self.patch_localization else CPP.container_scaling_factor_scar)
 
     @property

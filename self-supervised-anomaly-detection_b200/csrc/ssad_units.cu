@@ -131,6 +131,24 @@ __global__ void to_tensor_kernel(int height, int width, const uint8_t* __restric
         if (e_ != cudaSuccess) return ssad_set_cuda_error(e_); \
     } while (0)
 
+namespace ssad {
+// ---- Image.paste(patch, (left, top), mask) (dataset_generator.py:268-275; Pillow Paste.c for alpha in {0, 255})
+__global__ void __launch_bounds__(256)
+paste_kernel(uint8_t* __restrict__ img, int W, int H, const uint8_t* __restrict__ patch, int pw, int ph, int ch,
+             const uint8_t* __restrict__ mask, int left, int top) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pw * ph) return;
+    const int v = i / pw, u = i - v * pw;
+    const int X = left + u, Y = top + v;
+    if (X < 0 || Y < 0 || X >= W || Y >= H) return;            // the box is clipped to the image
+    const uint32_t a = mask ? mask[i] : (ch == 4 ? patch[(size_t)i * 4 + 3] : 255u);
+    if (a == 0) return;                                        // on this path alpha is 0 or 255
+    uint8_t* q = img + 3 * ((size_t)Y * W + X);
+    const uint8_t* s = patch + (size_t)i * ch;
+    q[0] = s[0]; q[1] = s[1]; q[2] = s[2];
+}
+}  // namespace ssad
+
 extern "C" int ssad_polygon_mask(int32_t n, const int16_t* poly_xy, const uint8_t* poly_n, const int16_t* size,
                                  uint8_t* out, int32_t max_w, int32_t max_h, void* stream) {
     if (n < 0 || !poly_xy || !poly_n || !size || !out || max_w <= 0 || max_h <= 0) return SSAD_EINVAL;
@@ -183,6 +201,16 @@ extern "C" int ssad_to_tensor(int32_t n, int32_t height, int32_t width, const ui
     if (n == 0) return SSAD_OK;
     dim3 grid((height * width + 255) / 256, n);
     ssad::to_tensor_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(height, width, src, src_pitch, src_stride, out);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_paste(uint8_t* image, int32_t width, int32_t height, const uint8_t* patch, int32_t pw, int32_t ph,
+                          int32_t channels, const uint8_t* mask, int32_t left, int32_t top, void* stream) {
+    if (!image || !patch || width <= 0 || height <= 0 || pw <= 0 || ph <= 0 || (channels != 3 && channels != 4)) return SSAD_EINVAL;
+    const int n = pw * ph;
+    ssad::paste_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(image, width, height, patch, pw, ph, channels,
+                                                                                   mask, left, top);
     SSAD_CHECK_LAUNCH();
     return SSAD_OK;
 }

@@ -1,0 +1,212 @@
+"""The reference-facing host API (``ssad_b200.dataset_generator`` / ``ssad_b200.datasets``): same names and argument
+meaning as ``src/self_supervised/dataset_generator.py``, ``datasets.py`` and the exerciser script's do_patch / do_scar.
+
+CPU part: host integer logic against the oracle, file-list logic of the datamodule.  GPU part (``-m gpu``): the
+function-level entry points against the golden vectors made from the reference's own do_patch / do_scar, against
+Pillow, and the batched dataset against the reference's ``__getitem__`` goldens."""
+import os
+
+import numpy as np
+import pytest
+
+import scenarios as S
+from golden import make_golden as G
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+# ---------------------------------------------------------------------------------------------- CPU
+def test_container_and_clamp_match_oracle():
+    from oracle import generator as og
+    from ssad_b200 import dataset_generator as dg
+    rng = np.random.default_rng(0)
+    for _ in range(3000):
+        W = int(rng.choice([32, 64, 256, 320, 1024]))
+        f = float(rng.choice([1, 1.75, 2]))
+        size = (int(rng.integers(2, W + 40)), int(rng.integers(2, W + 40)))
+        c = (int(rng.integers(0, W)), int(rng.integers(0, W)))
+        box = dg.Container((W, W), f)
+        ref = og.Container((W, W), f)
+        assert (box.left, box.top, box.right, box.bottom) == (ref.left, ref.top, ref.right, ref.bottom)
+        assert dg.check_valid_coordinates_by_container((W, W), size, c, f) == \
+            tuple(og.check_valid_coordinates_by_container((W, W), size, c, f, None))
+
+
+def test_clamp_draws_centre_inside_container_when_none():
+    from ssad_b200 import dataset_generator as dg
+    rng = np.random.default_rng(1)
+    box = dg.Container((256, 256), 2)
+    for _ in range(200):
+        l, t = dg.check_valid_coordinates_by_container((256, 256), (10, 6), None, 2, rng=rng)
+        assert box.left <= l <= box.right and box.top <= t <= box.bottom
+
+
+def test_get_random_coordinate_contract():
+    from ssad_b200 import dataset_generator as dg
+    assert dg.get_random_coordinate(np.zeros((0, 2))) is None          # dataset_generator.py:260-261
+    one = np.array([[3, 4]])
+    assert tuple(dg.get_random_coordinate(one)) == (3, 4)
+    many = np.arange(20).reshape(10, 2)
+    assert any(tuple(dg.get_random_coordinate(many, np.random.default_rng(s))) != (0, 1) for s in range(8))
+
+
+def test_duplicate_filenames_semantics():
+    from ssad_b200 import datasets as ds
+    names = np.array(["a", "b", "c"])
+    out = ds.duplicate_filenames(names, 10)
+    assert len(out) == 12 and list(out[:6]) == ["a", "b", "c", "a", "b", "c"]      # whole copies (functional.py:64-68)
+    assert len(ds.duplicate_filenames(names, 2)) == 3
+
+
+def _png_tree(tmp_path, subject="bottle", n_train=10, n_test=4, size=48):
+    from PIL import Image
+    from ssad_b200 import synth
+    for cls in (subject, "carpet"):
+        for split, n in (("train", n_train), ("test", n_test)):
+            d = tmp_path / "dataset" / cls / split / "good"
+            d.mkdir(parents=True)
+            imgs = synth.object_images(n, size, size, 11 + len(cls))
+            for i in range(n):
+                Image.fromarray(imgs[i]).save(d / f"{i:03d}.png")
+    return str(tmp_path / "dataset" / subject)
+
+
+def test_datamodule_file_lists(tmp_path):
+    from ssad_b200 import datasets as ds
+    root = _png_tree(tmp_path)
+    dm = ds.PretextTaskDatamodule("bottle", root, imsize=(32, 32), batch_size=4, min_dataset_length=30, seed=0)
+    assert len(dm.train_images_filenames) >= 30 and len(dm.val_images_filenames) >= 30 and len(dm.test_images_filenames) >= 30
+    assert len(set(dm.train_images_filenames)) == 8 and len(set(dm.val_images_filenames)) == 2      # sklearn 0.2 split of 10
+    assert not set(dm.train_images_filenames) & set(dm.val_images_filenames)
+    dm2 = ds.PretextTaskDatamodule("bottle", root, imsize=(32, 32), duplication=False)
+    assert len(dm2.train_images_filenames) == 8
+
+
+# ---------------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", ["do_patch", "do_scar"])
+@pytest.mark.parametrize("mode", ["image", "patch"])
+def test_do_patch_do_scar_match_reference_golden(which, mode):
+    """ssad_b200.dataset_generator.do_patch / do_scar on the parameters the golden run used == the reference's own
+    functions (test_artificial_transformations.py:20-122), bit for bit."""
+    from PIL import Image
+    import ssad_b200
+    from ssad_b200 import dataset_generator as dg
+    g = np.load(os.path.join(GOLD, "script_fns.npz"))
+    sc = S.build("image_level", 8, seed=7)
+    assert bytes(g["sha"]).hex() == G.scenario_sha(sc)
+    seg = S.mask_to_pil(sc.mask)
+    key = f"{which}_{mode}"
+    draws = {k[len(key) + 3:]: g[k] for k in g.files if k.startswith(key + "_d_")}
+    cfg = dg._script_config(sc.cfg.imsize, mode == "patch")
+    pb = ssad_b200.params_from_draws(cfg, draws)
+    rec_gold = np.frombuffer(g[key + "_rec"].tobytes(), dtype=pb.records.dtype)
+    for f in ("rect", "poly_xy", "poly_n", "scar_fix", "scar_size", "scar_k", "src_variant", "centre_r", "bright_f"):
+        assert np.array_equal(pb.records[f], rec_gold[f]), f        # (the golden records also carry an unused pre-warp)
+    fn = dg.do_patch if which == "do_patch" else dg.do_scar
+    for i in range(len(sc.images)):
+        img = Image.fromarray(sc.images[i])
+        x = fn(img, img, seg, mode == "patch", params=pb.slice(i, i + 1))
+        assert isinstance(x, Image.Image)
+        assert np.array_equal(np.array(x), g[key + "_x"][i]), (key, i)
+
+
+@pytest.mark.gpu
+def test_do_patch_samples_its_own_parameters():
+    from PIL import Image
+    from ssad_b200 import dataset_generator as dg
+    sc = S.build("image_level", 4, seed=3)
+    img = Image.fromarray(sc.images[0])
+    a = np.array(dg.do_patch(img, img, S.mask_to_pil(sc.mask), False, rng=np.random.default_rng(5)))
+    b = np.array(dg.do_patch(img, img, S.mask_to_pil(sc.mask), False, rng=np.random.default_rng(5)))
+    assert np.array_equal(a, b)                                   # same generator state -> same defect
+    changed = (a != sc.images[0]).any(axis=2)
+    assert 0 < changed.sum() < 0.08 * changed.size                 # area_ratio (0.03, 0.07): a patch, not the image
+
+
+@pytest.mark.gpu
+def test_rect2poly_matches_pillow():
+    from PIL import Image, ImageDraw
+    from ssad_b200 import dataset_generator as dg
+    rng = np.random.default_rng(2)
+    for _ in range(40):
+        pw, ph = int(rng.integers(2, 130)), int(rng.integers(2, 130))
+        ns, v = dg._redraw_vertices(pw, ph, rng)
+        from ssad_b200.params import polygon_vertices
+        pts = polygon_vertices(pw, ph, ns, v)
+        ref = Image.new("RGBA", (pw, ph), (0, 0, 0, 0))
+        ImageDraw.Draw(ref).polygon([tuple(int(c) for c in p) for p in pts], fill="white")     # dataset_generator.py:99-100
+        got = dg.rect2poly(Image.new("RGB", (pw, ph)), points=pts)
+        assert got.mode == "RGBA" and np.array_equal(np.array(got), np.array(ref)), (pw, ph, pts)
+
+
+@pytest.mark.gpu
+def test_paste_patch_matches_pillow():
+    from PIL import Image
+    from ssad_b200 import dataset_generator as dg
+    rng = np.random.default_rng(4)
+    img = Image.fromarray(rng.integers(0, 256, (40, 56, 3), dtype=np.uint8))
+    for _ in range(30):
+        pw, ph = int(rng.integers(2, 30)), int(rng.integers(2, 30))
+        patch = Image.fromarray(rng.integers(0, 256, (ph, pw, 3), dtype=np.uint8))
+        alpha = (rng.random((ph, pw)) < 0.6).astype(np.uint8) * 255
+        rgba = Image.fromarray(np.dstack([np.array(patch), alpha]), mode="RGBA")
+        at = (int(rng.integers(-20, 60)), int(rng.integers(-20, 45)))     # partly or wholly outside: Pillow clips
+        for p, m in ((patch, None), (patch, rgba), (rgba, rgba)):
+            ref = img.copy()
+            ref.paste(p, at, mask=m)                                 # dataset_generator.py:273-274
+            assert np.array_equal(np.array(dg.paste_patch(img, p, at, m)), np.array(ref)), (at, pw, ph)
+
+
+@pytest.mark.gpu
+def test_obj_mask_pil_in_pil_out():
+    from PIL import Image
+    from oracle import objmask as om
+    from ssad_b200 import dataset_generator as dg, synth
+    img = Image.fromarray(synth.screw_images(1, 96, 96, 3)[0])
+    got = dg.obj_mask(img)
+    ref = om.obj_mask(img)
+    assert got.mode == "RGB" and np.array_equal(np.array(got), np.array(ref))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["image_level", "patch_level", "texture", "non_fixed"])
+def test_dataset_batch_matches_reference_golden(name):
+    """PretextTaskDataset.get_batch with the golden run's parameters == the reference's __getitem__ outputs."""
+    import torch
+    from ssad_b200 import datasets as ds
+    g = np.load(os.path.join(GOLD, f"{name}.npz"))
+    sc = S.build(name, G.BATCH[name])
+    assert bytes(g["sha"]).hex() == G.scenario_sha(sc)
+    fixed = sc.mask if (sc.mask is not None and sc.mask.ndim == 2) else None
+    common = dict(imsize=sc.cfg.imsize, patch_localization=sc.cfg.patch_localization, patch_size=sc.cfg.patch_size,
+                  images=sc.images, donors=sc.donors, fixed_segmentation=fixed, dataset_dir="/nonexistent/")
+    dset = ds.PretextTaskDataset(sc.cfg.subject, transform=True, **common)
+    x, y, original = dset.get_batch(np.arange(len(sc.images)), params=sc.params)
+    assert np.array_equal(y.cpu().numpy(), g["y"])
+    assert np.array_equal(x.cpu().numpy()[:2], g["xn"])                          # Normalize(ToTensor(x))
+    assert torch.equal(original.cpu(), torch.from_numpy(sc.images).permute(0, 3, 1, 2).float().div(255))   # ToTensor(original)
+    raw = ds.PretextTaskDataset(sc.cfg.subject, transform=False, **common)
+    xu, yu, _ = raw.get_batch(np.arange(len(sc.images)), params=sc.params)
+    assert np.array_equal(xu.cpu().numpy(), g["x"])
+    x0, y0, o0 = dset[0]
+    assert tuple(x0.shape) == (3,) + tuple(x.shape[2:]) and int(y0) in (0, 1, 2) and tuple(o0.shape) == tuple(original.shape[1:])
+
+
+@pytest.mark.gpu
+def test_datamodule_yields_training_batches(tmp_path):
+    import torch
+    from ssad_b200 import datasets as ds
+    root = _png_tree(tmp_path, size=64)
+    dm = ds.PretextTaskDatamodule("bottle", root, imsize=(64, 64), batch_size=8, min_dataset_length=40, seed=0)
+    dm.setup()
+    n = 0
+    for x, y, original in dm.train_dataloader():
+        assert x.shape == (8, 3, 64, 64) and x.dtype == torch.float32 and x.is_cuda
+        assert y.shape == (8,) and y.dtype == torch.int64 and int(y.min()) >= 0 and int(y.max()) <= 2
+        assert original.shape == (8, 3, 64, 64) and float(original.max()) <= 1.0
+        n += 1
+    assert n == len(dm.train_dataloader()) == 5                      # 40 items, drop_last
+    assert len(dm.test_dataloader()) == 5
+    xt, yt, _ = next(iter(dm.test_dataloader()))
+    assert xt.shape[0] == 8
