@@ -30,6 +30,10 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 import numpy as np  # noqa: E402
 
+# the kernel ssad_generate dispatches to for the bench shapes (SSAD_KERNEL pins another one)
+KERNEL_NAME = {None: "generate_v6_kernel", "v6": "generate_v6_kernel", "v5": "generate_v5_kernel", "cluster": "generate_cluster_kernel",
+               "v3": "generate_v3_kernel", "v4": "v4 pipeline (7 kernels)", "generic": "generate_fused_kernel"}.get(os.environ.get("SSAD_KERNEL"), "?")
+
 
 # ------------------------------------------------------------------ workloads
 def make_workload(config: int, batch: int, seed: int = 0):
@@ -335,7 +339,7 @@ def main():
                    "l2": "two alternating resident input/output sets; one step moves more than the 126 MB L2",
                    "parallelism": f"image-sharded x{world}, no collective"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "kernel": "generate_fused_kernel", "algorithmic_bytes_per_image": ab,
+                     "traffic": traffic, "kernel": KERNEL_NAME, "algorithmic_bytes_per_image": ab,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s"},
         "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(images.nbytes + rec_bytes),
                 "d2h_bytes_per_step": int(h_out.numel() + h_y.numel() * 8), "steps": args.e2e_steps},

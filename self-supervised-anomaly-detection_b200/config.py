@@ -63,6 +63,9 @@ class GeneratorConfig:
     force_container_factor: Optional[float] = None
 
     def __post_init__(self):
+        if not 1 <= int(self.num_labels) <= 3:
+            # label 3 ("long line", datasets.py:357-388) is SURVEY.md section 8(f) "next": not built
+            raise ValueError("num_labels must be in 1..3: label 3 of the reference is not implemented")
         if self.patch_area_ratio is None:   # datasets.py:184-185
             self.patch_area_ratio = CPP.rectangle_area_ratio_patch if self.patch_localization else CPP.rectangle_area_ratio
         if self.scar_area_ratio is None:
