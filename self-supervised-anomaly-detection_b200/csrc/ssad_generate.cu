@@ -530,6 +530,11 @@ int ssad_launch_v6(const SsadBatchDesc& d, const SsadImageParams* params, const 
                    const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
                    SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 size_t ssad_v6_workspace(const SsadBatchDesc& d);
+// v7 (pipeline of five kernels: plan / pass 1 / canvas / finish / pass 2, ssad_generate_v7.cu)
+int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
+                   const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
+                   SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+size_t ssad_v7_workspace(const SsadBatchDesc& d);
 
 int ssad_set_cuda_error(cudaError_t e) {
     strncpy(g_cuda_err, cudaGetErrorString(e), sizeof(g_cuda_err) - 1);
@@ -540,6 +545,8 @@ extern "C" size_t ssad_generate_workspace(const SsadBatchDesc* desc) {
     if (!desc || desc->batch <= 0) return 0;
     size_t a = ssad_v5_workspace(*desc), b = ssad_v4_workspace(*desc), c = ssad_v6_workspace(*desc);
     if (b > a) a = b;
+    if (c > a) a = c;
+    c = ssad_v7_workspace(*desc);
     return c > a ? c : a;               // 0 for shapes only the on-chip kernels serve (they need no workspace)
 }
 
@@ -567,7 +574,12 @@ extern "C" int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* p
     // SSAD_KERNEL=v4|v3|cluster|generic pins one (tests, profiling).
     const char* force = getenv("SSAD_KERNEL");
     const bool only_v4 = force && strcmp(force, "v4") == 0, only_v5 = force && strcmp(force, "v5") == 0;
-    const bool only_v6 = force && strcmp(force, "v6") == 0;
+    const bool only_v6 = force && strcmp(force, "v6") == 0, only_v7 = force && strcmp(force, "v7") == 0;
+    if (!force || only_v7) {
+        int rc = ssad_launch_v7(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug, workspace,
+                                workspace_bytes, static_cast<cudaStream_t>(stream));
+        if (rc != SSAD_EUNSUPPORTED || only_v7) return rc;
+    }
     if (!force || only_v6) {
         int rc = ssad_launch_v6(d, params, src, donor_bank, mask_bits, norm_lut, out_u8, out_norm, y_out, debug, workspace,
                                 workspace_bytes, static_cast<cudaStream_t>(stream));

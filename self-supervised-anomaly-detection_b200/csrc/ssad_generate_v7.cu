@@ -1,0 +1,790 @@
+// ssad_generate, B200 path v7: the v6 arithmetic as a pipeline of five kernels on one stream.
+//
+// v6 runs the whole of PretextTaskDataset.__getitem__ (datasets.py:209-394) for one image inside one cluster; ncu shows
+// that kernel issue-bound with 39 % of every CTA's life spent in its short serial phases (geometry, decisions, canvas,
+// tables) and a 1.7-wave tail.  Here each phase is its own grid, sized for what it does, and the two passes over the
+// pixels are pure streaming kernels (thousands of small CTAs, every warp streaming all the time):
+//
+//   plan     CTA / image      parameters -> centres -> container clamp -> paste boxes; rect2poly / rotated-scar coverage
+//                             bit rows; rows-with-a-paste flags; the jitter plan and the tables of the ops ahead of
+//                             Contrast.  Reads the mask bits, no pixel.
+//   pass 1   CTA / slab       (RandomAffine gather) ; RGB sums of x ; ops ahead of Contrast ; sum of L of the unpasted
+//                             pixels ; RGB sums of the would-be cut  -> atomicAdd into the image's accumulators
+//   canvas   NC CTAs / image  cosine > 0.99 decision, flat colours; the patch canvas (packed RGB + L); sum of L of
+//                             the pasted pixels -> atomicAdd
+//   finish   CTA / image      Contrast mean -> tables of Contrast and the ops after it; labels, debug records
+//   pass 2   CTA / slab       re-read the slab (L2), paste on the fly, rest of the chain, stores
+//
+// The per-image state (plan, tables, accumulators), the coverage rows and the row flags live in the caller's workspace.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "ssad_v6_common.cuh"
+
+int ssad_set_cuda_error(cudaError_t e);
+
+namespace ssad {
+namespace v7 {
+
+using namespace v6;
+using namespace u8x;
+
+struct ImgState {                // per image, global memory
+    Plan D;
+    uint32_t acc[8];             // 0-2 RGB of x, 3 sum of L (unpasted), 4-6 RGB of the cut, 7 sum of L (pasted)
+    Tables TP, TF;
+};
+
+struct Geo7 {
+    int H, W, upr, rows_slab, nslab, ncanvas;
+    uint32_t cov_pitch, cov_rows, canvas_pitch;
+    size_t canvas_stride, cov_stride;                       // words per image
+    size_t o_canvas, o_state, o_cov, o_flags, ws_total;     // byte offsets in the workspace (x buffer at 0)
+    int fast;                                               // NT % upr == 0 and every slab holds NT * UPT units
+    uint32_t smem_plan;                                     // dynamic shared memory of the plan kernel (row prefix)
+};
+
+template <typename T>
+__device__ __forceinline__ void copy_words(T* dst, const T* src, int tid) {
+    static_assert(sizeof(T) % 4 == 0, "word copy");
+    uint32_t* d = reinterpret_cast<uint32_t*>(dst);
+    const uint32_t* s = reinterpret_cast<const uint32_t*>(src);
+    for (int i = tid; i < (int)(sizeof(T) / 4); i += NT) d[i] = s[i];
+}
+
+
+// ------------------------------------------------------------------ fast unit loops
+// Geometry of the fast path: NT % upr == 0 (a thread keeps its unit column: x0, the byte alignment and the set of
+// pastes that can touch the column are loop invariants; pointers advance by constants) and the slab holds exactly
+// NT * UPT units (no bounds test).  Every thread announces all its units to the L2 up front (prefetch.global.L2), then
+// keeps one unit of loads in flight in registers.
+constexpr int UPT = 8;
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// sum of Convert.c's L over the 8 pixels of a unit: two 16x8-bit dot products per pixel, straight from the words
+__device__ __forceinline__ uint32_t luma_sum_fast(const uint32_t (&w)[6]) {
+    constexpr uint32_t kRG = (38470u << 16) | 19595u, kB0 = 7471u, kR3 = 19595u << 16, kGB = (7471u << 16) | 38470u;
+    uint32_t s = 0;
+    #pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const uint32_t w0 = w[3 * q], w1 = w[3 * q + 1], w2 = w[3 * q + 2];
+        s += dp2a_hi(kB0, w0, dp2a_lo(kRG, w0, 0x8000u)) >> 16;        // bytes 0,1,2 of w0
+        s += dp2a_lo(kGB, w1, dp2a_hi(kR3, w0, 0x8000u)) >> 16;        // byte 3 of w0, bytes 0,1 of w1
+        s += dp2a_lo(kB0, w2, dp2a_hi(kRG, w1, 0x8000u)) >> 16;        // bytes 2,3 of w1, byte 0 of w2
+        s += dp2a_hi(kGB, w2, dp2a_lo(kR3, w2, 0x8000u)) >> 16;        // bytes 1,2,3 of w2
+    }
+    return s;
+}
+__device__ __forceinline__ uint32_t luma_sum_fast_skip(const uint32_t (&w)[6], uint32_t skip) {
+    uint32_t L[8];
+    luma_words(w, L);
+    uint32_t s = 0;
+    #pragma unroll
+    for (int p = 0; p < 8; ++p) s += ((skip >> p) & 1u) ? 0u : L[p];
+    return s;
+}
+
+struct FastCol {                // a thread's unit column
+    int rr0, cu, x0, dr;
+    uint32_t mis, colhit;
+};
+__device__ __forceinline__ FastCol fast_col(const Plan& D, int upr, int tid) {
+    FastCol F;
+    F.rr0 = tid / upr; F.cu = tid - F.rr0 * upr; F.x0 = F.cu * 8; F.dr = NT / upr;
+    F.mis = 0; F.colhit = 0;
+    if (D.y != 0)
+        for (int k = 0; k < D.npaste; ++k) {
+            const int u0 = F.x0 - D.paste[k][0];
+            if (u0 + 8 > 0 && u0 < D.bw) F.colhit |= 1u << k;
+        }
+    return F;
+}
+
+template <int LK>
+__device__ __forceinline__ void pass1_fast(const uint8_t* in0 /* slab row 0 */, int in_pitch, uint8_t* xb0 /* slab row 0 */,
+                                           int xpitch, bool store, bool need_rgb, bool need_luma, const ProgRegs& R,
+                                           const Plan& D, const Boxes& BX, const uint8_t* flags, int r0, int upr, int tid,
+                                           uint32_t (&acc)[7]) {
+    FastCol F = fast_col(D, upr, tid);
+    const uint8_t* ip = in0 + (size_t)F.rr0 * in_pitch + F.cu * 24;
+    F.mis = (uint32_t)(reinterpret_cast<uintptr_t>(ip) & 7u);
+    ip -= F.mis;
+    const size_t istep = (size_t)F.dr * in_pitch;
+    uint8_t* op = xb0 + (size_t)F.rr0 * xpitch + F.cu * 24;
+    const size_t ostep = (size_t)F.dr * xpitch;
+    #pragma unroll
+    for (int it = 1; it < UPT; ++it) prefetch_l2(ip + it * istep + 16);
+    uint32_t s0 = 0, s1 = 0, s2 = 0, sl = 0;
+    const bool four = F.mis != 0;
+    Raw nx;
+    ld_raw(ip, four, false, nx);
+    int rr = F.rr0;
+    uint32_t fnx = F.colhit ? (uint32_t)flags[rr] : 0u;
+    #pragma unroll 2
+    for (int it = 0; it < UPT; ++it) {
+        const Raw cur = nx;
+        const uint32_t rf = fnx & F.colhit;
+        const int yy = r0 + rr;
+        ip += istep; rr += F.dr;
+        if (it + 1 < UPT) {
+            ld_raw(ip, four, false, nx);
+            if (F.colhit) fnx = flags[rr];
+        }
+        uint32_t w[6];
+        raw_to_words(cur, F.mis, w);
+        if (need_rgb) {
+            uint32_t s[3] = {s0, s1, s2};
+            rgb_sums(w, s);
+            s0 = s[0]; s1 = s[1]; s2 = s[2];
+        }
+        if (need_luma) {
+            apply_prog<LK>(w, R);
+            // sum of L of what Contrast will see, minus the pixels a paste replaces (their L comes from the canvas)
+            const uint32_t skip = rf ? covered_bits8(D, BX, rf, yy, F.x0) : 0u;
+            sl += skip ? luma_sum_fast_skip(w, skip) : luma_sum_fast(w);
+            if (store) {                        // the x buffer keeps pre(x): pass 2 starts from there
+                uint2* const o = reinterpret_cast<uint2*>(op);
+                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+            }
+        }
+        op += ostep;
+    }
+    acc[0] += s0; acc[1] += s1; acc[2] += s2; acc[3] += sl;
+}
+
+template <int LK>
+__device__ __forceinline__ void pass2_fast(const uint8_t* in0 /* slab row 0 */, int in_pitch, const ProgRegs& R, const Plan& D,
+                                           const Boxes& BX, const uint8_t* flags, int r0, int upr, int tid, int W, int npix,
+                                           uint8_t* obase, void* onorm, int norm_dtype, const uint8_t* lutbase) {
+    FastCol F = fast_col(D, upr, tid);
+    const uint8_t* ip = in0 + (size_t)F.rr0 * in_pitch + F.cu * 24;
+    F.mis = (uint32_t)(reinterpret_cast<uintptr_t>(ip) & 7u);
+    ip -= F.mis;
+    const size_t istep = (size_t)F.dr * in_pitch;
+    int p0 = (r0 + F.rr0) * W + F.x0;                      // first pixel of the current unit inside the image
+    const int pstep = F.dr * W;
+    uint8_t* op = obase ? obase + (size_t)p0 * 3 : nullptr;
+    const size_t ostep = (size_t)pstep * 3;
+    #pragma unroll
+    for (int it = 1; it < UPT; ++it) prefetch_l2(ip + it * istep + 16);
+    const bool four = F.mis != 0;
+    Raw nx;
+    ld_raw(ip, four, false, nx);
+    int rr = F.rr0;
+    uint32_t fnx = F.colhit ? (uint32_t)flags[rr] : 0u;
+    #pragma unroll 2
+    for (int it = 0; it < UPT; ++it) {
+        const Raw cur = nx;
+        const uint32_t rf = fnx & F.colhit;
+        const int yy = r0 + rr;
+        ip += istep; rr += F.dr;
+        if (it + 1 < UPT) {
+            ld_raw(ip, four, false, nx);
+            if (F.colhit) fnx = flags[rr];
+        }
+        uint32_t w[6];
+        raw_to_words(cur, F.mis, w);
+        if (rf) paste_unit(D, BX, rf, yy, F.x0, w);
+        apply_prog<LK>(w, R);
+        if (op) {
+            uint2* o = reinterpret_cast<uint2*>(op);
+            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+            op += ostep;
+        }
+        if (onorm) {
+            // ToTensor + Normalize (datasets.py:392-393): exact table per channel, NCHW planes
+            uint32_t e[24];
+            #pragma unroll
+            for (int i = 0; i < 24; ++i) e[i] = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;      // byte i = pixel i / 3, channel i % 3
+            if (norm_dtype == SSAD_NORM_F32) {
+                const float* lut = reinterpret_cast<const float*>(lutbase);
+                float* ob = reinterpret_cast<float*>(onorm);
+                #pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    float4* o = reinterpret_cast<float4*>(ob + (size_t)ch * npix + p0);
+                    #pragma unroll
+                    for (int qq = 0; qq < 2; ++qq) {
+                        float4 v;
+                        v.x = lut[ch * 256 + e[3 * (4 * qq + 0) + ch]];
+                        v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
+                        v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
+                        v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
+                        o[qq] = v;
+                    }
+                }
+            } else {
+                const uint16_t* lut = reinterpret_cast<const uint16_t*>(lutbase);
+                uint16_t* ob = reinterpret_cast<uint16_t*>(onorm);
+                #pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    uint32_t wv[4];
+                    #pragma unroll
+                    for (int qq = 0; qq < 4; ++qq) {
+                        uint32_t lo = lut[ch * 256 + e[3 * (2 * qq) + ch]];
+                        uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
+                        wv[qq] = lo | (hi << 16);
+                    }
+                    *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+                }
+            }
+        }
+        p0 += pstep;
+    }
+}
+
+// ================================================================ plan
+__global__ void __launch_bounds__(NT)
+plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
+               const SsadImageParams* __restrict__ params, const uint32_t* __restrict__ mask_bits,
+               ImgState* __restrict__ state, uint32_t* __restrict__ cov_all, uint8_t* __restrict__ flags_all) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ SsadImageParams P;
+    __shared__ Plan D;
+    __shared__ Polygon G;
+    __shared__ Tables TP;
+    uint32_t* const rowpre = reinterpret_cast<uint32_t*>(smem);
+    const int tid = threadIdx.x, b = blockIdx.x;
+    const int H = g.H, W = g.W, npix = H * W;
+    uint32_t* const cov = cov_all + (size_t)b * g.cov_stride;
+    uint8_t* const flags = flags_all + (size_t)b * H;
+    ImgState* const S = state + b;
+
+    if (tid < (int)(sizeof(SsadImageParams) / 4))
+        reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
+    if (tid < 8) S->acc[tid] = 0;
+    __syncthreads();
+
+    const int cx0 = P.crop_off[0], cy0 = P.crop_off[1];
+    const uint32_t* mrow0 = nullptr;
+    if (d.mask_mode != SSAD_MASK_ALL)
+        mrow0 = mask_bits + (d.mask_mode == SSAD_MASK_PER_IMAGE ? (size_t)b * d.mask_stride_words : 0);
+    const bool defect = P.label != 0;
+    const int pw = P.rect[2], ph = P.rect[3];
+    if (defect && d.mask_mode != SSAD_MASK_ALL) {
+        // mask window: per-row popcounts -> prefix (coords_map is row-major, datasets.py:263-264)
+        for (int r = tid; r < H; r += NT)
+            rowpre[r + 1] = row_window_popc(mrow0 + (size_t)(cy0 + r) * d.mask_pitch_words, cx0, W);
+        __syncthreads();
+        if (tid < 32) {
+            uint32_t carry = 0;
+            for (int base = 0; base < H; base += 32) {
+                int r = base + tid;
+                uint32_t v = (r < H) ? rowpre[r + 1] : 0, s = v;
+                for (int o = 1; o < 32; o <<= 1) {
+                    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, s, o);
+                    if (tid >= o) s += t;
+                }
+                if (r < H) rowpre[r + 1] = carry + s;
+                carry += __shfl_sync(0xFFFFFFFFu, s, 31);
+            }
+            if (tid == 0) rowpre[0] = 0;
+        }
+        __syncthreads();
+    }
+    const int n_coords = (d.mask_mode == SSAD_MASK_ALL) ? npix : (defect ? (int)rowpre[H] : 0);
+    int y = P.label;
+    if (defect && d.coverage_min3 > 0 && 3 * n_coords < d.coverage_min3) y = 0;   // datasets.py:258-259
+    const int npaste = (y == 0) ? 0 : (y == 1 ? 1 : P.scar_k);
+    const int bw = (y == 1) ? pw : P.scar_size[0], bh = (y == 1) ? ph : P.scar_size[1];
+    if (tid < npaste) {
+        // centres + container clamp (dataset_generator.py:104-144, 259-265): one thread per paste
+        int cx, cy;
+        if (n_coords == 0) {
+            cx = P.fallback_c[tid][0]; cy = P.fallback_c[tid][1];
+        } else {
+            uint32_t idx = (n_coords < 2) ? 0u : (uint32_t)(((uint64_t)P.centre_r[tid] * (uint64_t)n_coords) >> 32);
+            if (d.mask_mode == SSAD_MASK_ALL) {
+                cy = idx / W; cx = idx - cy * W;
+            } else {
+                int lo = 0, hi = H;
+                while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (rowpre[mid] <= idx) lo = mid; else hi = mid; }
+                cy = lo;
+                cx = row_window_select(mrow0 + (size_t)(cy0 + cy) * d.mask_pitch_words, cx0, W, idx - rowpre[lo]);
+            }
+        }
+        int pl, pt;
+        clamp_to_container(y == 1 ? d.box_poly : d.box_scar, bw, bh, cx, cy, pl, pt);
+        D.paste[tid][0] = pl; D.paste[tid][1] = pt;
+    } else if (tid < 5) {
+        D.paste[tid][0] = 0; D.paste[tid][1] = 0;
+    }
+    if (y == 1 && tid == 32) polygon_setup(G, P.poly_xy, P.poly_n, ph);
+    if (tid == 64) {
+        D.y = y; D.npaste = npaste; D.n_coords = n_coords; D.bw = bw; D.bh = bh;
+        D.sim = 0; D.flat = 0; D.cosine = 0.0; D.cmean = -1;
+        D.flat_rgb[0] = D.flat_rgb[1] = D.flat_rgb[2] = 0;
+        D.avg_rgb[0] = D.avg_rgb[1] = D.avg_rgb[2] = 0;
+        D.bf1 = P.bright_f[0]; D.bf2 = P.bright_f[1];
+        // ColorJitter plan (datasets.py:391): ops in fn_idx order, positions of Contrast and Saturation
+        int nops = 0, cpos = -1, spos = -1;
+        D.ops[0] = D.ops[1] = D.ops[2] = 0; D.fac[0] = D.fac[1] = D.fac[2] = 1.0f;
+        for (int st = 0; st < 4; ++st) {
+            int fn = P.jit_order[st];
+            if (fn < 3 && ((P.jit_en >> fn) & 1)) {
+                if (fn == 1) cpos = nops;
+                if (fn == 2) spos = nops;
+                D.ops[nops] = fn; D.fac[nops] = P.jit_f[fn]; ++nops;
+            }
+        }
+        D.nops = nops; D.cpos = cpos;
+        D.s_in_pre = (cpos >= 0 && spos >= 0 && spos < cpos) ? 1 : 0;
+        D.fin.kind = PK_COPY; D.fin.sa = D.fin.sb = 0; D.fin.fs = 1.0f;
+    }
+    __syncthreads();
+    build_prog(D.pre, TP, D.ops, D.fac, 0, max(D.cpos, 0), 0, tid);      // ops ahead of Contrast (never Contrast itself)
+    const int pitchw = (int)g.cov_pitch;
+    if (y == 1) {
+        // rect2poly bit rows (dataset_generator.py:63-100)
+        for (int v = tid; v < ph; v += NT) {
+            uint32_t* row = cov + (size_t)v * pitchw;
+            for (int j = 0; j < pitchw; ++j) row[j] = 0;
+            polygon_fill_row(G, v, pw, row);
+        }
+    } else if (y == 2) {
+        // alpha of scar.rotate(angle, expand=True) (datasets.py:344): per canvas row one span of u, in closed form
+        for (int v = tid; v < bh; v += NT) {
+            uint32_t* row = cov + (size_t)v * pitchw;
+            for (int j = 0; j < pitchw; ++j) row[j] = 0;
+            int lo = 0, hi = bw - 1;
+            affine_span((long long)P.scar_fix[2] + (long long)v * P.scar_fix[1], P.scar_fix[0], (long long)pw << 16, lo, hi);
+            affine_span((long long)P.scar_fix[5] + (long long)v * P.scar_fix[4], P.scar_fix[3], (long long)ph << 16, lo, hi);
+            if (lo <= hi) row_set_bits(row, lo, hi);
+        }
+    }
+    for (int r = tid; r < H; r += NT) {
+        uint32_t f = 0;
+        for (int k = 0; k < npaste; ++k) {
+            const int v = r - D.paste[k][1];
+            if (v >= 0 && v < bh) f |= 1u << k;
+        }
+        flags[r] = (uint8_t)f;
+    }
+    __syncthreads();
+    copy_words(&S->D, &D, tid);
+    copy_words(&S->TP, &TP, tid);
+}
+
+// ================================================================ pass 1
+__global__ void __launch_bounds__(NT, 4)
+pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
+                const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
+                const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state,
+                const uint32_t* __restrict__ cov_all, const uint8_t* __restrict__ flags_all, uint8_t* xbuf) {
+    __shared__ SsadImageParams P;
+    __shared__ Plan D;
+    __shared__ Tables TP;
+    __shared__ uint32_t red[NWARP * 8 + 8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = (int)(blockIdx.x / (unsigned)g.nslab), slab = (int)(blockIdx.x - (unsigned)b * g.nslab);
+    const int H = g.H, W = g.W, npix = H * W;
+    ImgState* const S = state + b;
+    if (tid < (int)(sizeof(SsadImageParams) / 4))
+        reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
+    copy_words(&D, &S->D, tid);
+    copy_words(&TP, &S->TP, tid);
+    __syncthreads();
+
+    const int y = D.y, cpos = D.cpos;
+    const bool warped = P.warp_en != 0;
+    if (!warped && y == 0 && cpos < 0) return;
+    const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
+    const int cx0 = P.crop_off[0], cy0 = P.crop_off[1];
+    const int nunits = (r1 - r0) * g.upr;
+    const uint8_t* const sbase = src + (size_t)b * d.src_stride + (size_t)cy0 * d.src_pitch + (size_t)cx0 * 3;
+    const int spitch = (int)d.src_pitch;
+    uint8_t* const xb = xbuf + (size_t)b * npix * 3;
+    const int xpitch = W * 3;
+    Boxes BX;
+    BX.cov = cov_all + (size_t)b * g.cov_stride; BX.canvas = nullptr; BX.pitch = (int)g.cov_pitch; BX.cpitch = (int)g.canvas_pitch;
+    BX.bw = D.bw; BX.bh = D.bh; BX.npaste = D.npaste;
+    const uint8_t* const flags = flags_all + (size_t)b * H + r0;
+
+    uint32_t acc[7] = {0, 0, 0, 0, 0, 0, 0};          // 0-2 RGB of x, 3 sum of L, 4-6 RGB of the cut
+    const Slab SL = make_slab(r0, nunits, g.upr, tid);
+    if (warped) {
+        // RandomAffine(3, scale=(1.05, 1.1)) NEAREST, fill 0 (datasets.py:220-222): x gathered once into the x buffer
+        const int32_t a0 = P.warp_fix[0], a1 = P.warp_fix[1], a2 = P.warp_fix[2];
+        const int32_t a3 = P.warp_fix[3], a4 = P.warp_fix[4], a5 = P.warp_fix[5];
+        SSAD_SLAB_LOOP(SL) {
+            const int yy = r0 + rr, x0 = cu * 8;
+            const int xr = a2 + yy * a1 + x0 * a0, yr = a5 + yy * a4 + x0 * a3;
+            uint32_t w[6] = {0, 0, 0, 0, 0, 0};
+            #define SSAD_GATHER(PIX)                                                                      \
+                { const int xin = (xr + PIX * a0) >> 16, yin = (yr + PIX * a3) >> 16;                     \
+                  if ((unsigned)xin < (unsigned)W && (unsigned)yin < (unsigned)H) {                       \
+                      const uint8_t* q = sbase + yin * spitch + xin * 3;                                  \
+                      put_pixel<PIX>(w, __ldg(q), __ldg(q + 1), __ldg(q + 2)); } }
+            SSAD_GATHER(0) SSAD_GATHER(1) SSAD_GATHER(2) SSAD_GATHER(3) SSAD_GATHER(4) SSAD_GATHER(5) SSAD_GATHER(6) SSAD_GATHER(7)
+            #undef SSAD_GATHER
+            uint2* const o = reinterpret_cast<uint2*>(xb + (size_t)r0 * xpitch + (size_t)lin * 24);
+            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+        }
+    }
+    if (y == 0 && cpos < 0) return;
+    // x as the passes read it (each thread re-reads only what it wrote itself)
+    const uint8_t* const xin_base = warped ? xb : sbase;
+    const int xin_pitch = warped ? xpitch : spitch;
+    {
+        ProgRegs R;
+        R.fs = D.pre.fs; R.ta = smem_u32(TP.a); R.tab = smem_u32(TP.ab); R.tbc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
+        const bool need_rgb = y != 0, need_luma = cpos >= 0;
+        if (g.fast) {
+            const uint8_t* const in0 = xin_base + (size_t)r0 * xin_pitch;
+            uint8_t* const xb0 = xb + (size_t)r0 * xpitch;
+            switch (loop_kind(D.pre)) {
+                case LK_COPY:    pass1_fast<LK_COPY>(in0, xin_pitch, xb0, xpitch, false, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
+                case LK_BYTELUT: pass1_fast<LK_BYTELUT>(in0, xin_pitch, xb0, xpitch, false, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
+                case LK_SAT_UC:  pass1_fast<LK_SAT_UC>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
+                case LK_SAT_UL:  pass1_fast<LK_SAT_UL>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
+                case LK_SAT_LC:  pass1_fast<LK_SAT_LC>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
+                default:         pass1_fast<LK_SAT_LL>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
+            }
+        } else
+        switch (loop_kind(D.pre)) {
+            case LK_COPY:    pass1_loop<LK_COPY>(SL, xin_base, xin_pitch, !warped, xb, xpitch, false, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_BYTELUT: pass1_loop<LK_BYTELUT>(SL, xin_base, xin_pitch, !warped, xb, xpitch, false, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_SAT_UC:  pass1_loop<LK_SAT_UC>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_SAT_UL:  pass1_loop<LK_SAT_UL>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            case LK_SAT_LC:  pass1_loop<LK_SAT_LC>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            default:         pass1_loop<LK_SAT_LL>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+        }
+        // RGB sums of the would-be cut (dataset_generator.py:202-207 / 147-159): rows dealt over the image's warps
+        if (y != 0 && P.src_variant != 2) {
+            const Donor dn = donor_of(d, src, donor_bank, b, P);
+            for (int v = slab * NWARP + warp; v < dn.v_hi; v += g.nslab * NWARP) {
+                const uint8_t* q = dn.base + (size_t)v * dn.pitch;
+                for (int u = lane; u < dn.u_hi; u += 32) {
+                    acc[4] += __ldg(q + 3 * u); acc[5] += __ldg(q + 3 * u + 1); acc[6] += __ldg(q + 3 * u + 2);
+                }
+            }
+        }
+    }
+    block_sum_vec<7>(acc, red);
+    #pragma unroll
+    for (int i = 0; i < 7; ++i)
+        if (tid == i && acc[i] != 0) atomicAdd(&S->acc[i], acc[i]);
+}
+
+// ================================================================ canvas
+__global__ void __launch_bounds__(NT)
+canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
+                 const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
+                 const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state,
+                 const uint32_t* __restrict__ cov_all, uint32_t* __restrict__ canvas_all) {
+    __shared__ SsadImageParams P;
+    __shared__ Plan D;
+    __shared__ Tables TP;
+    __shared__ uint8_t simtab[256];
+    __shared__ uint32_t red[NWARP * 8 + 8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = (int)(blockIdx.x / (unsigned)g.ncanvas), part = (int)(blockIdx.x - (unsigned)b * g.ncanvas);
+    const int H = g.H, W = g.W, npix = H * W;
+    ImgState* const S = state + b;
+    if (S->D.y == 0) return;                     // (uniform over the CTA)
+    if (tid < (int)(sizeof(SsadImageParams) / 4))
+        reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
+    copy_words(&D, &S->D, tid);
+    copy_words(&TP, &S->TP, tid);
+    __syncthreads();
+    const int y = D.y, npaste = D.npaste, bw = D.bw, bh = D.bh, cpos = D.cpos;
+    const bool s_in_pre = D.s_in_pre != 0;
+    const int pw = P.rect[2], ph = P.rect[3];
+    const uint32_t* const cov = cov_all + (size_t)b * g.cov_stride;
+    uint32_t* const canvas = canvas_all + (size_t)b * g.canvas_stride;
+    const int pitchw = (int)g.cov_pitch;
+    const Donor dn = donor_of(d, src, donor_bank, b, P);
+
+    // ---- check_color_similarity + variant colours (every CTA of the image decides the same; part 0 records it)
+    if (tid == 0) {
+        const uint32_t np = (uint32_t)(pw * ph);
+        uint32_t xs[3] = {S->acc[0], S->acc[1], S->acc[2]};
+        uint32_t psum[3] = {S->acc[4], S->acc[5], S->acc[6]};
+        int flat = 0;
+        uint32_t frgb[3] = {0, 0, 0};
+        int avg[3] = {0, 0, 0};
+        if (P.src_variant == 1) {           // colour = int(mean) (dataset_generator.py:202-207)
+            flat = 1;
+            for (int k = 0; k < 3; ++k) { frgb[k] = psum[k] / np; avg[k] = (int)frgb[k]; psum[k] = frgb[k] * np; }
+        } else if (P.src_variant == 2) {    // random colour (dataset_generator.py:194-199)
+            flat = 1;
+            for (int k = 0; k < 3; ++k) { frgb[k] = P.rnd_rgb[k]; psum[k] = frgb[k] * np; }
+        }
+        double cs;
+        const bool sim = similarity_branch(xs, (double)npix, psum, (double)np, cs);     // datasets.py:295 / 335
+        if (flat && sim)                    // brightness of a flat patch is a flat patch
+            for (int k = 0; k < 3; ++k) frgb[k] = brightness_u8(brightness_u8(frgb[k], D.bf1), D.bf2);
+        D.flat = flat; D.sim = sim ? 1 : 0; D.cosine = cs;
+        for (int k = 0; k < 3; ++k) { D.flat_rgb[k] = frgb[k]; D.avg_rgb[k] = avg[k]; }
+        if (part == 0) {
+            S->D.flat = flat; S->D.sim = sim ? 1 : 0; S->D.cosine = cs;
+            for (int k = 0; k < 3; ++k) { S->D.flat_rgb[k] = frgb[k]; S->D.avg_rgb[k] = avg[k]; }
+        }
+    }
+    __syncthreads();
+    Colour K;
+    K.flat = D.flat; K.sim = D.sim; K.bf1 = D.bf1; K.bf2 = D.bf2;
+    K.frgb[0] = D.flat_rgb[0]; K.frgb[1] = D.flat_rgb[1]; K.frgb[2] = D.flat_rgb[2];
+
+    // ---- patch canvas: canvas pixel (u, v) -> packed (r, g, b, L); this CTA fills its share of the rows that land
+    // inside the image, one warp per row
+    uint32_t lnew = 0;
+    const bool cut_sim = !K.flat && K.sim;
+    if (cut_sim) {
+        for (int v = tid; v < 256; v += NT) simtab[v] = (uint8_t)brightness_u8(brightness_u8((uint32_t)v, K.bf1), K.bf2);
+        __syncthreads();
+    }
+    int cv_lo = bh, cv_hi = 0;
+    for (int k = 0; k < npaste; ++k) {
+        const int pt = D.paste[k][1];
+        const int v_lo = max(0, -pt), v_hi = min(bh, H - pt);
+        if (v_lo < v_hi) { cv_lo = min(cv_lo, v_lo); cv_hi = max(cv_hi, v_hi); }
+    }
+    const int per = (max(cv_hi - cv_lo, 0) + g.ncanvas - 1) / g.ncanvas;
+    const int my_lo = cv_lo + part * per, my_hi = min(cv_hi, my_lo + per);
+    const int cpitch = (int)g.canvas_pitch;
+    const int pl0 = D.paste[0][0];
+    const bool want_l = cpos >= 0;
+    for (int v = my_lo + warp; v < my_hi; v += NWARP) {
+        const uint32_t* crow = cov + (size_t)v * pitchw;
+        uint32_t* out = canvas + (size_t)v * cpitch;
+        const int xr = P.scar_fix[2] + v * P.scar_fix[1], yr = P.scar_fix[5] + v * P.scar_fix[4];
+        for (int u = lane; u < bw; u += 32) {
+            if (!((crow[u >> 5] >> (u & 31)) & 1u)) continue;
+            uint32_t r, gg, bl;
+            if (K.flat) { r = K.frgb[0]; gg = K.frgb[1]; bl = K.frgb[2]; }
+            else {
+                int su = u, sv = v;          // source pixel of the cut: itself (polygon) | inverse rotation (scar)
+                if (y == 2) { su = (xr + u * P.scar_fix[0]) >> 16; sv = (yr + u * P.scar_fix[3]) >> 16; }
+                r = gg = bl = 0;
+                if (su < dn.u_hi && sv < dn.v_hi) {
+                    const uint8_t* q = dn.base + (size_t)sv * dn.pitch + 3 * su;
+                    r = __ldg(q); gg = __ldg(q + 1); bl = __ldg(q + 2);
+                }
+                if (cut_sim) { r = simtab[r]; gg = simtab[gg]; bl = simtab[bl]; }
+            }
+            uint32_t L = 0;
+            if (want_l) {
+                uint32_t pr = r, pg = gg, pb = bl;
+                pixel_prog(D.pre, TP, pr, pg, pb);
+                L = luma_u8(pr, pg, pb);
+                if (s_in_pre) { r = pr; gg = pg; bl = pb; }
+                // a polygon is pasted once: visible wherever it lands inside the image
+                if (y == 1 && (unsigned)(pl0 + u) < (unsigned)W) lnew += L;
+            }
+            out[u] = r | (gg << 8) | (bl << 16) | (L << 24);
+        }
+    }
+    if (cpos < 0) return;
+    __syncthreads();
+    if (y == 2) {
+        // scars: k pastes of the same canvas, later ones overwrite earlier ones
+        for (int k = 0; k < npaste; ++k) {
+            const int pl = D.paste[k][0], pt = D.paste[k][1];
+            const int v_lo = max(max(0, -pt), my_lo), v_hi = min(min(bh, H - pt), my_hi);
+            for (int v = v_lo + warp; v < v_hi; v += NWARP) {
+                const int Y = pt + v;
+                for (int u = lane; u < bw; u += 32) {
+                    const int X = pl + u;
+                    if (X < 0 || X >= W) continue;
+                    if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
+                    bool later = false;          // a later paste overwrites this pixel: it is counted there
+                    for (int j = k + 1; j < npaste; ++j) {
+                        const int uj = X - D.paste[j][0], vj = Y - D.paste[j][1];
+                        if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) later = true;
+                    }
+                    if (later) continue;
+                    lnew += canvas[(size_t)v * cpitch + u] >> 24;
+                }
+            }
+        }
+    }
+    uint32_t v1[1] = {lnew};
+    block_sum_vec<1>(v1, red);
+    if (tid == 0 && v1[0] != 0) atomicAdd(&S->acc[7], v1[0]);
+}
+
+// ================================================================ finish
+__global__ void __launch_bounds__(NT)
+finish_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g, ImgState* __restrict__ state,
+                 int64_t* __restrict__ y_out, SsadDebug* __restrict__ debug) {
+    __shared__ Plan D;
+    __shared__ Tables TF;
+    const int tid = threadIdx.x, b = blockIdx.x;
+    const int npix = g.H * g.W;
+    ImgState* const S = state + b;
+    copy_words(&D, &S->D, tid);
+    __syncthreads();
+    const int cpos = D.cpos, nops = D.nops;
+    int cmean = -1;
+    if (cpos >= 0) {
+        // int(mean + 0.5) with mean = sum / count in float64 (ImageEnhance.py Contrast) == integer rounding
+        const uint32_t lsum = S->acc[3] + S->acc[7];
+        cmean = (int)((2ull * lsum + (uint32_t)npix) / (2ull * (uint32_t)npix));
+    }
+    // what pass 2 still has to do: Contrast and the ops after it on pre(x), or the whole chain on x
+    build_prog(D.fin, TF, D.ops, D.fac, D.s_in_pre ? cpos : 0, nops, cmean, tid);
+    if (tid == 0) D.cmean = cmean;
+    __syncthreads();
+    copy_words(&S->D, &D, tid);
+    copy_words(&S->TF, &TF, tid);
+    if (tid == 0) {
+        const int y = D.y;
+        if (y_out) y_out[b] = y;
+        if (debug) {
+            SsadDebug o;
+            memset(&o, 0, sizeof(o));
+            o.n_coords = D.n_coords;
+            o.label_out = y;
+            o.contrast_mean = cmean;
+            if (y != 0) {
+                o.sim = D.sim;
+                o.cosine = D.cosine;
+                for (int k = 0; k < D.npaste; ++k) { o.paste[k][0] = D.paste[k][0]; o.paste[k][1] = D.paste[k][1]; }
+                for (int k = 0; k < 3; ++k) o.avg_rgb[k] = D.avg_rgb[k];
+            }
+            debug[b] = o;
+        }
+    }
+}
+
+// ================================================================ pass 2
+__global__ void __launch_bounds__(NT, 4)
+pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
+                const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
+                const ImgState* __restrict__ state, const uint32_t* __restrict__ cov_all,
+                const uint8_t* __restrict__ flags_all, const uint8_t* xbuf, const uint32_t* __restrict__ canvas_all,
+                const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8, void* __restrict__ out_norm) {
+    __shared__ Plan D;
+    __shared__ Tables TF;
+    __shared__ __align__(16) uint8_t lut_s[3072];
+    __shared__ int32_t hdr[4];
+    const int tid = threadIdx.x;
+    const int b = (int)(blockIdx.x / (unsigned)g.nslab), slab = (int)(blockIdx.x - (unsigned)b * g.nslab);
+    const int H = g.H, W = g.W, npix = H * W;
+    const ImgState* const S = state + b;
+    copy_words(&D, &S->D, tid);
+    copy_words(&TF, &S->TF, tid);
+    if (tid == 0) {
+        const SsadImageParams* p = params + b;
+        hdr[0] = p->crop_off[0]; hdr[1] = p->crop_off[1]; hdr[2] = p->warp_en;
+    }
+    if (out_norm != nullptr) {
+        const int nw = (d.out_norm_dtype == SSAD_NORM_F32) ? 768 : 384;
+        for (int i = tid; i < nw; i += NT)
+            reinterpret_cast<uint32_t*>(lut_s)[i] = reinterpret_cast<const uint32_t*>(norm_lut)[i];
+    }
+    __syncthreads();
+    const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
+    const int nunits = (r1 - r0) * g.upr;
+    const int cx0 = hdr[0], cy0 = hdr[1];
+    const bool stored = hdr[2] != 0 || D.s_in_pre != 0;          // pass 1 left its bytes in the x buffer
+    const uint8_t* const sbase = src + (size_t)b * d.src_stride + (size_t)cy0 * d.src_pitch + (size_t)cx0 * 3;
+    const uint8_t* const xb = xbuf + (size_t)b * npix * 3;
+    Boxes BX;
+    BX.cov = cov_all + (size_t)b * g.cov_stride; BX.canvas = canvas_all + (size_t)b * g.canvas_stride;
+    BX.pitch = (int)g.cov_pitch; BX.cpitch = (int)g.canvas_pitch; BX.bw = D.bw; BX.bh = D.bh; BX.npaste = D.npaste;
+    const uint8_t* const flags = flags_all + (size_t)b * H + r0;
+    const Slab SL = make_slab(r0, nunits, g.upr, tid);
+    ProgRegs R;
+    R.fs = D.fin.fs; R.ta = smem_u32(TF.a); R.tab = smem_u32(TF.ab); R.tbc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
+    const uint8_t* const in2 = stored ? xb : sbase;
+    const int in2_pitch = stored ? W * 3 : (int)d.src_pitch;
+    uint8_t* const obase = out_u8 ? out_u8 + (size_t)b * d.out_u8_stride : nullptr;
+    void* onorm = nullptr;
+    if (out_norm) onorm = (d.out_norm_dtype == SSAD_NORM_F32) ? (void*)(reinterpret_cast<float*>(out_norm) + (size_t)b * 3 * npix)
+                                                               : (void*)(reinterpret_cast<uint16_t*>(out_norm) + (size_t)b * 3 * npix);
+    if (g.fast) {
+        const uint8_t* const in0 = in2 + (size_t)r0 * in2_pitch;
+        switch (loop_kind(D.fin)) {
+            case LK_COPY:    pass2_fast<LK_COPY>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+            case LK_BYTELUT: pass2_fast<LK_BYTELUT>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+            case LK_SAT_UC:  pass2_fast<LK_SAT_UC>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+            case LK_SAT_UL:  pass2_fast<LK_SAT_UL>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+            case LK_SAT_LC:  pass2_fast<LK_SAT_LC>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+            default:         pass2_fast<LK_SAT_LL>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+        }
+        return;
+    }
+    switch (loop_kind(D.fin)) {
+        case LK_COPY:    pass2_loop<LK_COPY>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+        case LK_BYTELUT: pass2_loop<LK_BYTELUT>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+        case LK_SAT_UC:  pass2_loop<LK_SAT_UC>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+        case LK_SAT_UL:  pass2_loop<LK_SAT_UL>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+        case LK_SAT_LC:  pass2_loop<LK_SAT_LC>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+        default:         pass2_loop<LK_SAT_LL>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+    }
+}
+
+static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
+    g.H = d.height; g.W = d.width;
+    if (g.W % 8 != 0 || g.W < 8) return false;
+    if (!(d.sat_factor_max <= kSatMax)) return false;       // the table after Saturation covers factors up to kSatMax
+    g.upr = g.W / 8;
+    int upt = UPT;                                          // units per thread and slab
+    if (const char* f = getenv("SSAD_V7_UPT")) { int v = atoi(f); if (v > 0 && v <= 64) upt = v; }
+    g.rows_slab = (NT * upt + g.upr - 1) / g.upr;
+    if (g.rows_slab < 1) g.rows_slab = 1;
+    if (g.rows_slab > g.H) g.rows_slab = g.H;
+    g.nslab = (g.H + g.rows_slab - 1) / g.rows_slab;
+    g.fast = (NT % g.upr == 0 && upt == UPT && g.rows_slab * g.upr == NT * UPT && g.H % g.rows_slab == 0) ? 1 : 0;
+    if (getenv("SSAD_V7_NOFAST")) g.fast = 0;
+    g.ncanvas = 4;
+    if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
+    g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;
+    g.cov_rows = (uint32_t)d.max_patch_h;
+    g.cov_stride = (size_t)g.cov_pitch * g.cov_rows;
+    g.canvas_pitch = (uint32_t)d.max_patch_w;
+    g.canvas_stride = (size_t)d.max_patch_w * (size_t)d.max_patch_h;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    g.o_canvas = up((size_t)d.batch * d.height * d.width * 3);
+    g.o_state = g.o_canvas + up((size_t)d.batch * g.canvas_stride * 4);
+    g.o_cov = g.o_state + up((size_t)d.batch * sizeof(ImgState));
+    g.o_flags = g.o_cov + up((size_t)d.batch * g.cov_stride * 4);
+    g.ws_total = g.o_flags + up((size_t)d.batch * d.height);
+    g.smem_plan = (((uint32_t)g.H + 1u) * 4u + 15u) & ~15u;
+    return true;
+}
+
+}  // namespace v7
+}  // namespace ssad
+
+size_t ssad_v7_workspace(const SsadBatchDesc& d) {
+    ssad::v7::Geo7 g;
+    if (!ssad::v7::make_geo7(d, g)) return 0;
+    return g.ws_total;
+}
+
+// returns SSAD_OK when launched, SSAD_EUNSUPPORTED when the caller should use another kernel
+int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
+                   const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
+                   SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    using namespace ssad::v7;
+    Geo7 g;
+    if (!make_geo7(d, g)) return SSAD_EUNSUPPORTED;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) || (d.src_pitch & 7) || (d.src_stride & 7)) return SSAD_EUNSUPPORTED;
+    if (g.smem_plan > 40u * 1024u) return SSAD_EUNSUPPORTED;
+    if ((long long)d.batch * g.nslab > 0x7FFFFFFFll) return SSAD_EUNSUPPORTED;
+    if (!workspace || workspace_bytes < g.ws_total) return SSAD_EWORKSPACE;
+    if (reinterpret_cast<uintptr_t>(workspace) & 255) return SSAD_EALIGN;
+    uint8_t* const ws = static_cast<uint8_t*>(workspace);
+    uint8_t* const xbuf = ws;
+    uint32_t* const canvas = reinterpret_cast<uint32_t*>(ws + g.o_canvas);
+    ImgState* const state = reinterpret_cast<ImgState*>(ws + g.o_state);
+    uint32_t* const cov = reinterpret_cast<uint32_t*>(ws + g.o_cov);
+    uint8_t* const flags = ws + g.o_flags;
+    const unsigned B = (unsigned)d.batch;
+    plan_v7_kernel<<<B, NT, g.smem_plan, stream>>>(d, g, params, mask_bits, state, cov, flags);
+    pass1_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, donor_bank, state, cov, flags, xbuf);
+    canvas_v7_kernel<<<B * (unsigned)g.ncanvas, NT, 0, stream>>>(d, g, params, src, donor_bank, state, cov, canvas);
+    finish_v7_kernel<<<B, NT, 0, stream>>>(d, g, state, y_out, debug);
+    pass2_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, state, cov, flags, xbuf, canvas, norm_lut, out_u8,
+                                                            out_norm);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ssad_set_cuda_error(e);
+    return SSAD_OK;
+}

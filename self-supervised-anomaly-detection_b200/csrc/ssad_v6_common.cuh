@@ -1,0 +1,640 @@
+// Device code shared by the v6 (one cluster per image) and v7 (streaming kernel pipeline) generator paths:
+// per-image plan and tables, 8-pixel-unit stages (tables, Saturation, luma / RGB sums), paste on the fly, the two unit loops.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ssad_device.cuh"
+#include "ssad_sm100.cuh"
+#include "ssad_unit8.cuh"
+
+namespace ssad {
+namespace v6 {
+
+using namespace u8x;
+
+constexpr int NT = 256;
+constexpr int NWARP = NT / 32;
+constexpr int MAXC = 8;
+// table after Saturation: index = bits(2^23 + t, rounded toward zero) - 0x4B000000 + TB_OFF.  t < 0 lands in the
+// binade below 2^23 (half steps): offsets down to -2 * 64; t < 255 * kSatMax above.  Valid for Saturation factors <= kSatMax.
+constexpr int TB_OFF = 128;
+constexpr int TB_SIZE = TB_OFF + 320;                  // t < 255 * kSatMax
+constexpr float kSatMax = 1.25f;
+
+struct Geom {
+    int H, W, C, rows_cta;
+    int upr, upr_shift;                 // units per row (log2 when a power of two, else -1)
+    uint32_t cov_pitch, cov_rows;       // coverage canvas: words per row, rows
+    uint32_t canvas_pitch;              // colour canvas (global): words per row
+    size_t canvas_stride, o_canvas, ws_total;   // words per image; workspace offsets / size in bytes
+    uint32_t o_rowpre, o_cov, o_flags, o_lut, total;
+};
+
+// one stage program: bytes -> bytes
+enum { PK_COPY = 0, PK_BYTELUT = 1, PK_SAT = 2 };
+enum { SA_UNPACK = 0, SA_LUT = 1 };
+enum { SB_PACK = 0, SB_CLAMP = 1, SB_LUT = 2 };
+struct Prog {
+    int32_t kind, sa, sb;
+    float fs;                           // Saturation factor
+};
+struct Tables {                         // shared memory, per program
+    uint32_t a[256];                    // SA_LUT: magic float (2^23 + run(v)) of the per-channel run ahead of Saturation
+    uint8_t ab[256];                    // PK_BYTELUT: run(v)
+    uint8_t b[TB_SIZE];                 // SB_LUT: run(clip(t)) of the per-channel run after Saturation
+};
+
+// per-image plan, one copy per CTA (shared memory)
+struct Plan {
+    int32_t y, npaste, n_coords, sim;
+    int32_t paste[5][2];
+    int32_t bw, bh;                     // canvas size: (pw, ph) polygon | (nw, nh) rotated scar
+    int32_t flat;
+    uint32_t flat_rgb[3];
+    int32_t avg_rgb[3];
+    float bf1, bf2;
+    int32_t nops, cpos, cmean;
+    int32_t ops[3];
+    float fac[3];
+    int32_t s_in_pre;                   // Saturation precedes Contrast: pass 1 stores its result
+    Prog pre, fin;                      // ops ahead of Contrast | what pass 2 still has to do
+    double cosine;
+};
+
+// ------------------------------------------------------------------ per-channel ops, scalar (table fill)
+__device__ __forceinline__ uint32_t op_brightness(uint32_t v, float f) {       // ImageEnhance.Brightness: blend(0, v, f)
+    const float m = magic_from_u8(v);
+    return magic_to_u8(f > 1.0f ? magic_brightness<true>(m, f) : magic_brightness<false>(m, f));
+}
+__device__ __forceinline__ uint32_t op_contrast(uint32_t v, float f, int mean) {  // ImageEnhance.Contrast: blend(mean, v, f)
+    const float m = magic_from_u8(v), mA = magic_from_u8((uint32_t)mean), aF = (float)mean;
+    return magic_to_u8(blend_needs_clip(f) ? magic_blend<true>(m, mA, aF, f) : magic_blend<false>(m, mA, aF, f));
+}
+// run of per-channel ops ops[i0 .. i1) applied to v
+__device__ __forceinline__ uint32_t run_ops(uint32_t v, const int32_t* ops, const float* fac, int i0, int i1, int mean) {
+    for (int i = i0; i < i1; ++i) v = (ops[i] == 0) ? op_brightness(v, fac[i]) : op_contrast(v, fac[i], mean);
+    return v;
+}
+
+// program for ops[i0 .. i1) (at most one Saturation inside) + its tables
+__device__ inline void build_prog(Prog& G, Tables& T, const int32_t* ops, const float* fac, int i0, int i1, int mean, int tid) {
+    int is = -1;
+    for (int i = i0; i < i1; ++i) if (ops[i] == 2) is = i;
+    if (i1 <= i0) { if (tid == 0) { G.kind = PK_COPY; G.sa = G.sb = 0; G.fs = 1.0f; } return; }
+    if (is < 0) {
+        if (tid == 0) { G.kind = PK_BYTELUT; G.sa = G.sb = 0; G.fs = 1.0f; }
+        for (int v = tid; v < 256; v += NT) T.ab[v] = (uint8_t)run_ops((uint32_t)v, ops, fac, i0, i1, mean);
+        return;
+    }
+    const float fs = fac[is];
+    const int sa = (is > i0) ? SA_LUT : SA_UNPACK;
+    const int sb = (is + 1 < i1) ? SB_LUT : SB_CLAMP;          // (the clamp form also serves factors <= 1)
+    if (tid == 0) { G.kind = PK_SAT; G.sa = sa; G.sb = sb; G.fs = fs; }
+    if (sa == SA_LUT)
+        for (int v = tid; v < 256; v += NT) T.a[v] = kMagicBits | run_ops((uint32_t)v, ops, fac, i0, is, mean);
+    if (sb == SB_LUT)
+        for (int j = tid; j < TB_SIZE; j += NT) {
+            const int t = j - TB_OFF;
+            const uint32_t v = (uint32_t)min(max(t, 0), 255);       // Blend.c clip (negative half steps -> 0)
+            T.b[j] = (uint8_t)run_ops(v, ops, fac, is + 1, i1, mean);
+        }
+}
+
+// ------------------------------------------------------------------ small helpers
+__device__ __forceinline__ void st_cluster_u32(const void* local_ptr, uint32_t rank, uint32_t v) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(rank));
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(remote), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ f32x2 fma2_rn(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
+// 24 bytes at p (any alignment) -> 6 words.  nc = read-only path (source images); plain loads for the x buffer.
+template <bool NC>
+__device__ __forceinline__ uint2 ld8(const uint2* q) {
+    if (NC) return __ldg(q);
+    return *q;
+}
+template <bool NC>
+__device__ __forceinline__ void load24(const uint8_t* __restrict__ p, uint32_t (&w)[6]) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint32_t mis = (uint32_t)(a & 7u);
+    const uint2* q = reinterpret_cast<const uint2*>(a - mis);
+    if (mis == 0) {
+        const uint2 A = ld8<NC>(q), B = ld8<NC>(q + 1), C = ld8<NC>(q + 2);
+        w[0] = A.x; w[1] = A.y; w[2] = B.x; w[3] = B.y; w[4] = C.x; w[5] = C.y;
+    } else {
+        const uint2 A = ld8<NC>(q), B = ld8<NC>(q + 1), C = ld8<NC>(q + 2), D = ld8<NC>(q + 3);
+        const uint32_t sh = (mis & 3u) * 8u;
+        if (mis < 4) {
+            w[0] = __funnelshift_r(A.x, A.y, sh); w[1] = __funnelshift_r(A.y, B.x, sh); w[2] = __funnelshift_r(B.x, B.y, sh);
+            w[3] = __funnelshift_r(B.y, C.x, sh); w[4] = __funnelshift_r(C.x, C.y, sh); w[5] = __funnelshift_r(C.y, D.x, sh);
+        } else {
+            w[0] = __funnelshift_r(A.y, B.x, sh); w[1] = __funnelshift_r(B.x, B.y, sh); w[2] = __funnelshift_r(B.y, C.x, sh);
+            w[3] = __funnelshift_r(C.x, C.y, sh); w[4] = __funnelshift_r(C.y, D.x, sh); w[5] = __funnelshift_r(D.x, D.y, sh);
+        }
+    }
+}
+
+// the same load split in two for software pipelining: raw 8-byte-aligned loads now, the byte shift later
+struct Raw { uint2 a, b, c, d; };
+__device__ __forceinline__ void ld_raw(const uint8_t* q /* 8-byte aligned */, bool four, bool nc, Raw& r) {
+    const uint2* p = reinterpret_cast<const uint2*>(q);
+    r.d = make_uint2(0u, 0u);
+    (void)nc;        // one flavour of load: the x buffer is written by this kernel, so no ld.global.nc
+    r.a = p[0]; r.b = p[1]; r.c = p[2]; if (four) r.d = p[3];
+}
+__device__ __forceinline__ void raw_to_words(const Raw& r, uint32_t mis, uint32_t (&w)[6]) {
+    if (mis == 0) {
+        w[0] = r.a.x; w[1] = r.a.y; w[2] = r.b.x; w[3] = r.b.y; w[4] = r.c.x; w[5] = r.c.y;
+    } else {
+        const uint32_t sh = (mis & 3u) * 8u;
+        if (mis < 4) {
+            w[0] = __funnelshift_r(r.a.x, r.a.y, sh); w[1] = __funnelshift_r(r.a.y, r.b.x, sh); w[2] = __funnelshift_r(r.b.x, r.b.y, sh);
+            w[3] = __funnelshift_r(r.b.y, r.c.x, sh); w[4] = __funnelshift_r(r.c.x, r.c.y, sh); w[5] = __funnelshift_r(r.c.y, r.d.x, sh);
+        } else {
+            w[0] = __funnelshift_r(r.a.y, r.b.x, sh); w[1] = __funnelshift_r(r.b.x, r.b.y, sh); w[2] = __funnelshift_r(r.b.y, r.c.x, sh);
+            w[3] = __funnelshift_r(r.c.x, r.c.y, sh); w[4] = __funnelshift_r(r.c.y, r.d.x, sh); w[5] = __funnelshift_r(r.d.x, r.d.y, sh);
+        }
+    }
+}
+
+// replace pixel PIX (0..7, compile time) of the unit's words
+template <int PIX>
+__device__ __forceinline__ void put_pixel(uint32_t (&w)[6], uint32_t r, uint32_t g, uint32_t b) {
+    constexpr int b0 = 3 * PIX, b1 = b0 + 1, b2 = b0 + 2;
+    constexpr uint32_t keep = 0x3210u;
+    w[b0 >> 2] = __byte_perm(w[b0 >> 2], r, (keep & ~(0xFu << (4 * (b0 & 3)))) | (4u << (4 * (b0 & 3))));
+    w[b1 >> 2] = __byte_perm(w[b1 >> 2], g, (keep & ~(0xFu << (4 * (b1 & 3)))) | (4u << (4 * (b1 & 3))));
+    w[b2 >> 2] = __byte_perm(w[b2 >> 2], b, (keep & ~(0xFu << (4 * (b2 & 3)))) | (4u << (4 * (b2 & 3))));
+}
+
+__device__ __forceinline__ void rgb_sums(const uint32_t (&w)[6], uint32_t (&s)[3]) {
+    #pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const uint32_t w0 = w[3 * q], w1 = w[3 * q + 1], w2 = w[3 * q + 2];
+        s[0] = __dp4a(w0, 0x01000001u, s[0]); s[0] = __dp4a(w1, 0x00010000u, s[0]); s[0] = __dp4a(w2, 0x00000100u, s[0]);
+        s[1] = __dp4a(w0, 0x00000100u, s[1]); s[1] = __dp4a(w1, 0x01000001u, s[1]); s[1] = __dp4a(w2, 0x00010000u, s[1]);
+        s[2] = __dp4a(w0, 0x00010000u, s[2]); s[2] = __dp4a(w1, 0x00000100u, s[2]); s[2] = __dp4a(w2, 0x01000001u, s[2]);
+    }
+}
+
+// sum of Convert.c's L over the 8 pixels of a unit, straight from the packed bytes:
+// L = (19595 R + 38470 G + 7471 B + 0x8000) >> 16 with two 16x8-bit dot products per pixel.
+__device__ __forceinline__ uint32_t dp2a_lo(uint32_t a16x2, uint32_t b8x4, uint32_t c) {
+    uint32_t d;
+    asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a16x2), "r"(b8x4), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t dp2a_hi(uint32_t a16x2, uint32_t b8x4, uint32_t c) {
+    uint32_t d;
+    asm("dp2a.hi.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a16x2), "r"(b8x4), "r"(c));
+    return d;
+}
+__device__ __forceinline__ void luma_words(const uint32_t (&w)[6], uint32_t (&L)[8]) {
+    constexpr uint32_t kRG = (38470u << 16) | 19595u, kB0 = 7471u;          // pixel at bytes 0,1,2 of a word
+    constexpr uint32_t k0R = (19595u << 16), kGB = (7471u << 16) | 38470u;  // pixel at bytes 1,2,3 of a word
+    #pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const uint32_t w0 = w[3 * q], w1 = w[3 * q + 1], w2 = w[3 * q + 2];
+        const uint32_t p1 = __byte_perm(w0, w1, 0x0543);     // pixel 1: byte 3 of w0, bytes 0,1 of w1
+        const uint32_t p2 = __byte_perm(w1, w2, 0x0432);     // pixel 2: bytes 2,3 of w1, byte 0 of w2
+        L[4 * q + 0] = dp2a_hi(kB0, w0, dp2a_lo(kRG, w0, 0x8000u)) >> 16;
+        L[4 * q + 1] = dp2a_hi(kB0, p1, dp2a_lo(kRG, p1, 0x8000u)) >> 16;
+        L[4 * q + 2] = dp2a_hi(kB0, p2, dp2a_lo(kRG, p2, 0x8000u)) >> 16;
+        L[4 * q + 3] = dp2a_hi(kGB, w2, dp2a_lo(k0R, w2, 0x8000u)) >> 16;
+    }
+}
+__device__ __forceinline__ uint32_t luma_sum_words(const uint32_t (&w)[6]) {
+    uint32_t L[8];
+    luma_words(w, L);
+    return ((L[0] + L[1]) + (L[2] + L[3])) + ((L[4] + L[5]) + (L[6] + L[7]));
+}
+// ... leaving out the pixels whose bit is set in `skip`
+__device__ __forceinline__ uint32_t luma_sum_words_skip(const uint32_t (&w)[6], uint32_t skip) {
+    uint32_t L[8];
+    luma_words(w, L);
+    uint32_t s = 0;
+    #pragma unroll
+    for (int p = 0; p < 8; ++p) s += ((skip >> p) & 1u) ? 0u : L[p];
+    return s;
+}
+
+// sum NV values over the CTA; result valid in every thread
+template <int NV>
+__device__ __forceinline__ void block_sum_vec(uint32_t (&v)[NV], uint32_t* red /* NWARP * 8 + 8 words */) {
+    #pragma unroll
+    for (int i = 0; i < NV; ++i)
+        for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xFFFFFFFFu, v[i], o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) {
+        #pragma unroll
+        for (int i = 0; i < NV; ++i) red[(threadIdx.x >> 5) * 8 + i] = v[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        uint32_t t = 0;
+        #pragma unroll
+        for (int w = 0; w < NWARP; ++w) t += red[w * 8 + threadIdx.x];
+        red[NWARP * 8 + threadIdx.x] = t;
+    }
+    __syncthreads();
+    #pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = red[NWARP * 8 + i];
+}
+
+// ------------------------------------------------------------------ donor / cut source, patch colours
+// donor / cut source of image b (datasets.py:225-228, 253): patch pixel (u, v) = donor window pixel (rl + u, rt + v)
+struct Donor {
+    const uint8_t* base;       // patch pixel (0, 0)
+    int pitch, u_hi, v_hi;     // u < u_hi, v < v_hi: inside the donor window and the donor image (PIL's crop pads with 0)
+};
+__device__ __forceinline__ Donor donor_of(const SsadBatchDesc& d, const uint8_t* src, const uint8_t* donor_bank, int b,
+                                          const SsadImageParams& P) {
+    const uint8_t* dimg = src + (size_t)b * d.src_stride;
+    int dpitch = (int)d.src_pitch, dH = d.src_height, dW = d.src_width;
+    if (P.donor_idx >= 0) {
+        dimg = donor_bank + (size_t)P.donor_idx * d.donor_stride;
+        dpitch = (int)d.donor_pitch; dH = d.donor_height; dW = d.donor_width;
+    }
+    const int rl = P.rect[0], rt = P.rect[1], pw = P.rect[2], ph = P.rect[3];
+    const int dox = P.donor_off[0], doy = P.donor_off[1];
+    Donor D;
+    D.pitch = dpitch;
+    D.u_hi = min(min(pw, d.donor_win_w - rl), dW - dox - rl);
+    D.v_hi = min(min(ph, d.donor_win_h - rt), dH - doy - rt);
+    D.base = dimg + (size_t)(doy + rt) * dpitch + (size_t)(dox + rl) * 3;
+    return D;
+}
+
+// colour of patch pixel (u, v) after the variant / similarity-brightness decisions (datasets.py:270-299)
+struct Colour {
+    int flat, sim;
+    uint32_t frgb[3];
+    float bf1, bf2;
+};
+__device__ __forceinline__ void patch_colour(const Colour& K, const Donor& dn, int u, int v, uint32_t& r, uint32_t& g, uint32_t& bl) {
+    if (K.flat) { r = K.frgb[0]; g = K.frgb[1]; bl = K.frgb[2]; return; }
+    r = g = bl = 0;
+    if (u < dn.u_hi && v < dn.v_hi) {
+        const uint8_t* q = dn.base + (size_t)v * dn.pitch + 3 * u;
+        r = __ldg(q); g = __ldg(q + 1); bl = __ldg(q + 2);
+    }
+    if (K.sim) {        // two successive ImageEnhance.Brightness, each re-quantised (datasets.py:298-299)
+        r = brightness_u8(brightness_u8(r, K.bf1), K.bf2);
+        g = brightness_u8(brightness_u8(g, K.bf1), K.bf2);
+        bl = brightness_u8(brightness_u8(bl, K.bf1), K.bf2);
+    }
+}
+
+// ------------------------------------------------------------------ paste on the fly
+// 8 coverage bits of canvas row `crow` starting at canvas x = u0 (u0 may be negative or run past bw: those bits are 0)
+__device__ __forceinline__ uint32_t cov_bits8(const uint32_t* __restrict__ crow, int u0, int pitch_words) {
+    const int lo = max(u0, 0);
+    const int wi = lo >> 5;
+    uint32_t a = crow[wi];
+    uint32_t b = (wi + 1 < pitch_words) ? crow[wi + 1] : 0u;
+    uint32_t bits = __funnelshift_r(a, b, lo & 31) & 0xFFu;          // bits for canvas x = lo .. lo + 7
+    return (u0 < 0) ? (bits << (-u0)) & 0xFFu : bits;                 // pixel PIX <-> canvas x = u0 + PIX
+}
+
+// ------------------------------------------------------------------ stages on 8-pixel units
+__device__ __forceinline__ uint32_t min_relu_s16x2(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("min.relu.s16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+// stage A: bytes -> magic floats, plain (PRMT) or through the table of the run ahead of Saturation
+template <int SA>
+__device__ __forceinline__ void stage_in(Unit8& u, const uint32_t (&w)[6], uint32_t ta /* smem address of Tables::a */) {
+    if (SA == SA_UNPACK) {
+        unit_unpack(u, make_uint2(w[0], w[1]), make_uint2(w[2], w[3]), make_uint2(w[4], w[5]));
+    } else {
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            #pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                const int b0 = 6 * k + ch, b1 = 6 * k + 3 + ch;
+                const uint32_t i0 = __byte_perm(w[b0 >> 2], 0, 0x4440 + (b0 & 3)), i1 = __byte_perm(w[b1 >> 2], 0, 0x4440 + (b1 & 3));
+                u.v[ch][k] = pack2(__uint_as_float(lds_u32(ta + i0 * 4u)), __uint_as_float(lds_u32(ta + i1 * 4u)));
+            }
+        }
+    }
+}
+
+// ImageEnhance.Color on a unit, result left unclipped as RZ(2^23 + t)
+__device__ __forceinline__ void unit_saturation_raw(Unit8& u, float f) {
+    const f32x2 F = pack2(f, f), MAG = pack2(kMagic, kMagic);
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float r0, r1, g0, g1, b0, b1;
+        unpack2(u.v[0][k], r0, r1); unpack2(u.v[1][k], g0, g1); unpack2(u.v[2][k], b0, b1);
+        const uint32_t a0 = luma_bits(__float_as_uint(r0), __float_as_uint(g0), __float_as_uint(b0));
+        const uint32_t a1 = luma_bits(__float_as_uint(r1), __float_as_uint(g1), __float_as_uint(b1));
+        // -(2^23 + L): bit pattern 0xCB0000LL
+        const f32x2 NML = pack2(__uint_as_float(__byte_perm(a0, 0xCB000000u, 0x7542)),
+                                __uint_as_float(__byte_perm(a1, 0xCB000000u, 0x7542)));
+        const f32x2 NLF = add2_rn(NML, MAG);                // -(float)L, exact
+        #pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            const f32x2 p = mul2_rn(F, add2_rn(u.v[ch][k], NML));     // alpha * (v - L)
+            f32x2 t;
+            asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(p), "l"(NLF));   // L + p (same rounding as Pillow's A + p)
+            u.v[ch][k] = add2_rz(t, MAG);
+        }
+    }
+}
+
+// stage B: magic floats -> bytes
+template <int SB>
+__device__ __forceinline__ void stage_out(const Unit8& u, uint32_t (&w)[6], uint32_t tbc /* smem address of Tables::b + TB_OFF - 0x4B000000 */) {
+    float m[24];
+    unit_scalars(u, m);
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const uint32_t q0 = __float_as_uint(m[4 * i]), q1 = __float_as_uint(m[4 * i + 1]);
+        const uint32_t q2 = __float_as_uint(m[4 * i + 2]), q3 = __float_as_uint(m[4 * i + 3]);
+        if (SB == SB_PACK) {
+            w[i] = __byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+        } else if (SB == SB_CLAMP) {
+            // low halves as s16: in range 0x00vv, above 0x01vv, negative 0xFFvv -> min(.., 255) then relu
+            const uint32_t lo = min_relu_s16x2(__byte_perm(q0, q1, 0x5410), 0x00FF00FFu);
+            const uint32_t hi = min_relu_s16x2(__byte_perm(q2, q3, 0x5410), 0x00FF00FFu);
+            w[i] = __byte_perm(lo, hi, 0x6420);
+        } else {
+            const uint32_t a = lds_u8(q0 + tbc), b = lds_u8(q1 + tbc), c = lds_u8(q2 + tbc), d = lds_u8(q3 + tbc);
+            w[i] = __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
+        }
+    }
+}
+
+// bytes -> bytes through one 256-entry table
+__device__ __forceinline__ void unit_bytelut(uint32_t (&w)[6], uint32_t tab /* smem address of Tables::ab */) {
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const uint32_t x = w[i];
+        const uint32_t a = lds_u8(tab + (x & 0xFFu)), b = lds_u8(tab + __byte_perm(x, 0, 0x4441));
+        const uint32_t c = lds_u8(tab + __byte_perm(x, 0, 0x4442)), d = lds_u8(tab + (x >> 24));
+        w[i] = __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
+    }
+}
+
+template <int SA, int SB>
+__device__ __forceinline__ void unit_sat_prog(uint32_t (&w)[6], float fs, uint32_t ta, uint32_t tbc) {
+    Unit8 u;
+    stage_in<SA>(u, w, ta);
+    unit_saturation_raw(u, fs);
+    stage_out<SB>(u, w, tbc);
+}
+
+// the same program on one pixel (paste colours, correction pass) -- identical float sequence
+__device__ __forceinline__ void pixel_prog(const Prog& G, const Tables& T, uint32_t& r, uint32_t& g, uint32_t& b) {
+    if (G.kind == PK_COPY) return;
+    if (G.kind == PK_BYTELUT) { r = T.ab[r]; g = T.ab[g]; b = T.ab[b]; return; }
+    float m[3];
+    if (G.sa == SA_LUT) { m[0] = __uint_as_float(T.a[r]); m[1] = __uint_as_float(T.a[g]); m[2] = __uint_as_float(T.a[b]); }
+    else { m[0] = magic_from_u8(r); m[1] = magic_from_u8(g); m[2] = magic_from_u8(b); }
+    const uint32_t acc = luma_bits(__float_as_uint(m[0]), __float_as_uint(m[1]), __float_as_uint(m[2]));
+    const float nml = __uint_as_float(__byte_perm(acc, 0xCB000000u, 0x7542));
+    const float nlf = __fadd_rn(nml, kMagic);
+    uint32_t q[3];
+    #pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float p = __fmul_rn(G.fs, __fadd_rn(m[c], nml));
+        q[c] = __float_as_uint(__fadd_rz(__fsub_rn(p, nlf), kMagic));
+    }
+    #pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const int t = (int)(q[c] - kMagicBits);
+        if (G.sb == SB_LUT) q[c] = T.b[t + TB_OFF];
+        else q[c] = (uint32_t)min(max(t, 0), 255);
+    }
+    r = q[0]; g = q[1]; b = q[2];
+}
+
+// program kinds the unit loops are specialised for
+enum { LK_COPY = 0, LK_BYTELUT = 1, LK_SAT_UC = 2, LK_SAT_UL = 3, LK_SAT_LC = 4, LK_SAT_LL = 5 };
+__device__ __forceinline__ int loop_kind(const Prog& G) {
+    if (G.kind == PK_COPY) return LK_COPY;
+    if (G.kind == PK_BYTELUT) return LK_BYTELUT;
+    return LK_SAT_UC + (G.sa == SA_LUT ? 2 : 0) + (G.sb == SB_LUT ? 1 : 0);
+}
+struct ProgRegs {              // a program's constants in registers
+    float fs;
+    uint32_t ta, tab, tbc;     // shared-memory addresses: Tables::a, Tables::ab, Tables::b + TB_OFF - 0x4B000000
+};
+template <int LK>
+__device__ __forceinline__ void apply_prog(uint32_t (&w)[6], const ProgRegs& R) {
+    if (LK == LK_COPY) return;
+    if (LK == LK_BYTELUT) { unit_bytelut(w, R.tab); return; }
+    if (LK == LK_SAT_UC) unit_sat_prog<SA_UNPACK, SB_CLAMP>(w, R.fs, R.ta, R.tbc);
+    if (LK == LK_SAT_UL) unit_sat_prog<SA_UNPACK, SB_LUT>(w, R.fs, R.ta, R.tbc);
+    if (LK == LK_SAT_LC) unit_sat_prog<SA_LUT, SB_CLAMP>(w, R.fs, R.ta, R.tbc);
+    if (LK == LK_SAT_LL) unit_sat_prog<SA_LUT, SB_LUT>(w, R.fs, R.ta, R.tbc);
+}
+
+struct Boxes {                 // paste geometry of one image, in registers inside the unit loops
+    const uint32_t* cov;       // coverage bit rows of the canvas (shared memory)
+    const uint32_t* canvas;    // packed (r, g, b, L) per canvas pixel (global, written by this CTA)
+    int pitch, cpitch, bw, bh, npaste;
+};
+
+// union of the coverage of all pastes over the 8 pixels of a unit (pass 1: those pixels are replaced later)
+__device__ __forceinline__ uint32_t covered_bits8(const Plan& D, const Boxes& B, uint32_t rowflag, int yy, int x0) {
+    uint32_t m = 0;
+    for (int k = 0; k < B.npaste; ++k) {
+        if (!((rowflag >> k) & 1u)) continue;
+        const int u0 = x0 - D.paste[k][0], v = yy - D.paste[k][1];
+        if (u0 + 8 <= 0 || u0 >= B.bw) continue;
+        m |= cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
+    }
+    return m;
+}
+
+// replace pixel PIX of the unit by the (r, g, b) bytes of a packed canvas word
+template <int PIX>
+__device__ __forceinline__ void put_pixel_c(uint32_t (&w)[6], uint32_t c) {
+    constexpr int b0 = 3 * PIX, b1 = b0 + 1, b2 = b0 + 2;
+    constexpr uint32_t keep = 0x3210u;
+    w[b0 >> 2] = __byte_perm(w[b0 >> 2], c, (keep & ~(0xFu << (4 * (b0 & 3)))) | (4u << (4 * (b0 & 3))));
+    w[b1 >> 2] = __byte_perm(w[b1 >> 2], c, (keep & ~(0xFu << (4 * (b1 & 3)))) | (5u << (4 * (b1 & 3))));
+    w[b2 >> 2] = __byte_perm(w[b2 >> 2], c, (keep & ~(0xFu << (4 * (b2 & 3)))) | (6u << (4 * (b2 & 3))));
+}
+
+// paste_patch / scar pastes (dataset_generator.py:268-275, datasets.py:340-355) applied to the 8 pixels of a unit:
+// covered pixels take the canvas colour; pastes in order, later ones overwrite earlier ones
+__device__ __forceinline__ void paste_unit(const Plan& D, const Boxes& B, uint32_t rowflag, int yy, int x0, uint32_t (&w)[6]) {
+    for (int k = 0; k < B.npaste; ++k) {
+        if (!((rowflag >> k) & 1u)) continue;
+        const int u0 = x0 - D.paste[k][0], v = yy - D.paste[k][1];
+        if (u0 + 8 <= 0 || u0 >= B.bw) continue;
+        const uint32_t bits = cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
+        if (!bits) continue;
+        const uint32_t* crow = B.canvas + (ptrdiff_t)v * B.cpitch + u0;
+        #define SSAD_PASTE(PIX) if (bits & (1u << PIX)) put_pixel_c<PIX>(w, crow[PIX]);
+        SSAD_PASTE(0) SSAD_PASTE(1) SSAD_PASTE(2) SSAD_PASTE(3) SSAD_PASTE(4) SSAD_PASTE(5) SSAD_PASTE(6) SSAD_PASTE(7)
+        #undef SSAD_PASTE
+    }
+}
+
+// u in [0, n) with 0 <= base + u * step < limit (int64: no wrap) -> [lo, hi] inclusive (empty: lo > hi)
+__device__ __forceinline__ long long floor_div(long long a, long long b) {     // b > 0
+    long long q = a / b;
+    return (a % b < 0) ? q - 1 : q;
+}
+__device__ __forceinline__ void affine_span(long long base, long long step, long long limit, int& lo, int& hi) {
+    if (step == 0) { if (!(base >= 0 && base < limit)) { lo = 1; hi = 0; } return; }
+    long long l, h;
+    if (step > 0) { l = -floor_div(base, step); h = floor_div(limit - 1 - base, step); }      // ceil(-base / step)
+    else { const long long sp = -step; h = floor_div(base, sp); l = floor_div(base - limit, sp) + 1; }
+    if (l > lo) lo = (int)min(l, (long long)0x3FFFFFFF);
+    if (h < hi) hi = (int)max(h, (long long)-1);
+}
+
+// ------------------------------------------------------------------ the unit loops
+// A CTA's slab = rows [r0, r0 + nrows) x upr units; thread t takes units t, t + NT, ... (row-major).
+struct Slab {
+    int r0, nunits, upr, tid;
+    int dr, dc;                // NT units further = dr rows and dc units (with one carry at most)
+    int rr0, cu0;              // this thread's first unit
+};
+__device__ __forceinline__ Slab make_slab(int r0, int nunits, int upr, int tid) {
+    Slab S;
+    S.r0 = r0; S.nunits = nunits; S.upr = upr; S.tid = tid;
+    S.dr = NT / upr; S.dc = NT - S.dr * upr;
+    S.rr0 = tid / upr; S.cu0 = tid - S.rr0 * upr;
+    return S;
+}
+// rr / cu = row / unit-in-row of the current unit; lin = its dense index (rr * upr + cu = t, t + NT, ...)
+#define SSAD_SLAB_LOOP(S)                                                                                     \
+    for (int lin = (S).tid, rr = (S).rr0, cu = (S).cu0; lin < (S).nunits;                                     \
+         lin += NT, rr += (S).dr, cu += (S).dc, rr += (cu >= (S).upr) ? 1 : 0, cu -= (cu >= (S).upr) ? (S).upr : 0)
+
+// Software-pipelined walk over a thread's units: the loads of the next unit are issued before the current one is
+// processed.  Inside the body: w[6] = the unit's bytes, lin = its dense index in the slab, rr = its row in the slab,
+// yy / x0 = its image row / first pixel.  (Rows are 8-byte periodic: pitch % 8 == 0, so `mis` is one value per slab.)
+#define SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc)                                                          \
+    const uint32_t mis_ = (uint32_t)(reinterpret_cast<uintptr_t>(in0) & 7u);                                  \
+    const uint8_t* const in0a_ = (in0) - mis_;                                                                \
+    Raw nx_;                                                                                                  \
+    int nlin_ = (S).tid, nrr_ = (S).rr0, ncu_ = (S).cu0;                                                      \
+    if (nlin_ < (S).nunits) ld_raw(in0a_ + nrr_ * (in_pitch) + ncu_ * 24, mis_ != 0, in_nc, nx_);             \
+    while (nlin_ < (S).nunits)
+#define SSAD_PIPELINED_STEP(S, in_pitch, in_nc)                                                               \
+    const Raw cur_ = nx_;                                                                                     \
+    const int lin = nlin_, rr = nrr_, yy = (S).r0 + nrr_, x0 = ncu_ * 8;                                      \
+    nlin_ += NT; nrr_ += (S).dr; ncu_ += (S).dc;                                                              \
+    if (ncu_ >= (S).upr) { ncu_ -= (S).upr; ++nrr_; }                                                         \
+    if (nlin_ < (S).nunits) ld_raw(in0a_ + nrr_ * (in_pitch) + ncu_ * 24, mis_ != 0, in_nc, nx_);             \
+    uint32_t w[6];                                                                                            \
+    raw_to_words(cur_, mis_, w);
+
+// pass 1: RGB sums of x; the program ahead of Contrast; sum of L over the pixels no paste replaces; keep the bytes
+template <int LK>
+__device__ __forceinline__ void pass1_loop(const Slab& S, const uint8_t* in, int in_pitch, bool in_nc, uint8_t* xb, int xpitch,
+                                           bool store, bool need_rgb, bool need_luma, const ProgRegs& R, const Plan& D,
+                                           const Boxes& BX, const uint8_t* flags, uint32_t (&acc)[7]) {
+    uint32_t s0 = 0, s1 = 0, s2 = 0, sl = 0;
+    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
+    uint8_t* const xb0 = xb + (size_t)S.r0 * xpitch;           // dense rows: unit `lin` of the slab sits at lin * 24
+    SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc) {
+        SSAD_PIPELINED_STEP(S, in_pitch, in_nc)
+        if (need_rgb) {
+            uint32_t s[3] = {s0, s1, s2};
+            rgb_sums(w, s);
+            s0 = s[0]; s1 = s[1]; s2 = s[2];
+        }
+        if (need_luma) {
+            apply_prog<LK>(w, R);
+            // sum of L of what Contrast will see, minus the pixels a paste replaces (their L comes from the canvas)
+            const uint32_t rf = D.y != 0 ? (uint32_t)flags[rr] : 0u;
+            const uint32_t skip = rf ? covered_bits8(D, BX, rf, yy, x0) : 0u;
+            sl += skip ? luma_sum_words_skip(w, skip) : luma_sum_words(w);
+            if (store) {                        // the x buffer keeps pre(x): pass 2 starts from there
+                uint2* const o = reinterpret_cast<uint2*>(xb0 + lin * 24);
+                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+            }
+        }
+    }
+    acc[0] += s0; acc[1] += s1; acc[2] += s2; acc[3] += sl;
+}
+
+// pass 2: paste on the fly, the rest of the chain, stores
+template <int LK>
+__device__ __forceinline__ void pass2_loop(const Slab& S, const uint8_t* in, int in_pitch, bool in_nc, const ProgRegs& R,
+                                           const Plan& D, const Boxes& BX, const uint8_t* flags, int W, int npix,
+                                           uint8_t* obase, void* onorm, int norm_dtype, const uint8_t* lutbase) {
+    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
+    const size_t pbase = (size_t)S.r0 * W;                     // dense outputs: unit `lin` starts at pixel pbase + lin * 8
+    SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc) {
+        SSAD_PIPELINED_STEP(S, in_pitch, in_nc)
+        if (D.y != 0) {
+            const uint32_t rf = flags[rr];
+            if (rf) paste_unit(D, BX, rf, yy, x0, w);
+        }
+        apply_prog<LK>(w, R);
+        const size_t p0 = pbase + (size_t)lin * 8;
+        if (obase) {
+            uint2* o = reinterpret_cast<uint2*>(obase + p0 * 3);
+            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+        }
+        if (onorm) {
+            // ToTensor + Normalize (datasets.py:392-393): exact table per channel, NCHW planes
+            uint32_t e[24];
+            #pragma unroll
+            for (int i = 0; i < 24; ++i) e[i] = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;      // byte i = pixel i / 3, channel i % 3
+            if (norm_dtype == SSAD_NORM_F32) {
+                const float* lut = reinterpret_cast<const float*>(lutbase);
+                float* ob = reinterpret_cast<float*>(onorm);
+                #pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    float4* o = reinterpret_cast<float4*>(ob + (size_t)ch * npix + p0);
+                    #pragma unroll
+                    for (int qq = 0; qq < 2; ++qq) {
+                        float4 v;
+                        v.x = lut[ch * 256 + e[3 * (4 * qq + 0) + ch]];
+                        v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
+                        v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
+                        v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
+                        o[qq] = v;
+                    }
+                }
+            } else {
+                const uint16_t* lut = reinterpret_cast<const uint16_t*>(lutbase);
+                uint16_t* ob = reinterpret_cast<uint16_t*>(onorm);
+                #pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    uint32_t wv[4];
+                    #pragma unroll
+                    for (int qq = 0; qq < 4; ++qq) {
+                        uint32_t lo = lut[ch * 256 + e[3 * (2 * qq) + ch]];
+                        uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
+                        wv[qq] = lo | (hi << 16);
+                    }
+                    *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+                }
+            }
+        }
+    }
+}
+
+}  // namespace v6
+}  // namespace ssad
+

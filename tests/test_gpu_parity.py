@@ -58,7 +58,7 @@ def test_generate_big_images_match_oracle(name):
     _check_against_oracle(name, 5)
 
 
-@pytest.mark.parametrize("kernel", ["v6", "v5", "v4", "v3", "cluster", "generic"])
+@pytest.mark.parametrize("kernel", ["v7", "v6", "v5", "v4", "v3", "cluster", "generic"])
 @pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture"])
 def test_every_kernel_variant_matches_oracle(name, kernel, monkeypatch):
     _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": kernel})
@@ -80,6 +80,14 @@ def test_v5_cluster_sizes_match_oracle(name, csize, monkeypatch):
 @pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
 def test_v6_cluster_sizes_match_oracle(name, csize, monkeypatch):
     _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v6", "SSAD_V6_C": csize})
+
+
+@pytest.mark.parametrize("env", [{"SSAD_V7_NOFAST": "1"}, {"SSAD_V7_UPT": "3"}, {"SSAD_V7_NC": "1"}, {"SSAD_V7_NC": "16"}])
+@pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
+def test_v7_loop_and_grid_variants_match_oracle(name, env, monkeypatch):
+    """v7's general unit loops (the fast ones need a power-of-two width and whole slabs), odd slab sizes, and the
+    number of CTAs that share an image's patch canvas."""
+    _check_against_oracle(name, 12, monkeypatch, dict(env, SSAD_KERNEL="v7"))
 
 
 @pytest.mark.parametrize("name", S.ALL)

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Summarise an .ncu-rep (first profiled launch): key raw metrics, SASS opcode mix, and the CUDA source
-lines ranked by instructions executed / stall samples.   usage: ncu_summary.py file.ncu-rep [topN]"""
+lines ranked by instructions executed / stall samples.   usage: ncu_summary.py file.ncu-rep [topN [launch_index]]"""
 import collections
 import csv
 import subprocess
@@ -8,7 +8,8 @@ import sys
 
 rep = sys.argv[1]
 topn = int(sys.argv[2]) if len(sys.argv) > 2 else 30
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+skip = ["--launch-skip", sys.argv[3], "--launch-count", "1"] if len(sys.argv) > 3 else []   # which profiled launch
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"] + skip, capture_output=True, text=True).stdout
 r = list(csv.reader(raw.splitlines()))
 h, units, v = r[0], r[1], r[2]
 keys = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
@@ -32,7 +33,7 @@ for i, k in enumerate(h):
             pass
         print(f"{k:95s} {units[i]:12s} {v[i]}")
 
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"],
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"] + skip,
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(src.splitlines()))
 ops, smp = collections.Counter(), collections.Counter()
