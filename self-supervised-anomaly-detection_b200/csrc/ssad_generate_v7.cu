@@ -3,19 +3,23 @@
 // v6 runs the whole of PretextTaskDataset.__getitem__ (datasets.py:209-394) for one image inside one cluster; ncu shows
 // that kernel issue-bound with 39 % of every CTA's life spent in its short serial phases (geometry, decisions, canvas,
 // tables) and a 1.7-wave tail.  Here each phase is its own grid, sized for what it does, and the two passes over the
-// pixels are pure streaming kernels (thousands of small CTAs, every warp streaming all the time):
+// pixels are pure streaming kernels -- no paste, mask or flag logic inside their loops:
 //
 //   plan     CTA / image      parameters -> centres -> container clamp -> paste boxes; rect2poly / rotated-scar coverage
-//                             bit rows; rows-with-a-paste flags; the jitter plan and the tables of the ops ahead of
-//                             Contrast.  Reads the mask bits, no pixel.
-//   pass 1   CTA / slab       (RandomAffine gather) ; RGB sums of x ; ops ahead of Contrast ; sum of L of the unpasted
-//                             pixels ; RGB sums of the would-be cut  -> atomicAdd into the image's accumulators
-//   canvas   NC CTAs / image  cosine > 0.99 decision, flat colours; the patch canvas (packed RGB + L); sum of L of
-//                             the pasted pixels -> atomicAdd
+//                             bit rows; the jitter plan and the tables of the ops ahead of Contrast; the image joins the
+//                             work lists of the two passes, one list per loop kind.  Reads the mask bits, no pixel.
+//   pass 1   CTA / slab       (RandomAffine gather) ; RGB sums of x ; ops ahead of Contrast ; sum of L of EVERY pixel ;
+//                             RGB sums of the would-be cut -> atomicAdd into the image's accumulators.  Leaves in the
+//                             x buffer what pass 2 starts from: pre(x) when Saturation precedes Contrast, else x itself
+//                             when something will be pasted onto it.
+//   canvas   NC CTAs / image  cosine > 0.99 decision, flat colours; the patch canvas (packed RGB + L); the pastes written
+//                             INTO the x buffer, later pastes over earlier ones; sum of L(new) - L(old) -> atomicAdd
 //   finish   CTA / image      Contrast mean -> tables of Contrast and the ops after it; labels, debug records
-//   pass 2   CTA / slab       re-read the slab (L2), paste on the fly, rest of the chain, stores
+//   pass 2   CTA / slab       x buffer (or the source when nothing touched it) -> rest of the chain -> stores
 //
-// The per-image state (plan, tables, accumulators), the coverage rows and the row flags live in the caller's workspace.
+// CTAs of the passes are ordered by loop kind (the lists), so an SM runs one or two loop bodies at a time: the six
+// specialised bodies together are far larger than the instruction caches.
+// The per-image state (plan, tables, accumulators), the coverage rows and the lists live in the caller's workspace.
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -33,17 +37,22 @@ namespace v7 {
 using namespace v6;
 using namespace u8x;
 
+constexpr int NKIND = 6;         // LK_COPY .. LK_SAT_LL
+
 struct ImgState {                // per image, global memory
     Plan D;
-    uint32_t acc[8];             // 0-2 RGB of x, 3 sum of L (unpasted), 4-6 RGB of the cut, 7 sum of L (pasted)
+    uint32_t acc[8];             // 0-2 RGB of x, 3 sum of L of pre(x), 4-6 RGB of the cut, 7 sum of L(new) - L(old) over the pastes
     Tables TP, TF;
+};
+struct Sched {                   // work lists of the two passes: images per loop kind (zeroed before the plan kernel)
+    uint32_t count[2][8];
 };
 
 struct Geo7 {
-    int H, W, upr, rows_slab, nslab, ncanvas;
+    int H, W, upr, rows_slab, nslab, ncanvas, batch;
     uint32_t cov_pitch, cov_rows, canvas_pitch;
     size_t canvas_stride, cov_stride;                       // words per image
-    size_t o_canvas, o_state, o_cov, o_flags, ws_total;     // byte offsets in the workspace (x buffer at 0)
+    size_t o_canvas, o_state, o_cov, o_sched, o_order, ws_total;   // byte offsets in the workspace (x buffer at 0)
     int fast;                                               // NT % upr == 0 and every slab holds NT * UPT units
     uint32_t smem_plan;                                     // dynamic shared memory of the plan kernel (row prefix)
 };
@@ -56,12 +65,32 @@ __device__ __forceinline__ void copy_words(T* dst, const T* src, int tid) {
     for (int i = tid; i < (int)(sizeof(T) / 4); i += NT) d[i] = s[i];
 }
 
+// loop kind of the program build_prog makes of ops[i0 .. i1)
+__device__ __forceinline__ int kind_of_ops(const int32_t* ops, int i0, int i1) {
+    if (i1 <= i0) return LK_COPY;
+    int is = -1;
+    for (int i = i0; i < i1; ++i) if (ops[i] == 2) is = i;
+    if (is < 0) return LK_BYTELUT;
+    return LK_SAT_UC + ((is > i0) ? 2 : 0) + ((is + 1 < i1) ? 1 : 0);
+}
 
-// ------------------------------------------------------------------ fast unit loops
-// Geometry of the fast path: NT % upr == 0 (a thread keeps its unit column: x0, the byte alignment and the set of
-// pastes that can touch the column are loop invariants; pointers advance by constants) and the slab holds exactly
-// NT * UPT units (no bounds test).  Every thread announces all its units to the L2 up front (prefetch.global.L2), then
-// keeps one unit of loads in flight in registers.
+// image and loop kind of the j-th image of pass p's lists
+__device__ __forceinline__ int sched_lookup(const Sched* sc, const int32_t* order, int batch, int p, uint32_t j, int& kind) {
+    uint32_t c = 0;
+    #pragma unroll
+    for (int k = 0; k < NKIND; ++k) {
+        const uint32_t n = sc->count[p][k];
+        if (j < c + n) { kind = k; return order[((size_t)p * NKIND + k) * batch + (j - c)]; }
+        c += n;
+    }
+    kind = -1;
+    return -1;
+}
+
+// ------------------------------------------------------------------ unit loops
+// Fast path: NT % upr == 0 (a thread keeps its unit column: the byte alignment is a loop invariant, pointers advance by
+// constants) and the slab holds exactly NT * UPT units (no bounds test).  Every thread announces all its units to the
+// L2 up front (prefetch.global.L2), then keeps one unit of loads in flight in registers.
 constexpr int UPT = 8;
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -80,168 +109,184 @@ __device__ __forceinline__ uint32_t luma_sum_fast(const uint32_t (&w)[6]) {
     }
     return s;
 }
-__device__ __forceinline__ uint32_t luma_sum_fast_skip(const uint32_t (&w)[6], uint32_t skip) {
-    uint32_t L[8];
-    luma_words(w, L);
-    uint32_t s = 0;
-    #pragma unroll
-    for (int p = 0; p < 8; ++p) s += ((skip >> p) & 1u) ? 0u : L[p];
-    return s;
+
+__device__ __forceinline__ void store24(uint8_t* p, const uint32_t (&w)[6]) {
+    uint2* const o = reinterpret_cast<uint2*>(p);
+    o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
 }
 
-struct FastCol {                // a thread's unit column
-    int rr0, cu, x0, dr;
-    uint32_t mis, colhit;
-};
-__device__ __forceinline__ FastCol fast_col(const Plan& D, int upr, int tid) {
-    FastCol F;
-    F.rr0 = tid / upr; F.cu = tid - F.rr0 * upr; F.x0 = F.cu * 8; F.dr = NT / upr;
-    F.mis = 0; F.colhit = 0;
-    if (D.y != 0)
-        for (int k = 0; k < D.npaste; ++k) {
-            const int u0 = F.x0 - D.paste[k][0];
-            if (u0 + 8 > 0 && u0 < D.bw) F.colhit |= 1u << k;
+// what pass 1 does to one unit: sums of x, (store x), program ahead of Contrast, sum of L, (store pre(x))
+template <int LK>
+__device__ __forceinline__ void pass1_unit(uint32_t (&w)[6], uint8_t* o, bool store_raw, bool store_pre, bool need_rgb,
+                                           bool need_luma, const ProgRegs& R, uint32_t& s0, uint32_t& s1, uint32_t& s2,
+                                           uint32_t& sl) {
+    if (need_rgb) {
+        uint32_t s[3] = {s0, s1, s2};
+        rgb_sums(w, s);
+        s0 = s[0]; s1 = s[1]; s2 = s[2];
+    }
+    if (store_raw) store24(o, w);
+    if (need_luma) {
+        apply_prog<LK>(w, R);
+        sl += luma_sum_fast(w);
+        if (store_pre) store24(o, w);
+    }
+}
+
+// ToTensor + Normalize (datasets.py:392-393) of one unit: exact table per channel, NCHW planes
+__device__ __forceinline__ void store_norm(const uint32_t (&w)[6], void* onorm, int norm_dtype, const uint8_t* lutbase, int npix,
+                                           size_t p0) {
+    uint32_t e[24];
+    #pragma unroll
+    for (int i = 0; i < 24; ++i) e[i] = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;      // byte i = pixel i / 3, channel i % 3
+    if (norm_dtype == SSAD_NORM_F32) {
+        const float* lut = reinterpret_cast<const float*>(lutbase);
+        float* ob = reinterpret_cast<float*>(onorm);
+        #pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            float4* o = reinterpret_cast<float4*>(ob + (size_t)ch * npix + p0);
+            #pragma unroll
+            for (int qq = 0; qq < 2; ++qq) {
+                float4 v;
+                v.x = lut[ch * 256 + e[3 * (4 * qq + 0) + ch]];
+                v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
+                v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
+                v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
+                o[qq] = v;
+            }
         }
+    } else {
+        const uint16_t* lut = reinterpret_cast<const uint16_t*>(lutbase);
+        uint16_t* ob = reinterpret_cast<uint16_t*>(onorm);
+        #pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            uint32_t wv[4];
+            #pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+                uint32_t lo = lut[ch * 256 + e[3 * (2 * qq) + ch]];
+                uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
+                wv[qq] = lo | (hi << 16);
+            }
+            *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        }
+    }
+}
+
+struct FastCol {                // a thread's unit column in the fast path
+    const uint8_t* ip;          // 8-byte aligned load address of the current unit
+    size_t istep;
+    int rr0, cu, dr;
+    uint32_t mis;
+};
+__device__ __forceinline__ FastCol fast_col(const uint8_t* in0, int in_pitch, int upr, int tid) {
+    FastCol F;
+    F.rr0 = tid / upr; F.cu = tid - F.rr0 * upr; F.dr = NT / upr;
+    const uint8_t* ip = in0 + (size_t)F.rr0 * in_pitch + F.cu * 24;
+    F.mis = (uint32_t)(reinterpret_cast<uintptr_t>(ip) & 7u);
+    F.ip = ip - F.mis;
+    F.istep = (size_t)F.dr * in_pitch;
+    #pragma unroll
+    for (int it = 1; it < UPT; ++it) prefetch_l2(F.ip + it * F.istep + 16);
     return F;
 }
 
 template <int LK>
 __device__ __forceinline__ void pass1_fast(const uint8_t* in0 /* slab row 0 */, int in_pitch, uint8_t* xb0 /* slab row 0 */,
-                                           int xpitch, bool store, bool need_rgb, bool need_luma, const ProgRegs& R,
-                                           const Plan& D, const Boxes& BX, const uint8_t* flags, int r0, int upr, int tid,
-                                           uint32_t (&acc)[7]) {
-    FastCol F = fast_col(D, upr, tid);
-    const uint8_t* ip = in0 + (size_t)F.rr0 * in_pitch + F.cu * 24;
-    F.mis = (uint32_t)(reinterpret_cast<uintptr_t>(ip) & 7u);
-    ip -= F.mis;
-    const size_t istep = (size_t)F.dr * in_pitch;
+                                           int xpitch, bool store_raw, bool store_pre, bool need_rgb, bool need_luma,
+                                           const ProgRegs& R, int upr, int tid, uint32_t (&acc)[7]) {
+    FastCol F = fast_col(in0, in_pitch, upr, tid);
     uint8_t* op = xb0 + (size_t)F.rr0 * xpitch + F.cu * 24;
     const size_t ostep = (size_t)F.dr * xpitch;
-    #pragma unroll
-    for (int it = 1; it < UPT; ++it) prefetch_l2(ip + it * istep + 16);
     uint32_t s0 = 0, s1 = 0, s2 = 0, sl = 0;
     const bool four = F.mis != 0;
     Raw nx;
-    ld_raw(ip, four, false, nx);
-    int rr = F.rr0;
-    uint32_t fnx = F.colhit ? (uint32_t)flags[rr] : 0u;
+    ld_raw(F.ip, four, false, nx);
     #pragma unroll 2
     for (int it = 0; it < UPT; ++it) {
         const Raw cur = nx;
-        const uint32_t rf = fnx & F.colhit;
-        const int yy = r0 + rr;
-        ip += istep; rr += F.dr;
-        if (it + 1 < UPT) {
-            ld_raw(ip, four, false, nx);
-            if (F.colhit) fnx = flags[rr];
-        }
+        F.ip += F.istep;
+        if (it + 1 < UPT) ld_raw(F.ip, four, false, nx);
         uint32_t w[6];
         raw_to_words(cur, F.mis, w);
-        if (need_rgb) {
-            uint32_t s[3] = {s0, s1, s2};
-            rgb_sums(w, s);
-            s0 = s[0]; s1 = s[1]; s2 = s[2];
-        }
-        if (need_luma) {
-            apply_prog<LK>(w, R);
-            // sum of L of what Contrast will see, minus the pixels a paste replaces (their L comes from the canvas)
-            const uint32_t skip = rf ? covered_bits8(D, BX, rf, yy, F.x0) : 0u;
-            sl += skip ? luma_sum_fast_skip(w, skip) : luma_sum_fast(w);
-            if (store) {                        // the x buffer keeps pre(x): pass 2 starts from there
-                uint2* const o = reinterpret_cast<uint2*>(op);
-                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
-            }
-        }
+        pass1_unit<LK>(w, op, store_raw, store_pre, need_rgb, need_luma, R, s0, s1, s2, sl);
         op += ostep;
     }
     acc[0] += s0; acc[1] += s1; acc[2] += s2; acc[3] += sl;
 }
 
 template <int LK>
-__device__ __forceinline__ void pass2_fast(const uint8_t* in0 /* slab row 0 */, int in_pitch, const ProgRegs& R, const Plan& D,
-                                           const Boxes& BX, const uint8_t* flags, int r0, int upr, int tid, int W, int npix,
-                                           uint8_t* obase, void* onorm, int norm_dtype, const uint8_t* lutbase) {
-    FastCol F = fast_col(D, upr, tid);
-    const uint8_t* ip = in0 + (size_t)F.rr0 * in_pitch + F.cu * 24;
-    F.mis = (uint32_t)(reinterpret_cast<uintptr_t>(ip) & 7u);
-    ip -= F.mis;
-    const size_t istep = (size_t)F.dr * in_pitch;
-    int p0 = (r0 + F.rr0) * W + F.x0;                      // first pixel of the current unit inside the image
+__device__ __forceinline__ void pass2_fast(const uint8_t* in0 /* slab row 0 */, int in_pitch, const ProgRegs& R, int r0, int upr,
+                                           int tid, int W, int npix, uint8_t* obase, void* onorm, int norm_dtype,
+                                           const uint8_t* lutbase) {
+    FastCol F = fast_col(in0, in_pitch, upr, tid);
+    int p0 = (r0 + F.rr0) * W + F.cu * 8;                  // first pixel of the current unit inside the image
     const int pstep = F.dr * W;
     uint8_t* op = obase ? obase + (size_t)p0 * 3 : nullptr;
     const size_t ostep = (size_t)pstep * 3;
-    #pragma unroll
-    for (int it = 1; it < UPT; ++it) prefetch_l2(ip + it * istep + 16);
     const bool four = F.mis != 0;
     Raw nx;
-    ld_raw(ip, four, false, nx);
-    int rr = F.rr0;
-    uint32_t fnx = F.colhit ? (uint32_t)flags[rr] : 0u;
+    ld_raw(F.ip, four, false, nx);
     #pragma unroll 2
     for (int it = 0; it < UPT; ++it) {
         const Raw cur = nx;
-        const uint32_t rf = fnx & F.colhit;
-        const int yy = r0 + rr;
-        ip += istep; rr += F.dr;
-        if (it + 1 < UPT) {
-            ld_raw(ip, four, false, nx);
-            if (F.colhit) fnx = flags[rr];
-        }
+        F.ip += F.istep;
+        if (it + 1 < UPT) ld_raw(F.ip, four, false, nx);
         uint32_t w[6];
         raw_to_words(cur, F.mis, w);
-        if (rf) paste_unit(D, BX, rf, yy, F.x0, w);
         apply_prog<LK>(w, R);
-        if (op) {
-            uint2* o = reinterpret_cast<uint2*>(op);
-            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
-            op += ostep;
-        }
-        if (onorm) {
-            // ToTensor + Normalize (datasets.py:392-393): exact table per channel, NCHW planes
-            uint32_t e[24];
-            #pragma unroll
-            for (int i = 0; i < 24; ++i) e[i] = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;      // byte i = pixel i / 3, channel i % 3
-            if (norm_dtype == SSAD_NORM_F32) {
-                const float* lut = reinterpret_cast<const float*>(lutbase);
-                float* ob = reinterpret_cast<float*>(onorm);
-                #pragma unroll
-                for (int ch = 0; ch < 3; ++ch) {
-                    float4* o = reinterpret_cast<float4*>(ob + (size_t)ch * npix + p0);
-                    #pragma unroll
-                    for (int qq = 0; qq < 2; ++qq) {
-                        float4 v;
-                        v.x = lut[ch * 256 + e[3 * (4 * qq + 0) + ch]];
-                        v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
-                        v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
-                        v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
-                        o[qq] = v;
-                    }
-                }
-            } else {
-                const uint16_t* lut = reinterpret_cast<const uint16_t*>(lutbase);
-                uint16_t* ob = reinterpret_cast<uint16_t*>(onorm);
-                #pragma unroll
-                for (int ch = 0; ch < 3; ++ch) {
-                    uint32_t wv[4];
-                    #pragma unroll
-                    for (int qq = 0; qq < 4; ++qq) {
-                        uint32_t lo = lut[ch * 256 + e[3 * (2 * qq) + ch]];
-                        uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
-                        wv[qq] = lo | (hi << 16);
-                    }
-                    *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
-                }
-            }
-        }
+        if (op) { store24(op, w); op += ostep; }
+        if (onorm) store_norm(w, onorm, norm_dtype, lutbase, npix, (size_t)p0);
         p0 += pstep;
     }
 }
+
+// General path: any width that is a multiple of 8, ragged last slab.
+template <int LK>
+__device__ __forceinline__ void pass1_gen(const Slab& S, const uint8_t* in, int in_pitch, uint8_t* xb, int xpitch, bool store_raw,
+                                          bool store_pre, bool need_rgb, bool need_luma, const ProgRegs& R, uint32_t (&acc)[7]) {
+    uint32_t s0 = 0, s1 = 0, s2 = 0, sl = 0;
+    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
+    uint8_t* const xb0 = xb + (size_t)S.r0 * xpitch;           // dense rows: unit `lin` of the slab sits at lin * 24
+    SSAD_PIPELINED_LOOP(S, in0, in_pitch, false) {
+        SSAD_PIPELINED_STEP(S, in_pitch, false)
+        (void)rr; (void)yy; (void)x0;
+        pass1_unit<LK>(w, xb0 + (size_t)lin * 24, store_raw, store_pre, need_rgb, need_luma, R, s0, s1, s2, sl);
+    }
+    acc[0] += s0; acc[1] += s1; acc[2] += s2; acc[3] += sl;
+}
+
+template <int LK>
+__device__ __forceinline__ void pass2_gen(const Slab& S, const uint8_t* in, int in_pitch, const ProgRegs& R, int W, int npix,
+                                          uint8_t* obase, void* onorm, int norm_dtype, const uint8_t* lutbase) {
+    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
+    const size_t pbase = (size_t)S.r0 * W;                     // dense outputs: unit `lin` starts at pixel pbase + lin * 8
+    SSAD_PIPELINED_LOOP(S, in0, in_pitch, false) {
+        SSAD_PIPELINED_STEP(S, in_pitch, false)
+        (void)rr; (void)yy; (void)x0;
+        apply_prog<LK>(w, R);
+        const size_t p0 = pbase + (size_t)lin * 8;
+        if (obase) store24(obase + p0 * 3, w);
+        if (onorm) store_norm(w, onorm, norm_dtype, lutbase, npix, p0);
+    }
+}
+
+// the loop of pass 1 / pass 2 for one slab, by kind
+#define SSAD_V7_BY_KIND(kind, CALL)                                                     \
+    switch (kind) {                                                                     \
+        case LK_COPY:    CALL(LK_COPY); break;                                          \
+        case LK_BYTELUT: CALL(LK_BYTELUT); break;                                       \
+        case LK_SAT_UC:  CALL(LK_SAT_UC); break;                                        \
+        case LK_SAT_UL:  CALL(LK_SAT_UL); break;                                        \
+        case LK_SAT_LC:  CALL(LK_SAT_LC); break;                                        \
+        default:         CALL(LK_SAT_LL); break;                                        \
+    }
 
 // ================================================================ plan
 __global__ void __launch_bounds__(NT)
 plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
                const SsadImageParams* __restrict__ params, const uint32_t* __restrict__ mask_bits,
-               ImgState* __restrict__ state, uint32_t* __restrict__ cov_all, uint8_t* __restrict__ flags_all) {
+               ImgState* __restrict__ state, uint32_t* __restrict__ cov_all, Sched* __restrict__ sched,
+               int32_t* __restrict__ order) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ SsadImageParams P;
     __shared__ Plan D;
@@ -251,7 +296,6 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
     const int tid = threadIdx.x, b = blockIdx.x;
     const int H = g.H, W = g.W, npix = H * W;
     uint32_t* const cov = cov_all + (size_t)b * g.cov_stride;
-    uint8_t* const flags = flags_all + (size_t)b * H;
     ImgState* const S = state + b;
 
     if (tid < (int)(sizeof(SsadImageParams) / 4))
@@ -356,42 +400,48 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
             if (lo <= hi) row_set_bits(row, lo, hi);
         }
     }
-    for (int r = tid; r < H; r += NT) {
-        uint32_t f = 0;
-        for (int k = 0; k < npaste; ++k) {
-            const int v = r - D.paste[k][1];
-            if (v >= 0 && v < bh) f |= 1u << k;
+    if (tid == 0) {
+        // work lists: pass 1 runs the ops ahead of Contrast (and may have nothing to do at all), pass 2 the rest
+        const bool need1 = P.warp_en != 0 || y != 0 || D.cpos >= 0;
+        if (need1) {
+            const int k1 = kind_of_ops(D.ops, 0, max(D.cpos, 0));
+            order[((size_t)0 * NKIND + k1) * g.batch + atomicAdd(&sched->count[0][k1], 1u)] = b;
         }
-        flags[r] = (uint8_t)f;
+        const int k2 = kind_of_ops(D.ops, D.s_in_pre ? D.cpos : 0, D.nops);
+        order[((size_t)1 * NKIND + k2) * g.batch + atomicAdd(&sched->count[1][k2], 1u)] = b;
     }
     __syncthreads();
     copy_words(&S->D, &D, tid);
     copy_words(&S->TP, &TP, tid);
 }
 
+
 // ================================================================ pass 1
 __global__ void __launch_bounds__(NT, 4)
 pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
                 const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
                 const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state,
-                const uint32_t* __restrict__ cov_all, const uint8_t* __restrict__ flags_all, uint8_t* xbuf) {
+                const Sched* __restrict__ sched, const int32_t* __restrict__ order, uint8_t* xbuf) {
     __shared__ SsadImageParams P;
     __shared__ Plan D;
     __shared__ Tables TP;
     __shared__ uint32_t red[NWARP * 8 + 8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int b = (int)(blockIdx.x / (unsigned)g.nslab), slab = (int)(blockIdx.x - (unsigned)b * g.nslab);
+    const uint32_t j = blockIdx.x / (unsigned)g.nslab;
+    const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
+    int kind;
+    const int b = sched_lookup(sched, order, g.batch, 0, j, kind);
+    if (b < 0) return;                           // images with nothing to do in pass 1 are on no list
     const int H = g.H, W = g.W, npix = H * W;
     ImgState* const S = state + b;
     if (tid < (int)(sizeof(SsadImageParams) / 4))
         reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
     copy_words(&D, &S->D, tid);
-    copy_words(&TP, &S->TP, tid);
+    if (kind != LK_COPY) copy_words(&TP, &S->TP, tid);
     __syncthreads();
 
     const int y = D.y, cpos = D.cpos;
     const bool warped = P.warp_en != 0;
-    if (!warped && y == 0 && cpos < 0) return;
     const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
     const int cx0 = P.crop_off[0], cy0 = P.crop_off[1];
     const int nunits = (r1 - r0) * g.upr;
@@ -399,10 +449,6 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     const int spitch = (int)d.src_pitch;
     uint8_t* const xb = xbuf + (size_t)b * npix * 3;
     const int xpitch = W * 3;
-    Boxes BX;
-    BX.cov = cov_all + (size_t)b * g.cov_stride; BX.canvas = nullptr; BX.pitch = (int)g.cov_pitch; BX.cpitch = (int)g.canvas_pitch;
-    BX.bw = D.bw; BX.bh = D.bh; BX.npaste = D.npaste;
-    const uint8_t* const flags = flags_all + (size_t)b * H + r0;
 
     uint32_t acc[7] = {0, 0, 0, 0, 0, 0, 0};          // 0-2 RGB of x, 3 sum of L, 4-6 RGB of the cut
     const Slab SL = make_slab(r0, nunits, g.upr, tid);
@@ -421,11 +467,10 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
                       put_pixel<PIX>(w, __ldg(q), __ldg(q + 1), __ldg(q + 2)); } }
             SSAD_GATHER(0) SSAD_GATHER(1) SSAD_GATHER(2) SSAD_GATHER(3) SSAD_GATHER(4) SSAD_GATHER(5) SSAD_GATHER(6) SSAD_GATHER(7)
             #undef SSAD_GATHER
-            uint2* const o = reinterpret_cast<uint2*>(xb + (size_t)r0 * xpitch + (size_t)lin * 24);
-            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
+            store24(xb + (size_t)r0 * xpitch + (size_t)lin * 24, w);
         }
     }
-    if (y == 0 && cpos < 0) return;
+    if (y == 0 && cpos < 0) return;              // only the gather was needed
     // x as the passes read it (each thread re-reads only what it wrote itself)
     const uint8_t* const xin_base = warped ? xb : sbase;
     const int xin_pitch = warped ? xpitch : spitch;
@@ -433,25 +478,18 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
         ProgRegs R;
         R.fs = D.pre.fs; R.ta = smem_u32(TP.a); R.tab = smem_u32(TP.ab); R.tbc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
         const bool need_rgb = y != 0, need_luma = cpos >= 0;
+        const bool store_pre = D.s_in_pre != 0;                           // pass 2 starts from pre(x)
+        const bool store_raw = y != 0 && !store_pre && !warped;           // the pastes are written into x
         if (g.fast) {
             const uint8_t* const in0 = xin_base + (size_t)r0 * xin_pitch;
             uint8_t* const xb0 = xb + (size_t)r0 * xpitch;
-            switch (loop_kind(D.pre)) {
-                case LK_COPY:    pass1_fast<LK_COPY>(in0, xin_pitch, xb0, xpitch, false, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
-                case LK_BYTELUT: pass1_fast<LK_BYTELUT>(in0, xin_pitch, xb0, xpitch, false, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
-                case LK_SAT_UC:  pass1_fast<LK_SAT_UC>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
-                case LK_SAT_UL:  pass1_fast<LK_SAT_UL>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
-                case LK_SAT_LC:  pass1_fast<LK_SAT_LC>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
-                default:         pass1_fast<LK_SAT_LL>(in0, xin_pitch, xb0, xpitch, true, need_rgb, need_luma, R, D, BX, flags, r0, g.upr, tid, acc); break;
-            }
-        } else
-        switch (loop_kind(D.pre)) {
-            case LK_COPY:    pass1_loop<LK_COPY>(SL, xin_base, xin_pitch, !warped, xb, xpitch, false, need_rgb, need_luma, R, D, BX, flags, acc); break;
-            case LK_BYTELUT: pass1_loop<LK_BYTELUT>(SL, xin_base, xin_pitch, !warped, xb, xpitch, false, need_rgb, need_luma, R, D, BX, flags, acc); break;
-            case LK_SAT_UC:  pass1_loop<LK_SAT_UC>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
-            case LK_SAT_UL:  pass1_loop<LK_SAT_UL>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
-            case LK_SAT_LC:  pass1_loop<LK_SAT_LC>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
-            default:         pass1_loop<LK_SAT_LL>(SL, xin_base, xin_pitch, !warped, xb, xpitch, true, need_rgb, need_luma, R, D, BX, flags, acc); break;
+            #define SSAD_CALL(LK) pass1_fast<LK>(in0, xin_pitch, xb0, xpitch, store_raw, store_pre, need_rgb, need_luma, R, g.upr, tid, acc)
+            SSAD_V7_BY_KIND(kind, SSAD_CALL)
+            #undef SSAD_CALL
+        } else {
+            #define SSAD_CALL(LK) pass1_gen<LK>(SL, xin_base, xin_pitch, xb, xpitch, store_raw, store_pre, need_rgb, need_luma, R, acc)
+            SSAD_V7_BY_KIND(kind, SSAD_CALL)
+            #undef SSAD_CALL
         }
         // RGB sums of the would-be cut (dataset_generator.py:202-207 / 147-159): rows dealt over the image's warps
         if (y != 0 && P.src_variant != 2) {
@@ -475,13 +513,13 @@ __global__ void __launch_bounds__(NT)
 canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
                  const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
                  const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state,
-                 const uint32_t* __restrict__ cov_all, uint32_t* __restrict__ canvas_all) {
+                 const uint32_t* __restrict__ cov_all, uint32_t* __restrict__ canvas_all, uint8_t* xbuf) {
     __shared__ SsadImageParams P;
     __shared__ Plan D;
     __shared__ Tables TP;
     __shared__ uint8_t simtab[256];
     __shared__ uint32_t red[NWARP * 8 + 8];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const int b = (int)(blockIdx.x / (unsigned)g.ncanvas), part = (int)(blockIdx.x - (unsigned)b * g.ncanvas);
     const int H = g.H, W = g.W, npix = H * W;
     ImgState* const S = state + b;
@@ -496,6 +534,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     const int pw = P.rect[2], ph = P.rect[3];
     const uint32_t* const cov = cov_all + (size_t)b * g.cov_stride;
     uint32_t* const canvas = canvas_all + (size_t)b * g.canvas_stride;
+    uint8_t* const xb = xbuf + (size_t)b * npix * 3;
     const int pitchw = (int)g.cov_pitch;
     const Donor dn = donor_of(d, src, donor_bank, b, P);
 
@@ -530,9 +569,9 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     K.flat = D.flat; K.sim = D.sim; K.bf1 = D.bf1; K.bf2 = D.bf2;
     K.frgb[0] = D.flat_rgb[0]; K.frgb[1] = D.flat_rgb[1]; K.frgb[2] = D.flat_rgb[2];
 
-    // ---- patch canvas: canvas pixel (u, v) -> packed (r, g, b, L); this CTA fills its share of the rows that land
-    // inside the image, one warp per row
-    uint32_t lnew = 0;
+    // ---- patch canvas: canvas pixel (u, v) -> packed (r, g, b, L): the colour that is pasted (after the `pre` program
+    // when the x buffer holds pre(x)) and the L Contrast will see there.  This CTA owns a share of the canvas rows that
+    // land inside the image; the (row, column) box is dealt pixel by pixel over the threads.
     const bool cut_sim = !K.flat && K.sim;
     if (cut_sim) {
         for (int v = tid; v < 256; v += NT) simtab[v] = (uint8_t)brightness_u8(brightness_u8((uint32_t)v, K.bf1), K.bf2);
@@ -546,20 +585,23 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     }
     const int per = (max(cv_hi - cv_lo, 0) + g.ncanvas - 1) / g.ncanvas;
     const int my_lo = cv_lo + part * per, my_hi = min(cv_hi, my_lo + per);
+    if (my_lo >= my_hi) return;
     const int cpitch = (int)g.canvas_pitch;
-    const int pl0 = D.paste[0][0];
     const bool want_l = cpos >= 0;
-    for (int v = my_lo + warp; v < my_hi; v += NWARP) {
-        const uint32_t* crow = cov + (size_t)v * pitchw;
-        uint32_t* out = canvas + (size_t)v * cpitch;
-        const int xr = P.scar_fix[2] + v * P.scar_fix[1], yr = P.scar_fix[5] + v * P.scar_fix[4];
-        for (int u = lane; u < bw; u += 32) {
-            if (!((crow[u >> 5] >> (u & 31)) & 1u)) continue;
+    const uint32_t inv_bw = 0xFFFFFFFFu / (uint32_t)bw + 1u;        // idx / bw == umulhi(idx, inv_bw) for idx * bw < 2^32
+    {
+        const int total = (my_hi - my_lo) * bw;
+        for (int idx = tid; idx < total; idx += NT) {
+            const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - vr * bw, v = my_lo + vr;
+            if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
             uint32_t r, gg, bl;
             if (K.flat) { r = K.frgb[0]; gg = K.frgb[1]; bl = K.frgb[2]; }
             else {
                 int su = u, sv = v;          // source pixel of the cut: itself (polygon) | inverse rotation (scar)
-                if (y == 2) { su = (xr + u * P.scar_fix[0]) >> 16; sv = (yr + u * P.scar_fix[3]) >> 16; }
+                if (y == 2) {
+                    su = (P.scar_fix[2] + v * P.scar_fix[1] + u * P.scar_fix[0]) >> 16;
+                    sv = (P.scar_fix[5] + v * P.scar_fix[4] + u * P.scar_fix[3]) >> 16;
+                }
                 r = gg = bl = 0;
                 if (su < dn.u_hi && sv < dn.v_hi) {
                     const uint8_t* q = dn.base + (size_t)sv * dn.pitch + 3 * su;
@@ -573,37 +615,42 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
                 pixel_prog(D.pre, TP, pr, pg, pb);
                 L = luma_u8(pr, pg, pb);
                 if (s_in_pre) { r = pr; gg = pg; bl = pb; }
-                // a polygon is pasted once: visible wherever it lands inside the image
-                if (y == 1 && (unsigned)(pl0 + u) < (unsigned)W) lnew += L;
             }
-            out[u] = r | (gg << 8) | (bl << 16) | (L << 24);
+            canvas[(size_t)v * cpitch + u] = r | (gg << 8) | (bl << 16) | (L << 24);
         }
     }
-    if (cpos < 0) return;
     __syncthreads();
-    if (y == 2) {
-        // scars: k pastes of the same canvas, later ones overwrite earlier ones
-        for (int k = 0; k < npaste; ++k) {
-            const int pl = D.paste[k][0], pt = D.paste[k][1];
-            const int v_lo = max(max(0, -pt), my_lo), v_hi = min(min(bh, H - pt), my_hi);
-            for (int v = v_lo + warp; v < v_hi; v += NWARP) {
-                const int Y = pt + v;
-                for (int u = lane; u < bw; u += 32) {
-                    const int X = pl + u;
-                    if (X < 0 || X >= W) continue;
-                    if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
-                    bool later = false;          // a later paste overwrites this pixel: it is counted there
-                    for (int j = k + 1; j < npaste; ++j) {
-                        const int uj = X - D.paste[j][0], vj = Y - D.paste[j][1];
-                        if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) later = true;
-                    }
-                    if (later) continue;
-                    lnew += canvas[(size_t)v * cpitch + u] >> 24;
-                }
+    // ---- paste_patch / scar pastes (dataset_generator.py:268-275, datasets.py:340-355) into the x buffer: every image
+    // pixel is written by the LAST paste that covers it, so no two threads meet; the sum of L Contrast sees moves by
+    // L(new) - L(old)
+    uint32_t dl = 0;
+    for (int k = 0; k < npaste; ++k) {
+        const int pl = D.paste[k][0], pt = D.paste[k][1];
+        const int v_lo = max(max(0, -pt), my_lo), v_hi = min(min(bh, H - pt), my_hi);
+        const int total = max(v_hi - v_lo, 0) * bw;
+        for (int idx = tid; idx < total; idx += NT) {
+            const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - vr * bw, v = v_lo + vr;
+            const int X = pl + u, Y = pt + v;
+            if (X < 0 || X >= W) continue;
+            if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
+            bool later = false;              // a later paste overwrites this pixel: it is written there
+            for (int jj = k + 1; jj < npaste; ++jj) {
+                const int uj = X - D.paste[jj][0], vj = Y - D.paste[jj][1];
+                if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) later = true;
             }
+            if (later) continue;
+            const uint32_t c = canvas[(size_t)v * cpitch + u];
+            uint8_t* const q = xb + ((size_t)Y * W + X) * 3;
+            if (want_l) {
+                uint32_t pr = q[0], pg = q[1], pb = q[2];
+                if (!s_in_pre) pixel_prog(D.pre, TP, pr, pg, pb);      // the x buffer holds x itself
+                dl += (c >> 24) - luma_u8(pr, pg, pb);
+            }
+            q[0] = (uint8_t)c; q[1] = (uint8_t)(c >> 8); q[2] = (uint8_t)(c >> 16);
         }
     }
-    uint32_t v1[1] = {lnew};
+    if (!want_l) return;
+    uint32_t v1[1] = {dl};
     block_sum_vec<1>(v1, red);
     if (tid == 0 && v1[0] != 0) atomicAdd(&S->acc[7], v1[0]);
 }
@@ -656,22 +703,26 @@ finish_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
 __global__ void __launch_bounds__(NT, 4)
 pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
                 const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
-                const ImgState* __restrict__ state, const uint32_t* __restrict__ cov_all,
-                const uint8_t* __restrict__ flags_all, const uint8_t* xbuf, const uint32_t* __restrict__ canvas_all,
-                const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8, void* __restrict__ out_norm) {
-    __shared__ Plan D;
+                const ImgState* __restrict__ state, const Sched* __restrict__ sched, const int32_t* __restrict__ order,
+                const uint8_t* xbuf, const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8,
+                void* __restrict__ out_norm) {
     __shared__ Tables TF;
     __shared__ __align__(16) uint8_t lut_s[3072];
-    __shared__ int32_t hdr[4];
+    __shared__ int32_t hdr[8];
     const int tid = threadIdx.x;
-    const int b = (int)(blockIdx.x / (unsigned)g.nslab), slab = (int)(blockIdx.x - (unsigned)b * g.nslab);
+    const uint32_t j = blockIdx.x / (unsigned)g.nslab;
+    const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
+    int kind;
+    const int b = sched_lookup(sched, order, g.batch, 1, j, kind);
+    if (b < 0) return;
     const int H = g.H, W = g.W, npix = H * W;
     const ImgState* const S = state + b;
-    copy_words(&D, &S->D, tid);
-    copy_words(&TF, &S->TF, tid);
+    if (kind != LK_COPY) copy_words(&TF, &S->TF, tid);
     if (tid == 0) {
         const SsadImageParams* p = params + b;
-        hdr[0] = p->crop_off[0]; hdr[1] = p->crop_off[1]; hdr[2] = p->warp_en;
+        hdr[0] = p->crop_off[0]; hdr[1] = p->crop_off[1];
+        hdr[2] = (p->warp_en != 0 || S->D.s_in_pre != 0 || S->D.y != 0) ? 1 : 0;      // pass 2 starts from the x buffer
+        hdr[3] = __float_as_int(S->D.fin.fs);
     }
     if (out_norm != nullptr) {
         const int nw = (d.out_norm_dtype == SSAD_NORM_F32) ? 768 : 384;
@@ -681,18 +732,11 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     __syncthreads();
     const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
     const int nunits = (r1 - r0) * g.upr;
-    const int cx0 = hdr[0], cy0 = hdr[1];
-    const bool stored = hdr[2] != 0 || D.s_in_pre != 0;          // pass 1 left its bytes in the x buffer
-    const uint8_t* const sbase = src + (size_t)b * d.src_stride + (size_t)cy0 * d.src_pitch + (size_t)cx0 * 3;
-    const uint8_t* const xb = xbuf + (size_t)b * npix * 3;
-    Boxes BX;
-    BX.cov = cov_all + (size_t)b * g.cov_stride; BX.canvas = canvas_all + (size_t)b * g.canvas_stride;
-    BX.pitch = (int)g.cov_pitch; BX.cpitch = (int)g.canvas_pitch; BX.bw = D.bw; BX.bh = D.bh; BX.npaste = D.npaste;
-    const uint8_t* const flags = flags_all + (size_t)b * H + r0;
-    const Slab SL = make_slab(r0, nunits, g.upr, tid);
+    const bool stored = hdr[2] != 0;
     ProgRegs R;
-    R.fs = D.fin.fs; R.ta = smem_u32(TF.a); R.tab = smem_u32(TF.ab); R.tbc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
-    const uint8_t* const in2 = stored ? xb : sbase;
+    R.fs = __int_as_float(hdr[3]); R.ta = smem_u32(TF.a); R.tab = smem_u32(TF.ab); R.tbc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
+    const uint8_t* const in2 = stored ? xbuf + (size_t)b * npix * 3
+                                      : src + (size_t)b * d.src_stride + (size_t)hdr[1] * d.src_pitch + (size_t)hdr[0] * 3;
     const int in2_pitch = stored ? W * 3 : (int)d.src_pitch;
     uint8_t* const obase = out_u8 ? out_u8 + (size_t)b * d.out_u8_stride : nullptr;
     void* onorm = nullptr;
@@ -700,28 +744,19 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
                                                                : (void*)(reinterpret_cast<uint16_t*>(out_norm) + (size_t)b * 3 * npix);
     if (g.fast) {
         const uint8_t* const in0 = in2 + (size_t)r0 * in2_pitch;
-        switch (loop_kind(D.fin)) {
-            case LK_COPY:    pass2_fast<LK_COPY>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-            case LK_BYTELUT: pass2_fast<LK_BYTELUT>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-            case LK_SAT_UC:  pass2_fast<LK_SAT_UC>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-            case LK_SAT_UL:  pass2_fast<LK_SAT_UL>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-            case LK_SAT_LC:  pass2_fast<LK_SAT_LC>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-            default:         pass2_fast<LK_SAT_LL>(in0, in2_pitch, R, D, BX, flags, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-        }
-        return;
-    }
-    switch (loop_kind(D.fin)) {
-        case LK_COPY:    pass2_loop<LK_COPY>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-        case LK_BYTELUT: pass2_loop<LK_BYTELUT>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-        case LK_SAT_UC:  pass2_loop<LK_SAT_UC>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-        case LK_SAT_UL:  pass2_loop<LK_SAT_UL>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-        case LK_SAT_LC:  pass2_loop<LK_SAT_LC>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
-        default:         pass2_loop<LK_SAT_LL>(SL, in2, in2_pitch, !stored, R, D, BX, flags, W, npix, obase, onorm, d.out_norm_dtype, lut_s); break;
+        #define SSAD_CALL(LK) pass2_fast<LK>(in0, in2_pitch, R, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s)
+        SSAD_V7_BY_KIND(kind, SSAD_CALL)
+        #undef SSAD_CALL
+    } else {
+        const Slab SL = make_slab(r0, nunits, g.upr, tid);
+        #define SSAD_CALL(LK) pass2_gen<LK>(SL, in2, in2_pitch, R, W, npix, obase, onorm, d.out_norm_dtype, lut_s)
+        SSAD_V7_BY_KIND(kind, SSAD_CALL)
+        #undef SSAD_CALL
     }
 }
 
 static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
-    g.H = d.height; g.W = d.width;
+    g.H = d.height; g.W = d.width; g.batch = d.batch;
     if (g.W % 8 != 0 || g.W < 8) return false;
     if (!(d.sat_factor_max <= kSatMax)) return false;       // the table after Saturation covers factors up to kSatMax
     g.upr = g.W / 8;
@@ -733,7 +768,7 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.nslab = (g.H + g.rows_slab - 1) / g.rows_slab;
     g.fast = (NT % g.upr == 0 && upt == UPT && g.rows_slab * g.upr == NT * UPT && g.H % g.rows_slab == 0) ? 1 : 0;
     if (getenv("SSAD_V7_NOFAST")) g.fast = 0;
-    g.ncanvas = 4;
+    g.ncanvas = 8;
     if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
     g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;
     g.cov_rows = (uint32_t)d.max_patch_h;
@@ -744,8 +779,9 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.o_canvas = up((size_t)d.batch * d.height * d.width * 3);
     g.o_state = g.o_canvas + up((size_t)d.batch * g.canvas_stride * 4);
     g.o_cov = g.o_state + up((size_t)d.batch * sizeof(ImgState));
-    g.o_flags = g.o_cov + up((size_t)d.batch * g.cov_stride * 4);
-    g.ws_total = g.o_flags + up((size_t)d.batch * d.height);
+    g.o_sched = g.o_cov + up((size_t)d.batch * g.cov_stride * 4);
+    g.o_order = g.o_sched + up(sizeof(Sched));
+    g.ws_total = g.o_order + up((size_t)2 * NKIND * d.batch * 4);
     g.smem_plan = (((uint32_t)g.H + 1u) * 4u + 15u) & ~15u;
     return true;
 }
@@ -758,6 +794,9 @@ size_t ssad_v7_workspace(const SsadBatchDesc& d) {
     if (!ssad::v7::make_geo7(d, g)) return 0;
     return g.ws_total;
 }
+
+// kernels one ssad_generate call launches on this path (bench.py's gpu_launches)
+int ssad_v7_launches(void) { return 5; }
 
 // returns SSAD_OK when launched, SSAD_EUNSUPPORTED when the caller should use another kernel
 int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
@@ -776,15 +815,18 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
     uint32_t* const canvas = reinterpret_cast<uint32_t*>(ws + g.o_canvas);
     ImgState* const state = reinterpret_cast<ImgState*>(ws + g.o_state);
     uint32_t* const cov = reinterpret_cast<uint32_t*>(ws + g.o_cov);
-    uint8_t* const flags = ws + g.o_flags;
+    Sched* const sched = reinterpret_cast<Sched*>(ws + g.o_sched);
+    int32_t* const order = reinterpret_cast<int32_t*>(ws + g.o_order);
     const unsigned B = (unsigned)d.batch;
-    plan_v7_kernel<<<B, NT, g.smem_plan, stream>>>(d, g, params, mask_bits, state, cov, flags);
-    pass1_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, donor_bank, state, cov, flags, xbuf);
-    canvas_v7_kernel<<<B * (unsigned)g.ncanvas, NT, 0, stream>>>(d, g, params, src, donor_bank, state, cov, canvas);
+    cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(Sched), stream);
+    if (e != cudaSuccess) return ssad_set_cuda_error(e);
+    plan_v7_kernel<<<B, NT, g.smem_plan, stream>>>(d, g, params, mask_bits, state, cov, sched, order);
+    pass1_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, donor_bank, state, sched, order, xbuf);
+    canvas_v7_kernel<<<B * (unsigned)g.ncanvas, NT, 0, stream>>>(d, g, params, src, donor_bank, state, cov, canvas, xbuf);
     finish_v7_kernel<<<B, NT, 0, stream>>>(d, g, state, y_out, debug);
-    pass2_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, state, cov, flags, xbuf, canvas, norm_lut, out_u8,
+    pass2_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, state, sched, order, xbuf, norm_lut, out_u8,
                                                             out_norm);
-    cudaError_t e = cudaGetLastError();
+    e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     return SSAD_OK;
 }
