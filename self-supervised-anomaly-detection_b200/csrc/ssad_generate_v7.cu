@@ -42,17 +42,28 @@ constexpr int NKIND = 6;         // LK_COPY .. LK_SAT_LL
 struct ImgState {                // per image, global memory
     Plan D;
     uint32_t acc[8];             // 0-2 RGB of x, 3 sum of L of pre(x), 4-6 RGB of the cut, 7 sum of L(new) - L(old) over the pastes
+    int32_t sk[4];               // loop kind and position in that kind's list: pass 1 (kind NKIND: nothing to do), pass 2
     Tables TP, TF;
 };
-struct Sched {                   // work lists of the two passes: images per loop kind (zeroed before the plan kernel)
-    uint32_t count[2][8];
+struct Sched {                   // images per loop kind in the two passes (zeroed before the plan kernel); [0][NKIND] counts
+    uint32_t count[2][8];        // the images pass 1 skips
 };
+// One slot per image and pass, ordered by loop kind: what a CTA of a pass needs to start streaming.
+struct alignas(16) Hdr {
+    int32_t b;                   // image, -1: no work
+    int32_t kind;                // LK_*
+    int32_t flags;               // HF_*
+    int32_t cx0, cy0;            // crop window
+    float fs;                    // Saturation factor of the pass's program
+    int32_t pad[2];
+};
+enum { HF_WARP = 1, HF_PRE = 2, HF_DEFECT = 4, HF_LUMA = 8 };
 
 struct Geo7 {
     int H, W, upr, rows_slab, nslab, ncanvas, batch;
     uint32_t cov_pitch, cov_rows, canvas_pitch;
     size_t canvas_stride, cov_stride;                       // words per image
-    size_t o_canvas, o_state, o_cov, o_sched, o_order, ws_total;   // byte offsets in the workspace (x buffer at 0)
+    size_t o_canvas, o_state, o_cov, o_sched, o_hdr, ws_total;   // byte offsets in the workspace (x buffer at 0)
     int fast;                                               // NT % upr == 0 and every slab holds NT * UPT units
     uint32_t smem_plan;                                     // dynamic shared memory of the plan kernel (row prefix)
 };
@@ -72,19 +83,6 @@ __device__ __forceinline__ int kind_of_ops(const int32_t* ops, int i0, int i1) {
     for (int i = i0; i < i1; ++i) if (ops[i] == 2) is = i;
     if (is < 0) return LK_BYTELUT;
     return LK_SAT_UC + ((is > i0) ? 2 : 0) + ((is + 1 < i1) ? 1 : 0);
-}
-
-// image and loop kind of the j-th image of pass p's lists
-__device__ __forceinline__ int sched_lookup(const Sched* sc, const int32_t* order, int batch, int p, uint32_t j, int& kind) {
-    uint32_t c = 0;
-    #pragma unroll
-    for (int k = 0; k < NKIND; ++k) {
-        const uint32_t n = sc->count[p][k];
-        if (j < c + n) { kind = k; return order[((size_t)p * NKIND + k) * batch + (j - c)]; }
-        c += n;
-    }
-    kind = -1;
-    return -1;
 }
 
 // ------------------------------------------------------------------ unit loops
@@ -190,17 +188,14 @@ __device__ __forceinline__ FastCol fast_col(const uint8_t* in0, int in_pitch, in
     return F;
 }
 
+// F / nx: the thread's column and its first unit's loads, already in flight (fast_col + ld_raw)
 template <int LK>
-__device__ __forceinline__ void pass1_fast(const uint8_t* in0 /* slab row 0 */, int in_pitch, uint8_t* xb0 /* slab row 0 */,
-                                           int xpitch, bool store_raw, bool store_pre, bool need_rgb, bool need_luma,
-                                           const ProgRegs& R, int upr, int tid, uint32_t (&acc)[7]) {
-    FastCol F = fast_col(in0, in_pitch, upr, tid);
+__device__ __forceinline__ void pass1_fast(FastCol& F, Raw& nx, uint8_t* xb0 /* slab row 0 */, int xpitch, bool store_raw,
+                                           bool store_pre, bool need_rgb, bool need_luma, const ProgRegs& R, uint32_t (&acc)[7]) {
     uint8_t* op = xb0 + (size_t)F.rr0 * xpitch + F.cu * 24;
     const size_t ostep = (size_t)F.dr * xpitch;
     uint32_t s0 = 0, s1 = 0, s2 = 0, sl = 0;
     const bool four = F.mis != 0;
-    Raw nx;
-    ld_raw(F.ip, four, false, nx);
     #pragma unroll 2
     for (int it = 0; it < UPT; ++it) {
         const Raw cur = nx;
@@ -215,17 +210,13 @@ __device__ __forceinline__ void pass1_fast(const uint8_t* in0 /* slab row 0 */, 
 }
 
 template <int LK>
-__device__ __forceinline__ void pass2_fast(const uint8_t* in0 /* slab row 0 */, int in_pitch, const ProgRegs& R, int r0, int upr,
-                                           int tid, int W, int npix, uint8_t* obase, void* onorm, int norm_dtype,
-                                           const uint8_t* lutbase) {
-    FastCol F = fast_col(in0, in_pitch, upr, tid);
+__device__ __forceinline__ void pass2_fast(FastCol& F, Raw& nx, int r0, int W, int npix, const ProgRegs& R, uint8_t* obase,
+                                           void* onorm, int norm_dtype, const uint8_t* lutbase) {
     int p0 = (r0 + F.rr0) * W + F.cu * 8;                  // first pixel of the current unit inside the image
     const int pstep = F.dr * W;
     uint8_t* op = obase ? obase + (size_t)p0 * 3 : nullptr;
     const size_t ostep = (size_t)pstep * 3;
     const bool four = F.mis != 0;
-    Raw nx;
-    ld_raw(F.ip, four, false, nx);
     #pragma unroll 2
     for (int it = 0; it < UPT; ++it) {
         const Raw cur = nx;
@@ -285,8 +276,7 @@ __device__ __forceinline__ void pass2_gen(const Slab& S, const uint8_t* in, int 
 __global__ void __launch_bounds__(NT)
 plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
                const SsadImageParams* __restrict__ params, const uint32_t* __restrict__ mask_bits,
-               ImgState* __restrict__ state, uint32_t* __restrict__ cov_all, Sched* __restrict__ sched,
-               int32_t* __restrict__ order) {
+               ImgState* __restrict__ state, uint32_t* __restrict__ cov_all, Sched* __restrict__ sched) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ SsadImageParams P;
     __shared__ Plan D;
@@ -403,12 +393,10 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
     if (tid == 0) {
         // work lists: pass 1 runs the ops ahead of Contrast (and may have nothing to do at all), pass 2 the rest
         const bool need1 = P.warp_en != 0 || y != 0 || D.cpos >= 0;
-        if (need1) {
-            const int k1 = kind_of_ops(D.ops, 0, max(D.cpos, 0));
-            order[((size_t)0 * NKIND + k1) * g.batch + atomicAdd(&sched->count[0][k1], 1u)] = b;
-        }
+        const int k1 = need1 ? kind_of_ops(D.ops, 0, max(D.cpos, 0)) : NKIND;
         const int k2 = kind_of_ops(D.ops, D.s_in_pre ? D.cpos : 0, D.nops);
-        order[((size_t)1 * NKIND + k2) * g.batch + atomicAdd(&sched->count[1][k2], 1u)] = b;
+        S->sk[0] = k1; S->sk[1] = (int32_t)atomicAdd(&sched->count[0][k1], 1u);
+        S->sk[2] = k2; S->sk[3] = (int32_t)atomicAdd(&sched->count[1][k2], 1u);
     }
     __syncthreads();
     copy_words(&S->D, &D, tid);
@@ -416,39 +404,76 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
 }
 
 
+// ================================================================ lists
+// slot of every image in the kind-ordered lists of the two passes (thread per image)
+__global__ void __launch_bounds__(NT)
+lists_v7_kernel(const __grid_constant__ Geo7 g, const SsadImageParams* __restrict__ params,
+                const ImgState* __restrict__ state, const Sched* __restrict__ sched, Hdr* __restrict__ hdr) {
+    const int b = blockIdx.x * NT + threadIdx.x;
+    if (b >= g.batch) return;
+    const ImgState* const S = state + b;
+    const SsadImageParams* const p = params + b;
+    const Plan& D = S->D;
+    const int flags = (p->warp_en ? HF_WARP : 0) | (D.s_in_pre ? HF_PRE : 0) | (D.y != 0 ? HF_DEFECT : 0) | (D.cpos >= 0 ? HF_LUMA : 0);
+    #pragma unroll
+    for (int ps = 0; ps < 2; ++ps) {
+        const int kind = S->sk[2 * ps], pos = S->sk[2 * ps + 1];
+        uint32_t rank = (uint32_t)pos;
+        for (int k = 0; k < kind; ++k) rank += sched->count[ps][k];
+        Hdr h;
+        h.b = (kind < NKIND) ? b : -1;
+        h.kind = kind; h.flags = flags; h.cx0 = p->crop_off[0]; h.cy0 = p->crop_off[1];
+        float fs = 1.0f;                 // factor of the Saturation inside the pass's program, if any
+        const int i0 = (ps == 0) ? 0 : (D.s_in_pre ? D.cpos : 0), i1 = (ps == 0) ? max(D.cpos, 0) : D.nops;
+        for (int i = i0; i < i1; ++i) if (D.ops[i] == 2) fs = D.fac[i];
+        h.fs = fs; h.pad[0] = h.pad[1] = 0;
+        hdr[(size_t)ps * g.batch + rank] = h;
+    }
+}
+
 // ================================================================ pass 1
 __global__ void __launch_bounds__(NT, 4)
 pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
                 const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
-                const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state,
-                const Sched* __restrict__ sched, const int32_t* __restrict__ order, uint8_t* xbuf) {
+                const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state, const Hdr* __restrict__ hdr,
+                uint8_t* xbuf) {
     __shared__ SsadImageParams P;
-    __shared__ Plan D;
     __shared__ Tables TP;
     __shared__ uint32_t red[NWARP * 8 + 8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t j = blockIdx.x / (unsigned)g.nslab;
     const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
-    int kind;
-    const int b = sched_lookup(sched, order, g.batch, 0, j, kind);
-    if (b < 0) return;                           // images with nothing to do in pass 1 are on no list
+    const int4 h0 = __ldg(reinterpret_cast<const int4*>(hdr + j));                  // b, kind, flags, cx0
+    const int b = h0.x, kind = h0.y, flags = h0.z;
+    if (b < 0) return;                           // images with nothing to do in pass 1 sit behind the lists
+    const int2 h1 = __ldg(reinterpret_cast<const int2*>(hdr + j) + 2);              // cy0, fs
     const int H = g.H, W = g.W, npix = H * W;
     ImgState* const S = state + b;
-    if (tid < (int)(sizeof(SsadImageParams) / 4))
-        reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
-    copy_words(&D, &S->D, tid);
-    if (kind != LK_COPY) copy_words(&TP, &S->TP, tid);
-    __syncthreads();
-
-    const int y = D.y, cpos = D.cpos;
-    const bool warped = P.warp_en != 0;
+    const bool warped = (flags & HF_WARP) != 0, defect = (flags & HF_DEFECT) != 0, need_luma = (flags & HF_LUMA) != 0;
+    const bool store_pre = (flags & HF_PRE) != 0;                    // pass 2 starts from pre(x)
+    const bool store_raw = defect && !store_pre && !warped;          // the pastes are written into x
     const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
-    const int cx0 = P.crop_off[0], cy0 = P.crop_off[1];
     const int nunits = (r1 - r0) * g.upr;
-    const uint8_t* const sbase = src + (size_t)b * d.src_stride + (size_t)cy0 * d.src_pitch + (size_t)cx0 * 3;
+    const uint8_t* const sbase = src + (size_t)b * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;
     const int spitch = (int)d.src_pitch;
     uint8_t* const xb = xbuf + (size_t)b * npix * 3;
     const int xpitch = W * 3;
+    // x as the passes read it (each thread re-reads only what it wrote itself)
+    const uint8_t* const xin_base = warped ? xb : sbase;
+    const int xin_pitch = warped ? xpitch : spitch;
+
+    // the first loads of the stream leave before the tables arrive
+    FastCol F;
+    Raw nx;
+    const bool fast = g.fast != 0;
+    if (fast && !warped) {
+        F = fast_col(xin_base + (size_t)r0 * xin_pitch, xin_pitch, g.upr, tid);
+        ld_raw(F.ip, F.mis != 0, false, nx);
+    }
+    if (tid < (int)(sizeof(SsadImageParams) / 4))
+        reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
+    if (kind != LK_COPY) copy_words(&TP, &S->TP, tid);
+    __syncthreads();
 
     uint32_t acc[7] = {0, 0, 0, 0, 0, 0, 0};          // 0-2 RGB of x, 3 sum of L, 4-6 RGB of the cut
     const Slab SL = make_slab(r0, nunits, g.upr, tid);
@@ -469,21 +494,19 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
             #undef SSAD_GATHER
             store24(xb + (size_t)r0 * xpitch + (size_t)lin * 24, w);
         }
+        if (!defect && !need_luma) return;       // only the gather was needed
+        if (fast) {
+            F = fast_col(xin_base + (size_t)r0 * xin_pitch, xin_pitch, g.upr, tid);
+            ld_raw(F.ip, F.mis != 0, false, nx);
+        }
     }
-    if (y == 0 && cpos < 0) return;              // only the gather was needed
-    // x as the passes read it (each thread re-reads only what it wrote itself)
-    const uint8_t* const xin_base = warped ? xb : sbase;
-    const int xin_pitch = warped ? xpitch : spitch;
     {
         ProgRegs R;
-        R.fs = D.pre.fs; R.ta = smem_u32(TP.a); R.tab = smem_u32(TP.ab); R.tbc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
-        const bool need_rgb = y != 0, need_luma = cpos >= 0;
-        const bool store_pre = D.s_in_pre != 0;                           // pass 2 starts from pre(x)
-        const bool store_raw = y != 0 && !store_pre && !warped;           // the pastes are written into x
-        if (g.fast) {
-            const uint8_t* const in0 = xin_base + (size_t)r0 * xin_pitch;
+        R.fs = __int_as_float(h1.y); R.ta = smem_u32(TP.a); R.tab = smem_u32(TP.ab); R.tbc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
+        const bool need_rgb = defect;
+        if (fast) {
             uint8_t* const xb0 = xb + (size_t)r0 * xpitch;
-            #define SSAD_CALL(LK) pass1_fast<LK>(in0, xin_pitch, xb0, xpitch, store_raw, store_pre, need_rgb, need_luma, R, g.upr, tid, acc)
+            #define SSAD_CALL(LK) pass1_fast<LK>(F, nx, xb0, xpitch, store_raw, store_pre, need_rgb, need_luma, R, acc)
             SSAD_V7_BY_KIND(kind, SSAD_CALL)
             #undef SSAD_CALL
         } else {
@@ -492,7 +515,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
             #undef SSAD_CALL
         }
         // RGB sums of the would-be cut (dataset_generator.py:202-207 / 147-159): rows dealt over the image's warps
-        if (y != 0 && P.src_variant != 2) {
+        if (defect && P.src_variant != 2) {
             const Donor dn = donor_of(d, src, donor_bank, b, P);
             for (int v = slab * NWARP + warp; v < dn.v_hi; v += g.nslab * NWARP) {
                 const uint8_t* q = dn.base + (size_t)v * dn.pitch;
@@ -523,7 +546,11 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     const int b = (int)(blockIdx.x / (unsigned)g.ncanvas), part = (int)(blockIdx.x - (unsigned)b * g.ncanvas);
     const int H = g.H, W = g.W, npix = H * W;
     ImgState* const S = state + b;
-    if (S->D.y == 0) return;                     // (uniform over the CTA)
+    const int y0 = S->D.y;                       // (uniform over the CTA)
+    if (y0 == 0) return;
+    // a polygon's canvas is shared by all NC CTAs of the image, the small scar canvas by a quarter of them
+    const int nparts = (y0 == 1) ? g.ncanvas : max(1, g.ncanvas / 2);
+    if (part >= nparts) return;
     if (tid < (int)(sizeof(SsadImageParams) / 4))
         reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
     copy_words(&D, &S->D, tid);
@@ -583,13 +610,72 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
         const int v_lo = max(0, -pt), v_hi = min(bh, H - pt);
         if (v_lo < v_hi) { cv_lo = min(cv_lo, v_lo); cv_hi = max(cv_hi, v_hi); }
     }
-    const int per = (max(cv_hi - cv_lo, 0) + g.ncanvas - 1) / g.ncanvas;
+    const int per = (max(cv_hi - cv_lo, 0) + nparts - 1) / nparts;
     const int my_lo = cv_lo + part * per, my_hi = min(cv_hi, my_lo + per);
     if (my_lo >= my_hi) return;
     const int cpitch = (int)g.canvas_pitch;
     const bool want_l = cpos >= 0;
     const uint32_t inv_bw = 0xFFFFFFFFu / (uint32_t)bw + 1u;        // idx / bw == umulhi(idx, inv_bw) for idx * bw < 2^32
-    {
+    uint32_t dl = 0;                             // sum of L(new) - L(old) over the pixels this CTA pastes
+    if (y == 1) {
+        // polygon: one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
+        // thread and round, their loads issued together: the chain coverage word -> cut pixel -> old pixel is three
+        // memory latencies long, and nothing else hides it.
+        constexpr int NB = 4;
+        const int total = (my_hi - my_lo) * bw;
+        const int pl = D.paste[0][0], pt = D.paste[0][1];
+        const bool read_cut = !K.flat;
+        for (int idx0 = tid; idx0 < total; idx0 += NT * NB) {
+            int uu[NB], vv[NB];
+            uint32_t cw[NB];
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                const int idx = min(idx0 + j * NT, total - 1);
+                const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw);
+                uu[j] = idx - vr * bw; vv[j] = my_lo + vr;
+                cw[j] = cov[(size_t)vv[j] * pitchw + (uu[j] >> 5)];
+            }
+            bool on[NB];
+            const uint8_t* qc[NB];
+            uint8_t* qx[NB];
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                const int X = pl + uu[j];
+                on[j] = (idx0 + j * NT < total) && ((cw[j] >> (uu[j] & 31)) & 1u) && X >= 0 && X < W;
+                const bool in_cut = on[j] && read_cut && uu[j] < dn.u_hi && vv[j] < dn.v_hi;
+                qc[j] = in_cut ? dn.base + (size_t)vv[j] * dn.pitch + 3 * uu[j] : nullptr;
+                qx[j] = on[j] ? xb + ((size_t)(pt + vv[j]) * W + X) * 3 : nullptr;
+            }
+            uint32_t cr[NB], cg[NB], cb[NB], xr[NB], xg[NB], xbl[NB];
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                cr[j] = cg[j] = cb[j] = 0;
+                if (qc[j]) { cr[j] = __ldg(qc[j]); cg[j] = __ldg(qc[j] + 1); cb[j] = __ldg(qc[j] + 2); }
+            }
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                xr[j] = xg[j] = xbl[j] = 0;
+                if (qx[j] && want_l) { xr[j] = qx[j][0]; xg[j] = qx[j][1]; xbl[j] = qx[j][2]; }
+            }
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                if (!on[j]) continue;
+                uint32_t r = cr[j], gg = cg[j], bl = cb[j];
+                if (K.flat) { r = K.frgb[0]; gg = K.frgb[1]; bl = K.frgb[2]; }
+                else if (cut_sim) { r = simtab[r]; gg = simtab[gg]; bl = simtab[bl]; }
+                if (want_l) {
+                    uint32_t pr = r, pg = gg, pb = bl;
+                    pixel_prog(D.pre, TP, pr, pg, pb);
+                    const uint32_t L = luma_u8(pr, pg, pb);
+                    if (s_in_pre) { r = pr; gg = pg; bl = pb; }
+                    uint32_t orr = xr[j], og = xg[j], ob = xbl[j];
+                    if (!s_in_pre) pixel_prog(D.pre, TP, orr, og, ob);     // the x buffer holds x itself
+                    dl += L - luma_u8(orr, og, ob);
+                }
+                qx[j][0] = (uint8_t)r; qx[j][1] = (uint8_t)gg; qx[j][2] = (uint8_t)bl;
+            }
+        }
+    } else {
         const int total = (my_hi - my_lo) * bw;
         for (int idx = tid; idx < total; idx += NT) {
             const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - vr * bw, v = my_lo + vr;
@@ -616,37 +702,71 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
                 L = luma_u8(pr, pg, pb);
                 if (s_in_pre) { r = pr; gg = pg; bl = pb; }
             }
+            if (y == 1) {
+                // one paste: straight into the x buffer (paste_patch, dataset_generator.py:268-275)
+                const int X = D.paste[0][0] + u, Y = D.paste[0][1] + v;
+                if (X < 0 || X >= W) continue;
+                uint8_t* const q = xb + ((size_t)Y * W + X) * 3;
+                if (want_l) {
+                    uint32_t pr = q[0], pg = q[1], pb = q[2];
+                    if (!s_in_pre) pixel_prog(D.pre, TP, pr, pg, pb);      // the x buffer holds x itself
+                    dl += L - luma_u8(pr, pg, pb);
+                }
+                q[0] = (uint8_t)r; q[1] = (uint8_t)gg; q[2] = (uint8_t)bl;
+                continue;
+            }
             canvas[(size_t)v * cpitch + u] = r | (gg << 8) | (bl << 16) | (L << 24);
         }
     }
-    __syncthreads();
+    if (y == 2) __syncthreads();
     // ---- paste_patch / scar pastes (dataset_generator.py:268-275, datasets.py:340-355) into the x buffer: every image
     // pixel is written by the LAST paste that covers it, so no two threads meet; the sum of L Contrast sees moves by
     // L(new) - L(old)
-    uint32_t dl = 0;
-    for (int k = 0; k < npaste; ++k) {
-        const int pl = D.paste[k][0], pt = D.paste[k][1];
-        const int v_lo = max(max(0, -pt), my_lo), v_hi = min(min(bh, H - pt), my_hi);
-        const int total = max(v_hi - v_lo, 0) * bw;
-        for (int idx = tid; idx < total; idx += NT) {
-            const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - vr * bw, v = v_lo + vr;
-            const int X = pl + u, Y = pt + v;
-            if (X < 0 || X >= W) continue;
-            if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
-            bool later = false;              // a later paste overwrites this pixel: it is written there
-            for (int jj = k + 1; jj < npaste; ++jj) {
-                const int uj = X - D.paste[jj][0], vj = Y - D.paste[jj][1];
-                if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) later = true;
+    // (all pastes x canvas rows of this CTA x columns) dealt over the threads, NB items per thread and round with
+    // their loads issued together
+    if (y == 2) {
+        constexpr int NB = 4;
+        const int box = (my_hi - my_lo) * bw, total = npaste * box;
+        for (int id0 = tid; id0 < total; id0 += NT * NB) {
+            bool on[NB];
+            uint8_t* qx[NB];
+            const uint32_t* qc[NB];
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                const int id = min(id0 + j * NT, total - 1);
+                const int k = id / box, idx = id - k * box;
+                const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - vr * bw, v = my_lo + vr;
+                const int X = D.paste[k][0] + u, Y = D.paste[k][1] + v;
+                bool ok = (id0 + j * NT < total) && X >= 0 && X < W && Y >= 0 && Y < H &&
+                          ((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u);
+                if (ok)                          // a later paste overwrites this pixel: it is written there
+                    for (int jj = k + 1; jj < npaste; ++jj) {
+                        const int uj = X - D.paste[jj][0], vj = Y - D.paste[jj][1];
+                        if (uj >= 0 && uj < bw && vj >= 0 && vj < bh && ((cov[(size_t)vj * pitchw + (uj >> 5)] >> (uj & 31)) & 1u)) ok = false;
+                    }
+                on[j] = ok;
+                qc[j] = ok ? canvas + (size_t)v * cpitch + u : nullptr;
+                qx[j] = ok ? xb + ((size_t)Y * W + X) * 3 : nullptr;
             }
-            if (later) continue;
-            const uint32_t c = canvas[(size_t)v * cpitch + u];
-            uint8_t* const q = xb + ((size_t)Y * W + X) * 3;
-            if (want_l) {
-                uint32_t pr = q[0], pg = q[1], pb = q[2];
-                if (!s_in_pre) pixel_prog(D.pre, TP, pr, pg, pb);      // the x buffer holds x itself
-                dl += (c >> 24) - luma_u8(pr, pg, pb);
+            uint32_t c[NB], xr[NB], xg[NB], xbl[NB];
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                c[j] = xr[j] = xg[j] = xbl[j] = 0;
+                if (on[j]) {
+                    c[j] = *qc[j];
+                    if (want_l) { xr[j] = qx[j][0]; xg[j] = qx[j][1]; xbl[j] = qx[j][2]; }
+                }
             }
-            q[0] = (uint8_t)c; q[1] = (uint8_t)(c >> 8); q[2] = (uint8_t)(c >> 16);
+            #pragma unroll
+            for (int j = 0; j < NB; ++j) {
+                if (!on[j]) continue;
+                if (want_l) {
+                    uint32_t pr = xr[j], pg = xg[j], pb = xbl[j];
+                    if (!s_in_pre) pixel_prog(D.pre, TP, pr, pg, pb);      // the x buffer holds x itself
+                    dl += (c[j] >> 24) - luma_u8(pr, pg, pb);
+                }
+                qx[j][0] = (uint8_t)c[j]; qx[j][1] = (uint8_t)(c[j] >> 8); qx[j][2] = (uint8_t)(c[j] >> 16);
+            }
         }
     }
     if (!want_l) return;
@@ -701,50 +821,47 @@ finish_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
 
 // ================================================================ pass 2
 __global__ void __launch_bounds__(NT, 4)
-pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
-                const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
-                const ImgState* __restrict__ state, const Sched* __restrict__ sched, const int32_t* __restrict__ order,
-                const uint8_t* xbuf, const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8,
-                void* __restrict__ out_norm) {
+pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g, const uint8_t* __restrict__ src,
+                const ImgState* __restrict__ state, const Hdr* __restrict__ hdr, const uint8_t* xbuf,
+                const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8, void* __restrict__ out_norm) {
     __shared__ Tables TF;
     __shared__ __align__(16) uint8_t lut_s[3072];
-    __shared__ int32_t hdr[8];
     const int tid = threadIdx.x;
     const uint32_t j = blockIdx.x / (unsigned)g.nslab;
     const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
-    int kind;
-    const int b = sched_lookup(sched, order, g.batch, 1, j, kind);
+    const int4 h0 = __ldg(reinterpret_cast<const int4*>(hdr + j));                  // b, kind, flags, cx0
+    const int2 h1 = __ldg(reinterpret_cast<const int2*>(hdr + j) + 2);              // cy0, fs
+    const int b = h0.x, kind = h0.y;
     if (b < 0) return;
     const int H = g.H, W = g.W, npix = H * W;
-    const ImgState* const S = state + b;
-    if (kind != LK_COPY) copy_words(&TF, &S->TF, tid);
-    if (tid == 0) {
-        const SsadImageParams* p = params + b;
-        hdr[0] = p->crop_off[0]; hdr[1] = p->crop_off[1];
-        hdr[2] = (p->warp_en != 0 || S->D.s_in_pre != 0 || S->D.y != 0) ? 1 : 0;      // pass 2 starts from the x buffer
-        hdr[3] = __float_as_int(S->D.fin.fs);
+    const bool stored = (h0.z & (HF_WARP | HF_PRE | HF_DEFECT)) != 0;              // pass 2 starts from the x buffer
+    const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
+    const int nunits = (r1 - r0) * g.upr;
+    const uint8_t* const in2 = stored ? xbuf + (size_t)b * npix * 3
+                                      : src + (size_t)b * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;
+    const int in2_pitch = stored ? W * 3 : (int)d.src_pitch;
+    // the first loads of the stream leave before the tables arrive
+    FastCol F;
+    Raw nx;
+    if (g.fast) {
+        F = fast_col(in2 + (size_t)r0 * in2_pitch, in2_pitch, g.upr, tid);
+        ld_raw(F.ip, F.mis != 0, false, nx);
     }
+    if (kind != LK_COPY) copy_words(&TF, &state[b].TF, tid);
     if (out_norm != nullptr) {
         const int nw = (d.out_norm_dtype == SSAD_NORM_F32) ? 768 : 384;
         for (int i = tid; i < nw; i += NT)
             reinterpret_cast<uint32_t*>(lut_s)[i] = reinterpret_cast<const uint32_t*>(norm_lut)[i];
     }
     __syncthreads();
-    const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
-    const int nunits = (r1 - r0) * g.upr;
-    const bool stored = hdr[2] != 0;
     ProgRegs R;
-    R.fs = __int_as_float(hdr[3]); R.ta = smem_u32(TF.a); R.tab = smem_u32(TF.ab); R.tbc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
-    const uint8_t* const in2 = stored ? xbuf + (size_t)b * npix * 3
-                                      : src + (size_t)b * d.src_stride + (size_t)hdr[1] * d.src_pitch + (size_t)hdr[0] * 3;
-    const int in2_pitch = stored ? W * 3 : (int)d.src_pitch;
+    R.fs = __int_as_float(h1.y); R.ta = smem_u32(TF.a); R.tab = smem_u32(TF.ab); R.tbc = smem_u32(TF.b) + (uint32_t)TB_OFF - kMagicBits;
     uint8_t* const obase = out_u8 ? out_u8 + (size_t)b * d.out_u8_stride : nullptr;
     void* onorm = nullptr;
     if (out_norm) onorm = (d.out_norm_dtype == SSAD_NORM_F32) ? (void*)(reinterpret_cast<float*>(out_norm) + (size_t)b * 3 * npix)
                                                                : (void*)(reinterpret_cast<uint16_t*>(out_norm) + (size_t)b * 3 * npix);
     if (g.fast) {
-        const uint8_t* const in0 = in2 + (size_t)r0 * in2_pitch;
-        #define SSAD_CALL(LK) pass2_fast<LK>(in0, in2_pitch, R, r0, g.upr, tid, W, npix, obase, onorm, d.out_norm_dtype, lut_s)
+        #define SSAD_CALL(LK) pass2_fast<LK>(F, nx, r0, W, npix, R, obase, onorm, d.out_norm_dtype, lut_s)
         SSAD_V7_BY_KIND(kind, SSAD_CALL)
         #undef SSAD_CALL
     } else {
@@ -780,8 +897,8 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.o_state = g.o_canvas + up((size_t)d.batch * g.canvas_stride * 4);
     g.o_cov = g.o_state + up((size_t)d.batch * sizeof(ImgState));
     g.o_sched = g.o_cov + up((size_t)d.batch * g.cov_stride * 4);
-    g.o_order = g.o_sched + up(sizeof(Sched));
-    g.ws_total = g.o_order + up((size_t)2 * NKIND * d.batch * 4);
+    g.o_hdr = g.o_sched + up(sizeof(Sched));
+    g.ws_total = g.o_hdr + up((size_t)2 * d.batch * sizeof(Hdr));
     g.smem_plan = (((uint32_t)g.H + 1u) * 4u + 15u) & ~15u;
     return true;
 }
@@ -796,7 +913,7 @@ size_t ssad_v7_workspace(const SsadBatchDesc& d) {
 }
 
 // kernels one ssad_generate call launches on this path (bench.py's gpu_launches)
-int ssad_v7_launches(void) { return 5; }
+int ssad_v7_launches(void) { return 6; }
 
 // returns SSAD_OK when launched, SSAD_EUNSUPPORTED when the caller should use another kernel
 int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
@@ -816,16 +933,16 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
     ImgState* const state = reinterpret_cast<ImgState*>(ws + g.o_state);
     uint32_t* const cov = reinterpret_cast<uint32_t*>(ws + g.o_cov);
     Sched* const sched = reinterpret_cast<Sched*>(ws + g.o_sched);
-    int32_t* const order = reinterpret_cast<int32_t*>(ws + g.o_order);
+    Hdr* const hdr = reinterpret_cast<Hdr*>(ws + g.o_hdr);
     const unsigned B = (unsigned)d.batch;
     cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(Sched), stream);
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
-    plan_v7_kernel<<<B, NT, g.smem_plan, stream>>>(d, g, params, mask_bits, state, cov, sched, order);
-    pass1_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, donor_bank, state, sched, order, xbuf);
+    plan_v7_kernel<<<B, NT, g.smem_plan, stream>>>(d, g, params, mask_bits, state, cov, sched);
+    lists_v7_kernel<<<(B + NT - 1) / NT, NT, 0, stream>>>(g, params, state, sched, hdr);
+    pass1_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, donor_bank, state, hdr, xbuf);
     canvas_v7_kernel<<<B * (unsigned)g.ncanvas, NT, 0, stream>>>(d, g, params, src, donor_bank, state, cov, canvas, xbuf);
     finish_v7_kernel<<<B, NT, 0, stream>>>(d, g, state, y_out, debug);
-    pass2_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, state, sched, order, xbuf, norm_lut, out_u8,
-                                                            out_norm);
+    pass2_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, src, state, hdr + d.batch, xbuf, norm_lut, out_u8, out_norm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     return SSAD_OK;

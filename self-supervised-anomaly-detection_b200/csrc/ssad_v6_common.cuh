@@ -40,8 +40,9 @@ struct Prog {
     int32_t kind, sa, sb;
     float fs;                           // Saturation factor
 };
-struct Tables {                         // shared memory, per program
-    uint32_t a[256];                    // SA_LUT: magic float (2^23 + run(v)) of the per-channel run ahead of Saturation
+struct alignas(16) Tables {             // shared memory, per program
+    uint8_t a[256];                     // SA_LUT: run(v) of the per-channel run ahead of Saturation (a byte table: random
+                                        // lookups meet two words per bank at most)
     uint8_t ab[256];                    // PK_BYTELUT: run(v)
     uint8_t b[TB_SIZE];                 // SB_LUT: run(clip(t)) of the per-channel run after Saturation
 };
@@ -93,7 +94,7 @@ __device__ inline void build_prog(Prog& G, Tables& T, const int32_t* ops, const 
     const int sb = (is + 1 < i1) ? SB_LUT : SB_CLAMP;          // (the clamp form also serves factors <= 1)
     if (tid == 0) { G.kind = PK_SAT; G.sa = sa; G.sb = sb; G.fs = fs; }
     if (sa == SA_LUT)
-        for (int v = tid; v < 256; v += NT) T.a[v] = kMagicBits | run_ops((uint32_t)v, ops, fac, i0, is, mean);
+        for (int v = tid; v < 256; v += NT) T.a[v] = (uint8_t)run_ops((uint32_t)v, ops, fac, i0, is, mean);
     if (sb == SB_LUT)
         for (int j = tid; j < TB_SIZE; j += NT) {
             const int t = j - TB_OFF;
@@ -333,7 +334,7 @@ __device__ __forceinline__ void stage_in(Unit8& u, const uint32_t (&w)[6], uint3
             for (int ch = 0; ch < 3; ++ch) {
                 const int b0 = 6 * k + ch, b1 = 6 * k + 3 + ch;
                 const uint32_t i0 = __byte_perm(w[b0 >> 2], 0, 0x4440 + (b0 & 3)), i1 = __byte_perm(w[b1 >> 2], 0, 0x4440 + (b1 & 3));
-                u.v[ch][k] = pack2(__uint_as_float(lds_u32(ta + i0 * 4u)), __uint_as_float(lds_u32(ta + i1 * 4u)));
+                u.v[ch][k] = pack2(__uint_as_float(kMagicBits | lds_u8(ta + i0)), __uint_as_float(kMagicBits | lds_u8(ta + i1)));
             }
         }
     }
@@ -409,7 +410,7 @@ __device__ __forceinline__ void pixel_prog(const Prog& G, const Tables& T, uint3
     if (G.kind == PK_COPY) return;
     if (G.kind == PK_BYTELUT) { r = T.ab[r]; g = T.ab[g]; b = T.ab[b]; return; }
     float m[3];
-    if (G.sa == SA_LUT) { m[0] = __uint_as_float(T.a[r]); m[1] = __uint_as_float(T.a[g]); m[2] = __uint_as_float(T.a[b]); }
+    if (G.sa == SA_LUT) { m[0] = magic_from_u8(T.a[r]); m[1] = magic_from_u8(T.a[g]); m[2] = magic_from_u8(T.a[b]); }
     else { m[0] = magic_from_u8(r); m[1] = magic_from_u8(g); m[2] = magic_from_u8(b); }
     const uint32_t acc = luma_bits(__float_as_uint(m[0]), __float_as_uint(m[1]), __float_as_uint(m[2]));
     const float nml = __uint_as_float(__byte_perm(acc, 0xCB000000u, 0x7542));
