@@ -189,6 +189,7 @@ def main():
     ap.add_argument("--out", default="u8", choices=["u8", "f32", "bf16"], help="output variant timed for `value`")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-steps", type=int, default=20)
+    ap.add_argument("--graph", type=int, default=1, help="1: replay each step's ssad_generate call from a CUDA graph")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -255,6 +256,10 @@ def main():
 
     plans = [gen.plan(srcs[j], params, want_u8=want_u8, norm_dtype=norm_dtype, params_dev=pdev,
                       out_u8=outs_u8[j], out_norm=outs_n[j], y_out=y_out) for j in range(2)]
+
+    if args.graph:
+        for pl in plans:
+            gen.capture(pl)                      # one cudaGraphLaunch per step instead of a dozen kernel launches
 
     def step(i):
         gen.run(plans[i & 1])

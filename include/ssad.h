@@ -9,7 +9,9 @@
  *
  * Conventions
  *  - all pointers except SsadBatchDesc* are DEVICE pointers owned by the caller (PyTorch);
- *    the library never allocates, frees or synchronises, and launches only on `stream`;
+ *    the library never allocates or frees device memory and never synchronises; work is ordered on `stream`
+ *    (ssad_generate may fork part of a large batch onto internal helper streams and joins them back with events
+ *    before it returns, so stream order and CUDA-graph capture see one call);
  *  - every random decision of the reference arrives as an explicit per-image parameter
  *    record (SsadImageParams); there is no RNG in the library;
  *  - images are uint8, interleaved RGB (HWC), row pitch in bytes;
@@ -139,6 +141,9 @@ int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, cons
                   uint8_t* out_u8, void* out_norm, int64_t* y_out, SsadDebug* debug,
                   void* workspace, size_t workspace_bytes, void* stream);
 size_t ssad_generate_workspace(const SsadBatchDesc* desc);
+/* Number of kernels one ssad_generate call launches for this descriptor (the kernel pipeline cuts large batches into
+ * chunks that run side by side on helper streams forked from, and joined back to, the caller's stream). */
+int ssad_generate_launches(const SsadBatchDesc* desc);
 
 /* Host-computed constants of skimage.feature.canny(image, sigma=1.5, low_threshold=5, high_threshold=15) as
  * obj_mask calls it (dataset_generator.py:30).  They are inputs (not computed by the library) because the Gaussian

@@ -68,6 +68,11 @@ struct Geo7 {
     uint32_t smem_plan;                                     // dynamic shared memory of the plan kernel (row prefix)
 };
 
+// Programmatic dependent launch: every kernel lets its successor's CTAs start as soon as its own have all started
+// (they fill the SMs the tail of this grid leaves idle), and waits for its predecessor's memory before its first read.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 template <typename T>
 __device__ __forceinline__ void copy_words(T* dst, const T* src, int tid) {
     static_assert(sizeof(T) % 4 == 0, "word copy");
@@ -286,6 +291,7 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
     const int tid = threadIdx.x, b = blockIdx.x;
     const int H = g.H, W = g.W, npix = H * W;
     uint32_t* const cov = cov_all + (size_t)b * g.cov_stride;
+    pdl_launch_dependents();
     ImgState* const S = state + b;
 
     if (tid < (int)(sizeof(SsadImageParams) / 4))
@@ -411,6 +417,8 @@ lists_v7_kernel(const __grid_constant__ Geo7 g, const SsadImageParams* __restric
                 const ImgState* __restrict__ state, const Sched* __restrict__ sched, Hdr* __restrict__ hdr) {
     const int b = blockIdx.x * NT + threadIdx.x;
     if (b >= g.batch) return;
+    pdl_launch_dependents();
+    pdl_wait();
     const ImgState* const S = state + b;
     const SsadImageParams* const p = params + b;
     const Plan& D = S->D;
@@ -437,12 +445,13 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
                 const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
                 const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state, const Hdr* __restrict__ hdr,
                 uint8_t* xbuf) {
-    __shared__ SsadImageParams P;
     __shared__ Tables TP;
     __shared__ uint32_t red[NWARP * 8 + 8];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const uint32_t j = blockIdx.x / (unsigned)g.nslab;
     const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
+    pdl_launch_dependents();
+    pdl_wait();
     const int4 h0 = __ldg(reinterpret_cast<const int4*>(hdr + j));                  // b, kind, flags, cx0
     const int b = h0.x, kind = h0.y, flags = h0.z;
     if (b < 0) return;                           // images with nothing to do in pass 1 sit behind the lists
@@ -470,10 +479,11 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
         F = fast_col(xin_base + (size_t)r0 * xin_pitch, xin_pitch, g.upr, tid);
         ld_raw(F.ip, F.mis != 0, false, nx);
     }
-    if (tid < (int)(sizeof(SsadImageParams) / 4))
-        reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
-    if (kind != LK_COPY) copy_words(&TP, &S->TP, tid);
-    __syncthreads();
+    const SsadImageParams& P = params[b];        // read in place (L1 broadcast): only the gather and the cut sums need it
+    if (kind != LK_COPY) {                       // (uniform over the CTA)
+        copy_words(&TP, &S->TP, tid);
+        __syncthreads();
+    }
 
     uint32_t acc[7] = {0, 0, 0, 0, 0, 0, 0};          // 0-2 RGB of x, 3 sum of L, 4-6 RGB of the cut
     const Slab SL = make_slab(r0, nunits, g.upr, tid);
@@ -516,12 +526,24 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
         }
         // RGB sums of the would-be cut (dataset_generator.py:202-207 / 147-159): rows dealt over the image's warps
         if (defect && P.src_variant != 2) {
+            // the cut box dealt pixel by pixel over the threads of the image's slabs, four loads in flight per channel
             const Donor dn = donor_of(d, src, donor_bank, b, P);
-            for (int v = slab * NWARP + warp; v < dn.v_hi; v += g.nslab * NWARP) {
-                const uint8_t* q = dn.base + (size_t)v * dn.pitch;
-                for (int u = lane; u < dn.u_hi; u += 32) {
-                    acc[4] += __ldg(q + 3 * u); acc[5] += __ldg(q + 3 * u + 1); acc[6] += __ldg(q + 3 * u + 2);
+            const int bw = max(dn.u_hi, 0), total = bw * max(dn.v_hi, 0);
+            const uint32_t inv_bw = 0xFFFFFFFFu / (uint32_t)max(bw, 2) + 1u;
+            const int stride = g.nslab * NT;
+            for (int i0 = slab * NT + tid; i0 < total; i0 += 4 * stride) {
+                uint32_t r[4], gg[4], bl[4];
+                #pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int idx = i0 + q * stride;
+                    r[q] = gg[q] = bl[q] = 0;
+                    if (idx < total) {
+                        const int v = (bw < 2) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - v * bw;
+                        const uint8_t* p = dn.base + (size_t)v * dn.pitch + 3 * u;
+                        r[q] = __ldg(p); gg[q] = __ldg(p + 1); bl[q] = __ldg(p + 2);
+                    }
                 }
+                acc[4] += (r[0] + r[1]) + (r[2] + r[3]); acc[5] += (gg[0] + gg[1]) + (gg[2] + gg[3]); acc[6] += (bl[0] + bl[1]) + (bl[2] + bl[3]);
             }
         }
     }
@@ -546,6 +568,8 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     const int b = (int)(blockIdx.x / (unsigned)g.ncanvas), part = (int)(blockIdx.x - (unsigned)b * g.ncanvas);
     const int H = g.H, W = g.W, npix = H * W;
     ImgState* const S = state + b;
+    pdl_launch_dependents();
+    pdl_wait();
     const int y0 = S->D.y;                       // (uniform over the CTA)
     if (y0 == 0) return;
     // a polygon's canvas is shared by all NC CTAs of the image, the small scar canvas by a quarter of them
@@ -784,6 +808,8 @@ finish_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     const int tid = threadIdx.x, b = blockIdx.x;
     const int npix = g.H * g.W;
     ImgState* const S = state + b;
+    pdl_launch_dependents();
+    pdl_wait();
     copy_words(&D, &S->D, tid);
     __syncthreads();
     const int cpos = D.cpos, nops = D.nops;
@@ -829,6 +855,8 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     const int tid = threadIdx.x;
     const uint32_t j = blockIdx.x / (unsigned)g.nslab;
     const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
+    pdl_launch_dependents();
+    pdl_wait();
     const int4 h0 = __ldg(reinterpret_cast<const int4*>(hdr + j));                  // b, kind, flags, cx0
     const int2 h1 = __ldg(reinterpret_cast<const int2*>(hdr + j) + 2);              // cy0, fs
     const int b = h0.x, kind = h0.y;
@@ -906,19 +934,103 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
 }  // namespace v7
 }  // namespace ssad
 
+// The batch is cut into chunks that run the kernel pipeline side by side: chunk 0 on the caller's stream, the others on
+// helper streams forked from it and joined back before the call returns (events; legal under stream capture).  The short
+// latency-bound kernels of one chunk (plan, lists, canvas, finish) then overlap the streaming passes of another.
+static int v7_chunks(int batch) {
+    int n = (batch >= 256) ? 2 : 1;
+    if (const char* f = getenv("SSAD_V7_SPLIT")) { int v = atoi(f); if (v >= 1 && v <= 8) n = v; }
+    if (n > batch) n = batch;
+    return n < 1 ? 1 : n;
+}
+static int v7_chunk_size(int batch) { const int n = v7_chunks(batch); return (batch + n - 1) / n; }
+
 size_t ssad_v7_workspace(const SsadBatchDesc& d) {
     ssad::v7::Geo7 g;
-    if (!ssad::v7::make_geo7(d, g)) return 0;
-    return g.ws_total;
+    SsadBatchDesc dc = d;
+    dc.batch = v7_chunk_size(d.batch);
+    if (!ssad::v7::make_geo7(dc, g)) return 0;
+    return g.ws_total * (size_t)v7_chunks(d.batch);
 }
 
 // kernels one ssad_generate call launches on this path (bench.py's gpu_launches)
-int ssad_v7_launches(void) { return 6; }
+int ssad_v7_launches(int batch) { return 6 * v7_chunks(batch); }
+
+static int launch_v7_chunk(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
+                           const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
+                           SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
+struct V7Streams {               // helper streams and fork/join events of one device, created on first use
+    cudaStream_t s[8];
+    cudaEvent_t fork, join[8];
+    bool ok;
+};
+static V7Streams* v7_streams() {
+    static V7Streams per_dev[64];
+    static bool made[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    V7Streams& S = per_dev[dev];
+    if (!made[dev]) {
+        made[dev] = true;
+        S.ok = cudaEventCreateWithFlags(&S.fork, cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 1; i < 8 && S.ok; ++i)
+            S.ok = cudaStreamCreateWithFlags(&S.s[i], cudaStreamNonBlocking) == cudaSuccess &&
+                   cudaEventCreateWithFlags(&S.join[i], cudaEventDisableTiming) == cudaSuccess;
+    }
+    return S.ok ? &S : nullptr;
+}
 
 // returns SSAD_OK when launched, SSAD_EUNSUPPORTED when the caller should use another kernel
 int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
                    const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
                    SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    const int nchunk = v7_chunks(d.batch), csize = v7_chunk_size(d.batch);
+    const size_t need = ssad_v7_workspace(d);
+    if (need == 0) return SSAD_EUNSUPPORTED;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) || (d.src_pitch & 7) || (d.src_stride & 7)) return SSAD_EUNSUPPORTED;
+    if (nchunk > 1 && (d.src_stride & 15)) return SSAD_EUNSUPPORTED;      // every chunk's first image must stay 16-byte aligned
+    if (!workspace || workspace_bytes < need) return SSAD_EWORKSPACE;
+    if (reinterpret_cast<uintptr_t>(workspace) & 255) return SSAD_EALIGN;
+    const size_t ws_chunk = need / (size_t)nchunk;
+    V7Streams* const HS = (nchunk > 1) ? v7_streams() : nullptr;
+    if (nchunk > 1 && !HS) return SSAD_ELAUNCH;
+    cudaError_t e = cudaSuccess;
+    if (nchunk > 1) {
+        e = cudaEventRecord(HS->fork, stream);
+        for (int c = 1; c < nchunk && e == cudaSuccess; ++c) e = cudaStreamWaitEvent(HS->s[c], HS->fork, 0);
+        if (e != cudaSuccess) return ssad_set_cuda_error(e);
+    }
+    const size_t npix = (size_t)d.height * d.width;
+    const size_t norm_elem = (d.out_norm_dtype == SSAD_NORM_F32) ? 4 : 2;
+    int rc = SSAD_OK;
+    for (int c = 0; c < nchunk; ++c) {
+        const int b0 = c * csize, nb = (d.batch - b0 < csize) ? d.batch - b0 : csize;
+        if (nb <= 0) break;
+        SsadBatchDesc dc = d;
+        dc.batch = nb;
+        const uint32_t* mb = mask_bits;
+        if (mb && d.mask_mode == SSAD_MASK_PER_IMAGE) mb += (size_t)b0 * d.mask_stride_words;
+        cudaStream_t st = (c == 0) ? stream : HS->s[c];
+        rc = launch_v7_chunk(dc, params + b0, src + (size_t)b0 * d.src_stride, donor_bank, mb, norm_lut,
+                             out_u8 ? out_u8 + (size_t)b0 * d.out_u8_stride : nullptr,
+                             out_norm ? static_cast<uint8_t*>(out_norm) + (size_t)b0 * 3 * npix * norm_elem : nullptr,
+                             y_out ? y_out + b0 : nullptr, debug ? debug + b0 : nullptr,
+                             static_cast<uint8_t*>(workspace) + (size_t)c * ws_chunk, ws_chunk, st);
+        if (rc != SSAD_OK) break;
+    }
+    // join (also after a failed launch: the helper streams must not stay forked inside a capture)
+    for (int c = 1; c < nchunk; ++c) {
+        cudaError_t e2 = cudaEventRecord(HS->join[c], HS->s[c]);
+        if (e2 == cudaSuccess) e2 = cudaStreamWaitEvent(stream, HS->join[c], 0);
+        if (e2 != cudaSuccess && rc == SSAD_OK) rc = ssad_set_cuda_error(e2);
+    }
+    return rc;
+}
+
+static int launch_v7_chunk(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
+                           const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
+                           SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     using namespace ssad::v7;
     Geo7 g;
     if (!make_geo7(d, g)) return SSAD_EUNSUPPORTED;
@@ -937,12 +1049,35 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
     const unsigned B = (unsigned)d.batch;
     cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(Sched), stream);
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
-    plan_v7_kernel<<<B, NT, g.smem_plan, stream>>>(d, g, params, mask_bits, state, cov, sched);
-    lists_v7_kernel<<<(B + NT - 1) / NT, NT, 0, stream>>>(g, params, state, sched, hdr);
-    pass1_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, params, src, donor_bank, state, hdr, xbuf);
-    canvas_v7_kernel<<<B * (unsigned)g.ncanvas, NT, 0, stream>>>(d, g, params, src, donor_bank, state, cov, canvas, xbuf);
-    finish_v7_kernel<<<B, NT, 0, stream>>>(d, g, state, y_out, debug);
-    pass2_v7_kernel<<<B * (unsigned)g.nslab, NT, 0, stream>>>(d, g, src, state, hdr + d.batch, xbuf, norm_lut, out_u8, out_norm);
+    static const bool use_pdl = getenv("SSAD_V7_NOPDL") == nullptr;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    auto cfg_of = [&](unsigned grid, size_t smem, bool pdl) {
+        cudaLaunchConfig_t c;
+        memset(&c, 0, sizeof(c));
+        c.gridDim = dim3(grid, 1, 1); c.blockDim = dim3(NT, 1, 1); c.dynamicSmemBytes = smem; c.stream = stream;
+        c.attrs = attr; c.numAttrs = (pdl && use_pdl) ? 1 : 0;
+        return c;
+    };
+    const Hdr* const hdr2 = hdr + d.batch;
+    const uint8_t* const xbuf_c = xbuf;
+    const ImgState* const state_c = state;
+    const Sched* const sched_c = sched;
+    const uint32_t* const cov_c = cov;
+    cudaLaunchConfig_t c0 = cfg_of(B, g.smem_plan, false);          // follows the memset: a plain launch
+    e = cudaLaunchKernelEx(&c0, plan_v7_kernel, d, g, params, mask_bits, state, cov, sched);
+    cudaLaunchConfig_t c1 = cfg_of((B + NT - 1) / NT, 0, true);
+    if (e == cudaSuccess) e = cudaLaunchKernelEx(&c1, lists_v7_kernel, g, params, state_c, sched_c, hdr);
+    cudaLaunchConfig_t c2 = cfg_of(B * (unsigned)g.nslab, 0, true);
+    if (e == cudaSuccess) e = cudaLaunchKernelEx(&c2, pass1_v7_kernel, d, g, params, src, donor_bank, state, (const Hdr*)hdr, xbuf);
+    cudaLaunchConfig_t c3 = cfg_of(B * (unsigned)g.ncanvas, 0, true);
+    if (e == cudaSuccess) e = cudaLaunchKernelEx(&c3, canvas_v7_kernel, d, g, params, src, donor_bank, state, cov_c, canvas, xbuf);
+    cudaLaunchConfig_t c4 = cfg_of(B, 0, true);
+    if (e == cudaSuccess) e = cudaLaunchKernelEx(&c4, finish_v7_kernel, d, g, state, y_out, debug);
+    cudaLaunchConfig_t c5 = cfg_of(B * (unsigned)g.nslab, 0, true);
+    if (e == cudaSuccess) e = cudaLaunchKernelEx(&c5, pass2_v7_kernel, d, g, src, state_c, hdr2, xbuf_c, norm_lut, out_u8, out_norm);
+    if (e != cudaSuccess) return ssad_set_cuda_error(e);
     e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     return SSAD_OK;

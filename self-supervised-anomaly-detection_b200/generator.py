@@ -171,8 +171,26 @@ class BatchGenerator:
         return pl
 
     def run(self, plan: "Plan") -> None:
+        graph = getattr(plan, "graph", None)
+        if graph is not None:
+            graph.replay()
+            return
         stream = torch.cuda.current_stream(self.device).cuda_stream
         N.check(self.lib.ssad_generate(*plan.args, C.c_void_p(stream)), "ssad_generate")
+
+    def capture(self, plan: "Plan") -> "Plan":
+        """Record the plan's ssad_generate call (a handful of kernels, forked over helper streams) into a CUDA graph:
+        ``run(plan)`` then replays it with one launch.  The library never allocates or synchronises, so the call is
+        capturable as it is; inputs are read from, and outputs written to, the plan's tensors on every replay."""
+        with torch.cuda.device(self.device):
+            self.run(plan)                       # warm-up outside the capture (lazy module load, helper streams)
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                stream = torch.cuda.current_stream(self.device).cuda_stream
+                N.check(self.lib.ssad_generate(*plan.args, C.c_void_p(stream)), "ssad_generate")
+            plan.graph = g
+        return plan
 
     def generate(self, src: torch.Tensor, params: ParamBatch, *, masks: Optional[torch.Tensor] = None,
                  want_u8: bool = True, norm_dtype: Optional[torch.dtype] = None, debug: bool = False,

@@ -21,7 +21,7 @@ from __future__ import annotations
 
 import math
 from dataclasses import dataclass
-from typing import Dict, Optional
+from typing import Dict, Optional, Tuple
 
 import numpy as np
 
@@ -166,6 +166,21 @@ class ParamBatch:
 
     def slice(self, lo: int, hi: int) -> "ParamBatch":
         return ParamBatch(self.cfg, {k: v[lo:hi] for k, v in self.draws.items()}, self.records[lo:hi])
+
+    def shard(self, rank: int, world: int) -> "ParamBatch":
+        """This rank's contiguous block of the batch (one process per GPU; images are independent, so the shards
+        never exchange anything: SURVEY.md section 8e)."""
+        lo, hi = shard_bounds(len(self), rank, world)
+        return self.slice(lo, hi)
+
+
+def shard_bounds(batch: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous block split of ``batch`` images over ``world`` ranks; the first ``batch % world`` ranks get one more."""
+    if not 0 <= rank < world:
+        raise ValueError("rank must be in [0, world)")
+    q, r = divmod(int(batch), int(world))
+    lo = rank * q + min(rank, r)
+    return lo, lo + q + (1 if rank < r else 0)
 
 
 def derive_records(cfg: GeneratorConfig, draws: Dict[str, np.ndarray]) -> np.ndarray:

@@ -82,11 +82,12 @@ def test_v6_cluster_sizes_match_oracle(name, csize, monkeypatch):
     _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v6", "SSAD_V6_C": csize})
 
 
-@pytest.mark.parametrize("env", [{"SSAD_V7_NOFAST": "1"}, {"SSAD_V7_UPT": "3"}, {"SSAD_V7_NC": "1"}, {"SSAD_V7_NC": "16"}])
+@pytest.mark.parametrize("env", [{"SSAD_V7_NOFAST": "1"}, {"SSAD_V7_UPT": "3"}, {"SSAD_V7_NC": "1"}, {"SSAD_V7_NC": "16"}, {"SSAD_V7_SPLIT": "3"},
+                                 {"SSAD_V7_SPLIT": "8", "SSAD_V7_NOPDL": "1"}])
 @pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
 def test_v7_loop_and_grid_variants_match_oracle(name, env, monkeypatch):
     """v7's general unit loops (the fast ones need a power-of-two width and whole slabs), odd slab sizes, and the
-    number of CTAs that share an image's patch canvas."""
+    number of CTAs that share an image's patch canvas, and the batch cut into chunks on helper streams."""
     _check_against_oracle(name, 12, monkeypatch, dict(env, SSAD_KERNEL="v7"))
 
 
@@ -166,3 +167,29 @@ def test_large_batch_properties_config2_shape():
             inside |= (changed[:, 1] >= l) & (changed[:, 1] < l + w) & (changed[:, 0] >= t) & (changed[:, 0] < t + h)
         assert inside.all()
     assert n_def > B // 3
+
+
+@pytest.mark.parametrize("split", ["1", "3"])
+@pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture"])
+def test_graph_replay_matches_plain_launch(name, split, monkeypatch):
+    """BatchGenerator.capture(): the whole ssad_generate call (kernels on the caller's stream and on the helper
+    streams of the chunked pipeline) recorded in a CUDA graph; replays on fresh inputs equal plain launches."""
+    import gpu_utils as U
+    monkeypatch.setenv("SSAD_KERNEL", "v7")
+    monkeypatch.setenv("SSAD_V7_SPLIT", split)
+    sc = S.build(name, 12)
+    gen = U.make_generator(sc)
+    src = torch.from_numpy(sc.images).cuda()
+    ref = gen.generate(src, sc.params, masks=U.per_image_masks(sc), want_u8=True, norm_dtype=torch.float32)
+    torch.cuda.synchronize()
+    buf = torch.zeros_like(src)
+    plan = gen.plan(buf, sc.params, masks=U.per_image_masks(sc), want_u8=True, norm_dtype=torch.float32)
+    gen.capture(plan)
+    for _ in range(2):
+        plan.out_u8.zero_(); plan.out_norm.zero_(); plan.y_out.zero_()
+        buf.copy_(src)
+        gen.run(plan)
+        torch.cuda.synchronize()
+        assert torch.equal(plan.out_u8, ref["x_u8"])
+        assert torch.equal(plan.out_norm, ref["x"])
+        assert torch.equal(plan.y_out, ref["y"])
