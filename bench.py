@@ -2,7 +2,7 @@
 """Benchmark of the batched anomaly generator (BASELINE.json metric: synthetic-anomaly images/s and
 HBM GB/s, vs the reference CPU path).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config 1|2|3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config 1|2|3|4]
 
 A step = one pass of the hot path (ssad_generate) over one batch of synthetic inputs.  Workload at
 N=1 = BASELINE.json configs[1]: patch-level mode, batch 512 of 256x256 windows cut from 320x320
@@ -30,8 +30,10 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 import numpy as np  # noqa: E402
 
-# the kernel ssad_generate dispatches to for the bench shapes (SSAD_KERNEL pins another one)
-KERNEL_NAME = {None: "generate_v6_kernel", "v6": "generate_v6_kernel", "v5": "generate_v5_kernel", "cluster": "generate_cluster_kernel",
+# the kernels ssad_generate dispatches to for the bench shapes (SSAD_KERNEL pins an older single-kernel path)
+KERNEL_NAME = {None: "v7 pipeline: plan, lists, pass1, canvas, finish, pass2 (_v7_kernel), timed as one step",
+               "v7": "v7 pipeline: plan, lists, pass1, canvas, finish, pass2 (_v7_kernel), timed as one step",
+               "v6": "generate_v6_kernel", "v5": "generate_v5_kernel", "cluster": "generate_cluster_kernel",
                "v3": "generate_v3_kernel", "v4": "v4 pipeline (7 kernels)", "generic": "generate_fused_kernel"}.get(os.environ.get("SSAD_KERNEL"), "?")
 
 
@@ -67,8 +69,17 @@ def make_workload(config: int, batch: int, seed: int = 0):
         mask = None
         name = "texture class, 256x256, cross-class donor bank (15), all-positive mask, RandomAffine pre-warp"
         ab = 2 * 3 * S * S
+    elif config == 4:
+        S = 1024
+        cfg = GeneratorConfig(subject="screw", imsize=(S, S))
+        uniq = 8
+        base = synth.screw_images(uniq, S, S, 1234 + config)
+        mask = None                          # per image, rebuilt on the device every step (ssad_obj_mask)
+        donors = None
+        name = "non-fixed-pose object (screw-like), 1024x1024, per-image obj_mask recompute + generation"
+        ab = 2 * 3 * S * S + 2 * S * S
     else:
-        raise SystemExit(f"config {config} is not a bench line yet")
+        raise SystemExit(f"config {config} is not a bench line")
     images = base[np.arange(batch) % uniq]
     params = sample_params(cfg, batch, np.random.default_rng(5678 + config + seed))
     return cfg, images, mask, donors, params, name, ab
@@ -127,6 +138,11 @@ class ClockSampler(threading.Thread):
 _W = {}
 
 
+def _cpu_batch(config, batch):
+    """Images each CPU worker holds: the whole batch, or a slice of it where the batch is gigabytes (config 4)."""
+    return min(batch, 16) if config == 4 else batch
+
+
 def _cpu_init(config, batch):
     """Worker start-up: one torch / BLAS thread per process (as DataLoader workers run),
     the workload, and one untimed item so that imports (sklearn, torchvision) are outside the timed region."""
@@ -138,7 +154,7 @@ def _cpu_init(config, batch):
     except Exception:
         pass
     import scenarios as S
-    cfg, images, mask, donors, params, _, _ = make_workload(config, batch)
+    cfg, images, mask, donors, params, _, _ = make_workload(config, _cpu_batch(config, batch))
     _W["sc"] = S.Scenario("bench", cfg, images, mask, donors, params)
     _cpu_run(0)
 
@@ -147,7 +163,14 @@ def _cpu_run(i):
     import scenarios as S
     from PIL import Image
     from oracle import generator as og
-    x, y, _ = S.run_oracle(_W["sc"], i)
+    sc = _W["sc"]
+    if sc.cfg.is_non_fixed and sc.mask is None:
+        # per-image obj_mask on the CPU (dataset_generator.py:27-39 as restated in oracle/objmask.py), then the item
+        from oracle import objmask
+        x, y, _ = og.generate_item(Image.fromarray(sc.images[i]), sc.params.image_draws(i), sc.cfg, None, None, objmask.obj_mask)
+        x = np.array(x)
+    else:
+        x, y, _ = S.run_oracle(sc, i)
     xn = og.to_tensor_normalize(Image.fromarray(x))      # datasets.py:392-393, part of the path
     return int(y)
 
@@ -161,11 +184,12 @@ def cpu_oracle_images_per_s(config: int, batch: int, sample: int, procs: int, ta
     with ctx.Pool(procs, initializer=_cpu_init, initargs=(config, batch)) as pool:
         def run(n):
             t0 = time.perf_counter()
-            pool.map(_cpu_run, [i % batch for i in range(n)], chunksize=max(1, n // (procs * 8)))
+            pool.map(_cpu_run, [i % _cpu_batch(config, batch) for i in range(n)], chunksize=max(1, n // (procs * 8)))
             return time.perf_counter() - t0
+        run(min(sample, 2 * procs))          # untimed: first-call costs of every worker (page faults, lazy imports)
         dt = run(sample)
         if target_s > 0:
-            sample = int(max(sample, min(20000, target_s * sample / dt)))
+            sample = int(max(sample, min(50000, target_s * sample / dt)))
             dt = run(sample)
     return sample / dt, dt, sample
 
@@ -189,13 +213,14 @@ def main():
     ap.add_argument("--out", default="u8", choices=["u8", "f32", "bf16"], help="output variant timed for `value`")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-steps", type=int, default=20)
-    ap.add_argument("--graph", type=int, default=1, help="1: replay each step's ssad_generate call from a CUDA graph")
+    ap.add_argument("--e2e-chunks", type=int, default=None, help="pieces of the batch in flight in the host-buffer call")
+    ap.add_argument("--graph", type=int, default=0, help="1: replay each step's ssad_generate call from a CUDA graph")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    batch = args.batch or {1: 96, 2: 512, 3: 1024}[args.config]
+    batch = args.batch or {1: 96, 2: 512, 3: 1024, 4: 1024}[args.config]
     metric, unit = "synthetic_anomaly_images_per_sec", "images/s"
 
     if args.impl == "reference":
@@ -204,12 +229,12 @@ def main():
         cores = host_cores()
         _, _, _, _, _, name, _ = make_workload(args.config, 8)
         # bound the run: ~90 images/s/core expected; keep (steps + warmup) * sample under ~2 min
-        per_core = 60.0
+        per_core = 1.5 if args.config == 4 else 60.0
         sample = int(max(8, min(batch, 120.0 * per_core * cores / max(1, args.steps + args.warmup))))
         import multiprocessing as mp
         ctx = mp.get_context("fork")
         with ctx.Pool(cores, initializer=_cpu_init, initargs=(args.config, batch)) as pool:
-            idx = [i % batch for i in range(sample)]
+            idx = [i % _cpu_batch(args.config, batch) for i in range(sample)]
             for _ in range(args.warmup):
                 pool.map(_cpu_run, idx, chunksize=max(1, sample // (cores * 4)))
             t0 = time.perf_counter()
@@ -248,20 +273,31 @@ def main():
         ab = ab - 3 * H * W + 6 * H * W
     # two resident input sets, alternated, so consecutive steps never touch the same lines
     # (one step already moves > L2: e.g. config 2 = 157 MB in + 100 MB out vs 126 MB L2)
-    srcs = [torch.from_numpy(images).to(dev), torch.from_numpy(np.roll(images, 1, axis=0).copy()).to(dev)]
+    srcs = [torch.from_numpy(images).to(dev)]
+    srcs.append(torch.roll(srcs[0], 1, dims=0).contiguous())
+    per_image_masks = cfg.is_non_fixed
+    mask_bufs, mask_ws = [None, None], None
+    if per_image_masks:
+        from ssad_b200.generator import obj_mask_batch
+        mask_bufs = [obj_mask_batch(srcs[j]) for j in range(2)]
+        mask_ws = torch.empty((int(gen.lib.ssad_obj_mask_workspace(batch, images.shape[1], images.shape[2])) + 16,),
+                              dtype=torch.uint8, device=dev)
     pdev = gen.upload_params(params)
     outs_u8 = [torch.empty((batch, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)] if want_u8 else [None, None]
     outs_n = [torch.empty((batch, 3, H, W), dtype=norm_dtype, device=dev) for _ in range(2)] if norm_dtype else [None, None]
     y_out = torch.empty((batch,), dtype=torch.int64, device=dev)
 
-    plans = [gen.plan(srcs[j], params, want_u8=want_u8, norm_dtype=norm_dtype, params_dev=pdev,
+    plans = [gen.plan(srcs[j], params, masks=mask_bufs[j], want_u8=want_u8, norm_dtype=norm_dtype, params_dev=pdev,
                       out_u8=outs_u8[j], out_norm=outs_n[j], y_out=y_out) for j in range(2)]
+    launches_per_step = int(gen.lib.ssad_generate_launches(plans[0].args[0])) + (2 if per_image_masks else 0)
 
     if args.graph:
         for pl in plans:
             gen.capture(pl)                      # one cudaGraphLaunch per step instead of a dozen kernel launches
 
     def step(i):
+        if per_image_masks:                  # obj_mask of every image of the batch, then the generator (datasets.py:232-233)
+            obj_mask_batch(srcs[i & 1], out=mask_bufs[i & 1], workspace=mask_ws)
         gen.run(plans[i & 1])
 
     def barrier():
@@ -288,22 +324,30 @@ def main():
         ms = float(t.item())
     ms_per_step = ms / args.steps
     value = world * batch / (ms_per_step * 1e-3)
+    parts = None
+    if per_image_masks:                      # mask builder and generator on their own
+        parts = {}
+        for nm, fn in (("obj_mask_ms", lambda i: obj_mask_batch(srcs[i & 1], out=mask_bufs[i & 1], workspace=mask_ws)),
+                       ("generate_ms", lambda i: gen.run(plans[i & 1]))):
+            barrier()
+            e0.record()
+            for i in range(args.steps):
+                fn(i)
+            e1.record()
+            barrier()
+            parts[nm] = e0.elapsed_time(e1) / args.steps
 
     # ---- e2e: host buffers in, host buffers out, copies inside the timed region
-    h_src = [torch.from_numpy(images).pin_memory(), torch.from_numpy(np.roll(images, 1, axis=0).copy()).pin_memory()]
+    h_src = [torch.from_numpy(images).pin_memory()]
+    h_src.append(h_src[0] if images.nbytes > (1 << 30) else torch.from_numpy(np.roll(images, 1, axis=0).copy()).pin_memory())
     h_out = torch.empty((batch, H, W, 3), dtype=torch.uint8).pin_memory()
     h_y = torch.empty((batch,), dtype=torch.int64).pin_memory()
-    d_src = torch.empty_like(srcs[0])
-    d_out = torch.empty((batch, H, W, 3), dtype=torch.uint8, device=dev)
     rec_bytes = params.records.nbytes
+    masks_fn = (lambda t: obj_mask_batch(t)) if per_image_masks else None
 
     def e2e_step(i):
-        d_src.copy_(h_src[i & 1], non_blocking=True)
-        p = gen.upload_params(params)
-        gen.generate(d_src, params, want_u8=True, norm_dtype=None, params_dev=p, out_u8=d_out, y_out=y_out)
-        h_out.copy_(d_out, non_blocking=True)
-        h_y.copy_(y_out, non_blocking=True)
-        torch.cuda.current_stream().synchronize()      # the caller owns the result when the call returns
+        # the public host-buffer call: chunks of the batch flow through H2D copy -> ssad_generate -> D2H copy streams
+        gen.generate_from_host(h_src[i & 1], params, h_out, h_y, chunks=args.e2e_chunks, masks_fn=masks_fn)
 
     for i in range(3):
         e2e_step(i)
@@ -348,7 +392,8 @@ def main():
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s"},
         "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(images.nbytes + rec_bytes),
                 "d2h_bytes_per_step": int(h_out.numel() + h_y.numel() * 8), "steps": args.e2e_steps},
-        "gpu_launches": args.steps,
+        "gpu_launches": args.steps * launches_per_step,
+        **({"parts": parts} if parts else {}),
         "clocks": clocks,
     }
     if world == 1 and not args.no_cpu:

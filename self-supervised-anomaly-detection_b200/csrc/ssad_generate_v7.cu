@@ -94,7 +94,10 @@ __device__ __forceinline__ int kind_of_ops(const int32_t* ops, int i0, int i1) {
 // Fast path: NT % upr == 0 (a thread keeps its unit column: the byte alignment is a loop invariant, pointers advance by
 // constants) and the slab holds exactly NT * UPT units (no bounds test).  Every thread announces all its units to the
 // L2 up front (prefetch.global.L2), then keeps one unit of loads in flight in registers.
-constexpr int UPT = 8;
+#ifndef SSAD_V7_UPT_FAST
+#define SSAD_V7_UPT_FAST 8
+#endif
+constexpr int UPT = SSAD_V7_UPT_FAST;
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
@@ -572,8 +575,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     pdl_wait();
     const int y0 = S->D.y;                       // (uniform over the CTA)
     if (y0 == 0) return;
-    // a polygon's canvas is shared by all NC CTAs of the image, the small scar canvas by a quarter of them
-    const int nparts = (y0 == 1) ? g.ncanvas : max(1, g.ncanvas / 2);
+    const int nparts = g.ncanvas;                // CTAs that share the image's canvas
     if (part >= nparts) return;
     if (tid < (int)(sizeof(SsadImageParams) / 4))
         reinterpret_cast<uint32_t*>(&P)[tid] = reinterpret_cast<const uint32_t*>(params + b)[tid];
@@ -913,7 +915,7 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.nslab = (g.H + g.rows_slab - 1) / g.rows_slab;
     g.fast = (NT % g.upr == 0 && upt == UPT && g.rows_slab * g.upr == NT * UPT && g.H % g.rows_slab == 0) ? 1 : 0;
     if (getenv("SSAD_V7_NOFAST")) g.fast = 0;
-    g.ncanvas = 8;
+    g.ncanvas = 4;
     if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
     g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;
     g.cov_rows = (uint32_t)d.max_patch_h;

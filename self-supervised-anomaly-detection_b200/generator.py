@@ -226,6 +226,57 @@ class BatchGenerator:
         return out
 
 
+    # ------------------------------------------------------------------ host buffers in, host buffers out
+    def generate_from_host(self, h_src: torch.Tensor, params: ParamBatch, h_out: torch.Tensor, h_y: torch.Tensor, *,
+                           chunks: Optional[int] = None, masks_fn=None) -> None:
+        """The end-to-end call for data that lives in (pinned) host memory: uint8 images ``h_src`` [B, Hs, Ws, 3] ->
+        ``h_out`` uint8 [B, h, w, 3] and labels ``h_y`` int64 [B], all host tensors.  The batch is cut into ``chunks``
+        pieces that flow through three streams -- host-to-device copy, generation (``ssad_generate``), device-to-host
+        copy -- so the two PCIe directions and the kernels overlap.  Returns when the results are in host memory.
+        ``masks_fn(d_src_chunk) -> packed masks`` supplies per-image masks (non-fixed classes: ``obj_mask_batch``)."""
+        B = int(h_src.shape[0])
+        W, H = self.cfg.work_size
+        if chunks is None:
+            chunks = min(8, B // 64)             # pieces of at least 64 images, eight at most
+        chunks = max(1, min(int(chunks), B))
+        st = self._host_pipe(B, tuple(h_src.shape[1:]), chunks)
+        cur = torch.cuda.current_stream(self.device)
+        for s_ in (st["up"], st["run"], st["down"]):
+            s_.wait_stream(cur)
+        bounds = [(B * c // chunks, B * (c + 1) // chunks) for c in range(chunks)]
+        for c, (lo, hi) in enumerate(bounds):
+            d_src, d_out, d_y = st["src"][lo:hi], st["out"][lo:hi], st["y"][lo:hi]
+            with torch.cuda.stream(st["up"]):
+                d_src.copy_(h_src[lo:hi], non_blocking=True)
+                st["ev_up"][c].record(st["up"])
+            with torch.cuda.stream(st["run"]):
+                st["run"].wait_event(st["ev_up"][c])
+                sub = params.slice(lo, hi)
+                m = masks_fn(d_src) if masks_fn is not None else None
+                self.generate(d_src, sub, masks=m, want_u8=True, norm_dtype=None, out_u8=d_out, y_out=d_y)
+                st["ev_run"][c].record(st["run"])
+            with torch.cuda.stream(st["down"]):
+                st["down"].wait_event(st["ev_run"][c])
+                h_out[lo:hi].copy_(d_out, non_blocking=True)
+                h_y[lo:hi].copy_(d_y, non_blocking=True)
+        st["down"].synchronize()                 # the caller owns the results when the call returns
+        cur.wait_stream(st["up"]); cur.wait_stream(st["run"])
+
+    def _host_pipe(self, B: int, src_shape: tuple, chunks: int) -> dict:
+        key = (B, src_shape, chunks)
+        st = getattr(self, "_pipe", None)
+        if st is None or st["key"] != key:
+            W, H = self.cfg.work_size
+            dev = self.device
+            st = {"key": key, "up": torch.cuda.Stream(dev), "run": torch.cuda.Stream(dev), "down": torch.cuda.Stream(dev),
+                  "src": torch.empty((B,) + src_shape, dtype=torch.uint8, device=dev),
+                  "out": torch.empty((B, H, W, 3), dtype=torch.uint8, device=dev),
+                  "y": torch.empty((B,), dtype=torch.int64, device=dev),
+                  "ev_up": [torch.cuda.Event() for _ in range(chunks)], "ev_run": [torch.cuda.Event() for _ in range(chunks)]}
+            self._pipe = st
+        return st
+
+
 # ---------------------------------------------------------------------- obj_mask on device
 def canny_consts(sigma: float = 1.5, low_threshold: float = 5, high_threshold: float = 15) -> "N.SsadCannyConsts":
     """Constants of ``canny(gray, sigma=1.5, low_threshold=5, high_threshold=15)`` (dataset_generator.py:30) for a

@@ -193,3 +193,30 @@ def test_graph_replay_matches_plain_launch(name, split, monkeypatch):
         assert torch.equal(plan.out_u8, ref["x_u8"])
         assert torch.equal(plan.out_norm, ref["x"])
         assert torch.equal(plan.y_out, ref["y"])
+
+
+@pytest.mark.parametrize("chunks", [1, 3])
+@pytest.mark.parametrize("name", ["image_level_256", "patch_level", "non_fixed"])
+def test_host_buffer_pipeline_matches_device_call(name, chunks):
+    """generate_from_host: pinned host images in, host results out, the batch pipelined through copy / generate /
+    copy streams -- same bytes as the device-resident call."""
+    import gpu_utils as U
+    from ssad_b200.generator import pack_mask_bits
+    sc = S.build(name, 12)
+    gen = U.make_generator(sc)
+    ref = U.run_cuda(sc, norm_dtype=None, debug=False, gen=gen)
+    h_src = torch.from_numpy(sc.images).pin_memory()
+    W, H = sc.cfg.work_size
+    h_out = torch.zeros((12, H, W, 3), dtype=torch.uint8).pin_memory()
+    h_y = torch.zeros((12,), dtype=torch.int64).pin_memory()
+    masks_fn = None
+    if sc.mask is not None and sc.mask.ndim == 3:
+        all_masks = U.per_image_masks(sc)
+        state = {"lo": 0}
+
+        def masks_fn(d_src):                     # the scenario's own masks, chunk by chunk
+            lo = state["lo"]; state["lo"] = lo + d_src.shape[0]
+            return all_masks[lo:lo + d_src.shape[0]]
+    gen.generate_from_host(h_src, sc.params, h_out, h_y, chunks=chunks, masks_fn=masks_fn)
+    assert torch.equal(h_out, ref["x_u8"].cpu())
+    assert torch.equal(h_y, ref["y"].cpu())
