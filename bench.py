@@ -214,7 +214,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--e2e-chunks", type=int, default=None, help="pieces of the batch in flight in the host-buffer call")
-    ap.add_argument("--graph", type=int, default=0, help="1: replay each step's ssad_generate call from a CUDA graph")
+    ap.add_argument("--graph", type=int, default=1, help="1: replay each step's ssad_generate call from a CUDA graph")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -289,7 +289,7 @@ def main():
 
     plans = [gen.plan(srcs[j], params, masks=mask_bufs[j], want_u8=want_u8, norm_dtype=norm_dtype, params_dev=pdev,
                       out_u8=outs_u8[j], out_norm=outs_n[j], y_out=y_out) for j in range(2)]
-    launches_per_step = int(gen.lib.ssad_generate_launches(plans[0].args[0])) + (2 if per_image_masks else 0)
+    launches_per_step = int(gen.lib.ssad_generate_launches(plans[0].args[0], int(bool(args.graph)))) + (2 if per_image_masks else 0)
 
     if args.graph:
         for pl in plans:

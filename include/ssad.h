@@ -142,8 +142,9 @@ int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, cons
                   void* workspace, size_t workspace_bytes, void* stream);
 size_t ssad_generate_workspace(const SsadBatchDesc* desc);
 /* Number of kernels one ssad_generate call launches for this descriptor (the kernel pipeline cuts large batches into
- * chunks that run side by side on helper streams forked from, and joined back to, the caller's stream). */
-int ssad_generate_launches(const SsadBatchDesc* desc);
+ * chunks that run side by side on helper streams forked from, and joined back to, the caller's stream; a call that
+ * is being captured into a CUDA graph -- captured != 0 -- uses more chunks than a plainly launched one). */
+int ssad_generate_launches(const SsadBatchDesc* desc, int captured);
 
 /* Host-computed constants of skimage.feature.canny(image, sigma=1.5, low_threshold=5, high_threshold=15) as
  * obj_mask calls it (dataset_generator.py:30).  They are inputs (not computed by the library) because the Gaussian

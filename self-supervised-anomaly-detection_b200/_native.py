@@ -45,7 +45,7 @@ EXPORTS = {
     "ssad_sizeof_debug": (C.c_size_t, []),
     "ssad_generate": (C.c_int, [C.POINTER(SsadBatchDesc)] + [C.c_void_p] * 10 + [C.c_size_t, C.c_void_p]),
     "ssad_generate_workspace": (C.c_size_t, [C.POINTER(SsadBatchDesc)]),
-    "ssad_generate_launches": (C.c_int, [C.POINTER(SsadBatchDesc)]),
+    "ssad_generate_launches": (C.c_int, [C.POINTER(SsadBatchDesc), C.c_int]),
     "ssad_obj_mask": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                 C.c_int32, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
     "ssad_obj_mask_workspace": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),

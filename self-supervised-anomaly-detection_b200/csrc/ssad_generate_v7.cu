@@ -38,6 +38,7 @@ using namespace v6;
 using namespace u8x;
 
 constexpr int NKIND = 6;         // LK_COPY .. LK_SAT_LL
+constexpr int kCanvasRows = 512; // canvas rows one CTA of the canvas kernel can own
 
 struct ImgState {                // per image, global memory
     Plan D;
@@ -567,6 +568,8 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     __shared__ Tables TP;
     __shared__ uint8_t simtab[256];
     __shared__ uint32_t red[NWARP * 8 + 8];
+    __shared__ uint16_t row_lo[kCanvasRows];     // first covered column of this CTA's canvas rows
+    __shared__ uint32_t row_pre[kCanvasRows + 1];   // covered-span pixels in the rows before
     const int tid = threadIdx.x;
     const int b = (int)(blockIdx.x / (unsigned)g.ncanvas), part = (int)(blockIdx.x - (unsigned)b * g.ncanvas);
     const int H = g.H, W = g.W, npix = H * W;
@@ -641,14 +644,49 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     if (my_lo >= my_hi) return;
     const int cpitch = (int)g.canvas_pitch;
     const bool want_l = cpos >= 0;
-    const uint32_t inv_bw = 0xFFFFFFFFu / (uint32_t)bw + 1u;        // idx / bw == umulhi(idx, inv_bw) for idx * bw < 2^32
     uint32_t dl = 0;                             // sum of L(new) - L(old) over the pixels this CTA pastes
+    // Only the covered span [first set bit, last set bit] of every canvas row is visited (a rotated scar covers a third
+    // of its box): spans -> prefix over the rows -> item idx of the flattened spans -> (row, column) by bisection.
+    const int nrows = my_hi - my_lo;
+    for (int r = tid; r < nrows; r += NT) {
+        const uint32_t* crow = cov + (size_t)(my_lo + r) * pitchw;
+        int lo = -1, hi = -1;
+        for (int j = 0; j < pitchw; ++j) {
+            const uint32_t wv = crow[j];
+            if (wv) { if (lo < 0) lo = 32 * j + __ffs(wv) - 1; hi = 32 * j + 31 - __clz(wv); }
+        }
+        lo = min(max(lo, 0), max(bw - 1, 0)); hi = min(hi, bw - 1);
+        row_lo[r] = (uint16_t)lo;
+        row_pre[r + 1] = (hi >= lo && hi >= 0) ? (uint32_t)(hi - lo + 1) : 0u;
+    }
+    __syncthreads();
+    if (tid < 32) {
+        uint32_t carry = 0;
+        for (int base = 0; base < nrows; base += 32) {
+            const int r = base + tid;
+            uint32_t sv = (r < nrows) ? row_pre[r + 1] : 0u;
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, sv, o);
+                if (tid >= o) sv += t;
+            }
+            if (r < nrows) row_pre[r + 1] = carry + sv;
+            carry += __shfl_sync(0xFFFFFFFFu, sv, 31);
+        }
+        if (tid == 0) row_pre[0] = 0;
+    }
+    __syncthreads();
+    const int span_total = (int)row_pre[nrows];
+    auto locate = [&](int idx, int& u, int& v) {
+        int lo = 0, hi = nrows;
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((int)row_pre[mid] <= idx) lo = mid; else hi = mid; }
+        v = my_lo + lo; u = (int)row_lo[lo] + idx - (int)row_pre[lo];
+    };
     if (y == 1) {
         // polygon: one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
         // thread and round, their loads issued together: the chain coverage word -> cut pixel -> old pixel is three
         // memory latencies long, and nothing else hides it.
         constexpr int NB = 4;
-        const int total = (my_hi - my_lo) * bw;
+        const int total = span_total;
         const int pl = D.paste[0][0], pt = D.paste[0][1];
         const bool read_cut = !K.flat;
         for (int idx0 = tid; idx0 < total; idx0 += NT * NB) {
@@ -656,9 +694,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
             uint32_t cw[NB];
             #pragma unroll
             for (int j = 0; j < NB; ++j) {
-                const int idx = min(idx0 + j * NT, total - 1);
-                const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw);
-                uu[j] = idx - vr * bw; vv[j] = my_lo + vr;
+                locate(min(idx0 + j * NT, total - 1), uu[j], vv[j]);
                 cw[j] = cov[(size_t)vv[j] * pitchw + (uu[j] >> 5)];
             }
             bool on[NB];
@@ -702,9 +738,9 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
             }
         }
     } else {
-        const int total = (my_hi - my_lo) * bw;
-        for (int idx = tid; idx < total; idx += NT) {
-            const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - vr * bw, v = my_lo + vr;
+        for (int idx = tid; idx < span_total; idx += NT) {
+            int u, v;
+            locate(idx, u, v);
             if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
             uint32_t r, gg, bl;
             if (K.flat) { r = K.frgb[0]; gg = K.frgb[1]; bl = K.frgb[2]; }
@@ -752,7 +788,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     // their loads issued together
     if (y == 2) {
         constexpr int NB = 4;
-        const int box = (my_hi - my_lo) * bw, total = npaste * box;
+        const int box = max(span_total, 1), total = npaste * span_total;
         for (int id0 = tid; id0 < total; id0 += NT * NB) {
             bool on[NB];
             uint8_t* qx[NB];
@@ -761,7 +797,8 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
             for (int j = 0; j < NB; ++j) {
                 const int id = min(id0 + j * NT, total - 1);
                 const int k = id / box, idx = id - k * box;
-                const int vr = (bw == 1) ? idx : (int)__umulhi((uint32_t)idx, inv_bw), u = idx - vr * bw, v = my_lo + vr;
+                int u, v;
+                locate(idx, u, v);
                 const int X = D.paste[k][0] + u, Y = D.paste[k][1] + v;
                 bool ok = (id0 + j * NT < total) && X >= 0 && X < W && Y >= 0 && Y < H &&
                           ((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u);
@@ -917,6 +954,7 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     if (getenv("SSAD_V7_NOFAST")) g.fast = 0;
     g.ncanvas = 4;
     if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
+    while ((d.max_patch_h + g.ncanvas - 1) / g.ncanvas > kCanvasRows) ++g.ncanvas;
     g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;
     g.cov_rows = (uint32_t)d.max_patch_h;
     g.cov_stride = (size_t)g.cov_pitch * g.cov_rows;
@@ -939,28 +977,34 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
 // The batch is cut into chunks that run the kernel pipeline side by side: chunk 0 on the caller's stream, the others on
 // helper streams forked from it and joined back before the call returns (events; legal under stream capture).  The short
 // latency-bound kernels of one chunk (plan, lists, canvas, finish) then overlap the streaming passes of another.
-static int v7_chunks(int batch) {
-    int n = (batch >= 256) ? 2 : 1;
+// Chunks per call: 2 for plain launches (more would make the host the bottleneck: every chunk is 6 launches), 4 when the
+// call is being captured into a CUDA graph (one cudaGraphLaunch replays everything); SSAD_V7_SPLIT pins a number.
+static int v7_chunks(int batch, bool capturing) {
+    int n = (batch >= 256) ? (capturing ? 4 : 2) : 1;
     if (const char* f = getenv("SSAD_V7_SPLIT")) { int v = atoi(f); if (v >= 1 && v <= 8) n = v; }
     if (n > batch) n = batch;
     return n < 1 ? 1 : n;
 }
-static int v7_chunk_size(int batch) { const int n = v7_chunks(batch); return (batch + n - 1) / n; }
-
-size_t ssad_v7_workspace(const SsadBatchDesc& d) {
+static size_t v7_chunk_workspace(const SsadBatchDesc& d, int nchunk) {
     ssad::v7::Geo7 g;
     SsadBatchDesc dc = d;
-    dc.batch = v7_chunk_size(d.batch);
+    dc.batch = (d.batch + nchunk - 1) / nchunk;
     if (!ssad::v7::make_geo7(dc, g)) return 0;
-    return g.ws_total * (size_t)v7_chunks(d.batch);
+    return g.ws_total;
+}
+
+size_t ssad_v7_workspace(const SsadBatchDesc& d) {           // enough for either number of chunks
+    const int n0 = v7_chunks(d.batch, false), n1 = v7_chunks(d.batch, true);
+    const size_t a = v7_chunk_workspace(d, n0) * (size_t)n0, b = v7_chunk_workspace(d, n1) * (size_t)n1;
+    return a > b ? a : b;
 }
 
 // kernels one ssad_generate call launches on this path (bench.py's gpu_launches)
-int ssad_v7_launches(int batch) { return 6 * v7_chunks(batch); }
+int ssad_v7_launches(int batch, bool capturing) { return 6 * v7_chunks(batch, capturing); }
 
 static int launch_v7_chunk(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
                            const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
-                           SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+                           SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream, bool use_pdl);
 
 struct V7Streams {               // helper streams and fork/join events of one device, created on first use
     cudaStream_t s[8];
@@ -987,14 +1031,19 @@ static V7Streams* v7_streams() {
 int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
                    const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
                    SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
-    const int nchunk = v7_chunks(d.batch), csize = v7_chunk_size(d.batch);
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) { cap = cudaStreamCaptureStatusNone; (void)cudaGetLastError(); }
+    const bool capturing = cap == cudaStreamCaptureStatusActive;
+    // programmatic dependent launch pays on plain streams; inside a graph the programmatic edges cost more than they hide
+    const bool use_pdl = !capturing && getenv("SSAD_V7_NOPDL") == nullptr;
+    const int nchunk = v7_chunks(d.batch, capturing), csize = (d.batch + nchunk - 1) / nchunk;
     const size_t need = ssad_v7_workspace(d);
     if (need == 0) return SSAD_EUNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(src) & 15) || (d.src_pitch & 7) || (d.src_stride & 7)) return SSAD_EUNSUPPORTED;
     if (nchunk > 1 && (d.src_stride & 15)) return SSAD_EUNSUPPORTED;      // every chunk's first image must stay 16-byte aligned
     if (!workspace || workspace_bytes < need) return SSAD_EWORKSPACE;
     if (reinterpret_cast<uintptr_t>(workspace) & 255) return SSAD_EALIGN;
-    const size_t ws_chunk = need / (size_t)nchunk;
+    const size_t ws_chunk = v7_chunk_workspace(d, nchunk);
     V7Streams* const HS = (nchunk > 1) ? v7_streams() : nullptr;
     if (nchunk > 1 && !HS) return SSAD_ELAUNCH;
     cudaError_t e = cudaSuccess;
@@ -1018,7 +1067,7 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
                              out_u8 ? out_u8 + (size_t)b0 * d.out_u8_stride : nullptr,
                              out_norm ? static_cast<uint8_t*>(out_norm) + (size_t)b0 * 3 * npix * norm_elem : nullptr,
                              y_out ? y_out + b0 : nullptr, debug ? debug + b0 : nullptr,
-                             static_cast<uint8_t*>(workspace) + (size_t)c * ws_chunk, ws_chunk, st);
+                             static_cast<uint8_t*>(workspace) + (size_t)c * ws_chunk, ws_chunk, st, use_pdl);
         if (rc != SSAD_OK) break;
     }
     // join (also after a failed launch: the helper streams must not stay forked inside a capture)
@@ -1032,7 +1081,7 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
 
 static int launch_v7_chunk(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
                            const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
-                           SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+                           SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream, bool use_pdl) {
     using namespace ssad::v7;
     Geo7 g;
     if (!make_geo7(d, g)) return SSAD_EUNSUPPORTED;
@@ -1051,7 +1100,6 @@ static int launch_v7_chunk(const SsadBatchDesc& d, const SsadImageParams* params
     const unsigned B = (unsigned)d.batch;
     cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(Sched), stream);
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
-    static const bool use_pdl = getenv("SSAD_V7_NOPDL") == nullptr;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;

@@ -51,7 +51,7 @@ def test_argument_validation_happens_on_the_host():
     d.batch, d.height, d.width, d.src_pitch = 1, 8, 8, 8          # pitch < 3 * width
     assert lib.ssad_generate(C.byref(d), C.c_void_p(16), C.c_void_p(16), *([None] * 8), 0, None) == -1
     assert lib.ssad_generate_workspace(None) == 0
-    assert lib.ssad_generate_launches(None) == 0
+    assert lib.ssad_generate_launches(None, 0) == 0
     with pytest.raises(ValueError):
         _native.check(-1, "x")
     with pytest.raises(RuntimeError):
