@@ -214,6 +214,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--e2e-chunks", type=int, default=None, help="pieces of the batch in flight in the host-buffer call")
+    ap.add_argument("--inflight", type=int, default=2, help="batches in flight: steps alternate between this many streams (1|2)")
     ap.add_argument("--graph", type=int, default=1, help="1: replay each step's ssad_generate call from a CUDA graph")
     args = ap.parse_args()
 
@@ -280,8 +281,8 @@ def main():
     if per_image_masks:
         from ssad_b200.generator import obj_mask_batch
         mask_bufs = [obj_mask_batch(srcs[j]) for j in range(2)]
-        mask_ws = torch.empty((int(gen.lib.ssad_obj_mask_workspace(batch, images.shape[1], images.shape[2])) + 16,),
-                              dtype=torch.uint8, device=dev)
+        mask_ws = [torch.empty((int(gen.lib.ssad_obj_mask_workspace(batch, images.shape[1], images.shape[2])) + 16,),
+                               dtype=torch.uint8, device=dev) for _ in range(2)]
     pdev = gen.upload_params(params)
     outs_u8 = [torch.empty((batch, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)] if want_u8 else [None, None]
     outs_n = [torch.empty((batch, 3, H, W), dtype=norm_dtype, device=dev) for _ in range(2)] if norm_dtype else [None, None]
@@ -297,7 +298,7 @@ def main():
 
     def step(i):
         if per_image_masks:                  # obj_mask of every image of the batch, then the generator (datasets.py:232-233)
-            obj_mask_batch(srcs[i & 1], out=mask_bufs[i & 1], workspace=mask_ws)
+            obj_mask_batch(srcs[i & 1], out=mask_bufs[i & 1], workspace=mask_ws[i & 1])
         gen.run(plans[i & 1])
 
     def barrier():
@@ -305,31 +306,53 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # Batches in flight: consecutive steps alternate between `--inflight` streams (each step = the complete hot path over
+    # one batch, with its own input set, outputs and workspace), the way a loader keeps a second batch in preparation
+    # while the consumer takes the first.  --inflight 1 issues every step on one stream (also timed, `serial` below).
+    cur = torch.cuda.current_stream(dev)
+    lanes = [torch.cuda.Stream(dev) for _ in range(max(1, min(2, args.inflight)))]
+
+    def timed(nsteps, use_lanes):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(cur)
+        if use_lanes and len(lanes) > 1:
+            for ln in lanes:
+                ln.wait_stream(cur)
+            for i in range(nsteps):
+                with torch.cuda.stream(lanes[i & 1]):
+                    step(i)
+            for ln in lanes:
+                cur.wait_stream(ln)
+        else:
+            for i in range(nsteps):
+                step(i)
+        e1.record(cur)
+        barrier()
+        return e0.elapsed_time(e1)
+
     for i in range(max(args.warmup, 3)):
         step(i)
     barrier()
+    timed(max(args.warmup, 3), True)         # warm the lanes too
+    ms_serial = timed(args.steps, False)
     sampler = ClockSampler(local_rank)
     sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        step(i)
-    e1.record()
-    barrier()
+    ms = timed(args.steps, True)
     clocks = sampler.stop()
-    ms = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     ms_per_step = ms / args.steps
     value = world * batch / (ms_per_step * 1e-3)
+    serial_ms_per_step = ms_serial / args.steps
     parts = None
     if per_image_masks:                      # mask builder and generator on their own
         parts = {}
-        for nm, fn in (("obj_mask_ms", lambda i: obj_mask_batch(srcs[i & 1], out=mask_bufs[i & 1], workspace=mask_ws)),
+        for nm, fn in (("obj_mask_ms", lambda i: obj_mask_batch(srcs[i & 1], out=mask_bufs[i & 1], workspace=mask_ws[i & 1])),
                        ("generate_ms", lambda i: gen.run(plans[i & 1]))):
             barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             for i in range(args.steps):
                 fn(i)
@@ -386,6 +409,7 @@ def main():
         "dtype": "u8", "data": "synthetic",
         "config": {"workload": name, "batch_per_gpu": batch, "global_batch": batch * world, "output": args.out,
                    "l2": "two alternating resident input/output sets; one step moves more than the 126 MB L2",
+                   "inflight": len(lanes), "cuda_graph": bool(args.graph),
                    "parallelism": f"image-sharded x{world}, no collective"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "kernel": KERNEL_NAME, "algorithmic_bytes_per_image": ab,
@@ -393,6 +417,8 @@ def main():
         "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(images.nbytes + rec_bytes),
                 "d2h_bytes_per_step": int(h_out.numel() + h_y.numel() * 8), "steps": args.e2e_steps},
         "gpu_launches": args.steps * launches_per_step,
+        "serial": {"ms_per_step": serial_ms_per_step, "value": world * batch / (serial_ms_per_step * 1e-3),
+                   "note": "the same K steps issued on ONE stream (a step starts when the previous one has finished)"},
         **({"parts": parts} if parts else {}),
         "clocks": clocks,
     }

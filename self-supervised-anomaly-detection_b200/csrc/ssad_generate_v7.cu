@@ -676,10 +676,12 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     }
     __syncthreads();
     const int span_total = (int)row_pre[nrows];
+    // a thread's items go up through the rows (by NT items at a time): walk from the row of the previous item
+    int row_at = 0;
     auto locate = [&](int idx, int& u, int& v) {
-        int lo = 0, hi = nrows;
-        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((int)row_pre[mid] <= idx) lo = mid; else hi = mid; }
-        v = my_lo + lo; u = (int)row_lo[lo] + idx - (int)row_pre[lo];
+        if ((int)row_pre[row_at] > idx) row_at = 0;
+        while ((int)row_pre[row_at + 1] <= idx) ++row_at;
+        v = my_lo + row_at; u = (int)row_lo[row_at] + idx - (int)row_pre[row_at];
     };
     if (y == 1) {
         // polygon: one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
