@@ -415,6 +415,25 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
 
 
 // ================================================================ lists
+// CTA-wide sums of NV counters with one REDUX per counter and warp: thread i < NV returns the total of counter i.
+// `red` must not be in use by other warps of the CTA (it is written without a leading barrier).
+template <int NV>
+__device__ __forceinline__ uint32_t block_sum_to(uint32_t (&v)[NV], uint32_t* red /* NWARP * 8 words */) {
+    #pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = __reduce_add_sync(0xFFFFFFFFu, v[i]);
+    if ((threadIdx.x & 31) == 0) {
+        #pragma unroll
+        for (int i = 0; i < NV; ++i) red[(threadIdx.x >> 5) * 8 + i] = v[i];
+    }
+    __syncthreads();
+    uint32_t t = 0;
+    if (threadIdx.x < NV) {
+        #pragma unroll
+        for (int w = 0; w < NWARP; ++w) t += red[w * 8 + threadIdx.x];
+    }
+    return t;
+}
+
 // slot of every image in the kind-ordered lists of the two passes (thread per image)
 __global__ void __launch_bounds__(NT)
 lists_v7_kernel(const __grid_constant__ Geo7 g, const SsadImageParams* __restrict__ params,
@@ -551,10 +570,8 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
             }
         }
     }
-    block_sum_vec<7>(acc, red);
-    #pragma unroll
-    for (int i = 0; i < 7; ++i)
-        if (tid == i && acc[i] != 0) atomicAdd(&S->acc[i], acc[i]);
+    const uint32_t tot = block_sum_to<7>(acc, red);
+    if (tid < 7 && tot != 0) atomicAdd(&S->acc[tid], tot);
 }
 
 // ================================================================ canvas
@@ -836,8 +853,8 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     }
     if (!want_l) return;
     uint32_t v1[1] = {dl};
-    block_sum_vec<1>(v1, red);
-    if (tid == 0 && v1[0] != 0) atomicAdd(&S->acc[7], v1[0]);
+    const uint32_t tot = block_sum_to<1>(v1, red);
+    if (tid == 0 && tot != 0) atomicAdd(&S->acc[7], tot);
 }
 
 // ================================================================ finish
@@ -954,7 +971,7 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.nslab = (g.H + g.rows_slab - 1) / g.rows_slab;
     g.fast = (NT % g.upr == 0 && upt == UPT && g.rows_slab * g.upr == NT * UPT && g.H % g.rows_slab == 0) ? 1 : 0;
     if (getenv("SSAD_V7_NOFAST")) g.fast = 0;
-    g.ncanvas = 4;
+    g.ncanvas = d.batch >= 1024 ? 1 : 2;         // per chunk; measured: fewer, longer canvas CTAs win once the grid fills the GPU
     if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
     while ((d.max_patch_h + g.ncanvas - 1) / g.ncanvas > kCanvasRows) ++g.ncanvas;
     g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;
