@@ -535,7 +535,7 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
                    const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
                    SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 size_t ssad_v7_workspace(const SsadBatchDesc& d);
-int ssad_v7_launches(int batch, bool capturing);
+int ssad_v7_launches(const SsadBatchDesc& d, bool capturing);
 
 int ssad_set_cuda_error(cudaError_t e) {
     strncpy(g_cuda_err, cudaGetErrorString(e), sizeof(g_cuda_err) - 1);
@@ -554,7 +554,7 @@ extern "C" size_t ssad_generate_workspace(const SsadBatchDesc* desc) {
 extern "C" int ssad_generate_launches(const SsadBatchDesc* desc, int captured) {
     if (!desc || desc->batch <= 0) return 0;
     const char* force = getenv("SSAD_KERNEL");
-    if ((!force || strcmp(force, "v7") == 0) && ssad_v7_workspace(*desc) > 0) return ssad_v7_launches(desc->batch, captured != 0);
+    if ((!force || strcmp(force, "v7") == 0) && ssad_v7_workspace(*desc) > 0) return ssad_v7_launches(*desc, captured != 0);
     if (force && strcmp(force, "v4") == 0) return 7;
     return 1;
 }

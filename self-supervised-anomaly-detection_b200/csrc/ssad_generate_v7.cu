@@ -66,6 +66,8 @@ struct Geo7 {
     size_t canvas_stride, cov_stride;                       // words per image
     size_t o_canvas, o_state, o_cov, o_sched, o_hdr, ws_total;   // byte offsets in the workspace (x buffer at 0)
     int fast;                                               // NT % upr == 0 and every slab holds NT * UPT units
+    int nslab_shift;                                        // log2(nslab), or -1
+    uint32_t inv_upr;                                       // ceil(2^16 / upr): tid / upr == tid * inv_upr >> 16 for tid < 256
     uint32_t smem_plan;                                     // dynamic shared memory of the plan kernel (row prefix)
 };
 
@@ -185,9 +187,10 @@ struct FastCol {                // a thread's unit column in the fast path
     int rr0, cu, dr;
     uint32_t mis;
 };
-__device__ __forceinline__ FastCol fast_col(const uint8_t* in0, int in_pitch, int upr, int tid) {
+__device__ __forceinline__ FastCol fast_col(const uint8_t* in0, int in_pitch, const Geo7& g, int tid) {
     FastCol F;
-    F.rr0 = tid / upr; F.cu = tid - F.rr0 * upr; F.dr = NT / upr;
+    const int upr = g.upr;
+    F.rr0 = (int)(((uint32_t)tid * g.inv_upr) >> 16); F.cu = tid - F.rr0 * upr; F.dr = g.rows_slab / UPT;   // NT / upr
     const uint8_t* ip = in0 + (size_t)F.rr0 * in_pitch + F.cu * 24;
     F.mis = (uint32_t)(reinterpret_cast<uintptr_t>(ip) & 7u);
     F.ip = ip - F.mis;
@@ -471,7 +474,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     __shared__ Tables TP;
     __shared__ uint32_t red[NWARP * 8 + 8];
     const int tid = threadIdx.x;
-    const uint32_t j = blockIdx.x / (unsigned)g.nslab;
+    const uint32_t j = g.nslab_shift >= 0 ? blockIdx.x >> g.nslab_shift : blockIdx.x / (unsigned)g.nslab;
     const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
     pdl_launch_dependents();
     pdl_wait();
@@ -499,7 +502,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     Raw nx;
     const bool fast = g.fast != 0;
     if (fast && !warped) {
-        F = fast_col(xin_base + (size_t)r0 * xin_pitch, xin_pitch, g.upr, tid);
+        F = fast_col(xin_base + (size_t)r0 * xin_pitch, xin_pitch, g, tid);
         ld_raw(F.ip, F.mis != 0, false, nx);
     }
     const SsadImageParams& P = params[b];        // read in place (L1 broadcast): only the gather and the cut sums need it
@@ -509,8 +512,8 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     }
 
     uint32_t acc[7] = {0, 0, 0, 0, 0, 0, 0};          // 0-2 RGB of x, 3 sum of L, 4-6 RGB of the cut
-    const Slab SL = make_slab(r0, nunits, g.upr, tid);
     if (warped) {
+        const Slab SL = make_slab(r0, nunits, g.upr, tid);
         // RandomAffine(3, scale=(1.05, 1.1)) NEAREST, fill 0 (datasets.py:220-222): x gathered once into the x buffer
         const int32_t a0 = P.warp_fix[0], a1 = P.warp_fix[1], a2 = P.warp_fix[2];
         const int32_t a3 = P.warp_fix[3], a4 = P.warp_fix[4], a5 = P.warp_fix[5];
@@ -529,7 +532,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
         }
         if (!defect && !need_luma) return;       // only the gather was needed
         if (fast) {
-            F = fast_col(xin_base + (size_t)r0 * xin_pitch, xin_pitch, g.upr, tid);
+            F = fast_col(xin_base + (size_t)r0 * xin_pitch, xin_pitch, g, tid);
             ld_raw(F.ip, F.mis != 0, false, nx);
         }
     }
@@ -543,6 +546,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
             SSAD_V7_BY_KIND(kind, SSAD_CALL)
             #undef SSAD_CALL
         } else {
+            const Slab SL = make_slab(r0, nunits, g.upr, tid);
             #define SSAD_CALL(LK) pass1_gen<LK>(SL, xin_base, xin_pitch, xb, xpitch, store_raw, store_pre, need_rgb, need_luma, R, acc)
             SSAD_V7_BY_KIND(kind, SSAD_CALL)
             #undef SSAD_CALL
@@ -693,12 +697,26 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     }
     __syncthreads();
     const int span_total = (int)row_pre[nrows];
-    // a thread's items go up through the rows (by NT items at a time): walk from the row of the previous item
+    // Items are dealt to the warps in contiguous ranges (lanes = consecutive items), so a warp's items climb through
+    // the rows a span piece at a time: `seek` bisects to the row of a range's first item, `locate` walks on from the
+    // row of the previous item (items must not decrease between two seeks).
+    const int warp = tid >> 5, lane = tid & 31;
     int row_at = 0;
+    auto seek = [&](int idx) {
+        int lo = 0, hi = max(nrows - 1, 0);
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if ((int)row_pre[mid] <= idx) lo = mid; else hi = mid - 1;
+        }
+        row_at = lo;
+    };
     auto locate = [&](int idx, int& u, int& v) {
-        if ((int)row_pre[row_at] > idx) row_at = 0;
         while ((int)row_pre[row_at + 1] <= idx) ++row_at;
         v = my_lo + row_at; u = (int)row_lo[row_at] + idx - (int)row_pre[row_at];
+    };
+    auto warp_range = [&](int total, int& w_lo, int& w_hi) {
+        const int per_w = ((total + NWARP - 1) / NWARP + 31) & ~31;
+        w_lo = min(total, warp * per_w); w_hi = min(total, w_lo + per_w);
     };
     if (y == 1) {
         // polygon: one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
@@ -708,12 +726,15 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
         const int total = span_total;
         const int pl = D.paste[0][0], pt = D.paste[0][1];
         const bool read_cut = !K.flat;
-        for (int idx0 = tid; idx0 < total; idx0 += NT * NB) {
+        int w_lo, w_hi;
+        warp_range(total, w_lo, w_hi);
+        if (w_lo < w_hi) seek(w_lo);
+        for (int idx0 = w_lo + lane; idx0 < w_hi; idx0 += 32 * NB) {
             int uu[NB], vv[NB];
             uint32_t cw[NB];
             #pragma unroll
             for (int j = 0; j < NB; ++j) {
-                locate(min(idx0 + j * NT, total - 1), uu[j], vv[j]);
+                locate(min(idx0 + j * 32, w_hi - 1), uu[j], vv[j]);
                 cw[j] = cov[(size_t)vv[j] * pitchw + (uu[j] >> 5)];
             }
             bool on[NB];
@@ -722,7 +743,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
             #pragma unroll
             for (int j = 0; j < NB; ++j) {
                 const int X = pl + uu[j];
-                on[j] = (idx0 + j * NT < total) && ((cw[j] >> (uu[j] & 31)) & 1u) && X >= 0 && X < W;
+                on[j] = (idx0 + j * 32 < w_hi) && ((cw[j] >> (uu[j] & 31)) & 1u) && X >= 0 && X < W;
                 const bool in_cut = on[j] && read_cut && uu[j] < dn.u_hi && vv[j] < dn.v_hi;
                 qc[j] = in_cut ? dn.base + (size_t)vv[j] * dn.pitch + 3 * uu[j] : nullptr;
                 qx[j] = on[j] ? xb + ((size_t)(pt + vv[j]) * W + X) * 3 : nullptr;
@@ -757,7 +778,10 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
             }
         }
     } else {
-        for (int idx = tid; idx < span_total; idx += NT) {
+        int w_lo, w_hi;
+        warp_range(span_total, w_lo, w_hi);
+        if (w_lo < w_hi) seek(w_lo);
+        for (int idx = w_lo + lane; idx < w_hi; idx += 32) {
             int u, v;
             locate(idx, u, v);
             if (!((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u)) continue;
@@ -808,18 +832,23 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     if (y == 2) {
         constexpr int NB = 4;
         const int box = max(span_total, 1), total = npaste * span_total;
-        for (int id0 = tid; id0 < total; id0 += NT * NB) {
+        int w_lo, w_hi;
+        warp_range(total, w_lo, w_hi);
+        int k = 0, kbase = 0;                    // paste of the current item and its first id (ids only grow)
+        if (w_lo < w_hi) { k = (w_lo + lane) / box; kbase = k * box; seek(min(w_lo + lane, w_hi - 1) - kbase); }
+        for (int id0 = w_lo + lane; id0 < w_hi; id0 += 32 * NB) {
             bool on[NB];
             uint8_t* qx[NB];
             const uint32_t* qc[NB];
             #pragma unroll
             for (int j = 0; j < NB; ++j) {
-                const int id = min(id0 + j * NT, total - 1);
-                const int k = id / box, idx = id - k * box;
+                const int id = min(id0 + j * 32, w_hi - 1);
+                while (id >= kbase + box) { kbase += box; ++k; row_at = 0; }     // next paste: back to the first row
+                const int idx = id - kbase;
                 int u, v;
                 locate(idx, u, v);
                 const int X = D.paste[k][0] + u, Y = D.paste[k][1] + v;
-                bool ok = (id0 + j * NT < total) && X >= 0 && X < W && Y >= 0 && Y < H &&
+                bool ok = (id0 + j * 32 < w_hi) && X >= 0 && X < W && Y >= 0 && Y < H &&
                           ((cov[(size_t)v * pitchw + (u >> 5)] >> (u & 31)) & 1u);
                 if (ok)                          // a later paste overwrites this pixel: it is written there
                     for (int jj = k + 1; jj < npaste; ++jj) {
@@ -911,7 +940,7 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     __shared__ Tables TF;
     __shared__ __align__(16) uint8_t lut_s[3072];
     const int tid = threadIdx.x;
-    const uint32_t j = blockIdx.x / (unsigned)g.nslab;
+    const uint32_t j = g.nslab_shift >= 0 ? blockIdx.x >> g.nslab_shift : blockIdx.x / (unsigned)g.nslab;
     const int slab = (int)(blockIdx.x - j * (unsigned)g.nslab);
     pdl_launch_dependents();
     pdl_wait();
@@ -930,7 +959,7 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     FastCol F;
     Raw nx;
     if (g.fast) {
-        F = fast_col(in2 + (size_t)r0 * in2_pitch, in2_pitch, g.upr, tid);
+        F = fast_col(in2 + (size_t)r0 * in2_pitch, in2_pitch, g, tid);
         ld_raw(F.ip, F.mis != 0, false, nx);
     }
     if (kind != LK_COPY) copy_words(&TF, &state[b].TF, tid);
@@ -971,6 +1000,9 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.nslab = (g.H + g.rows_slab - 1) / g.rows_slab;
     g.fast = (NT % g.upr == 0 && upt == UPT && g.rows_slab * g.upr == NT * UPT && g.H % g.rows_slab == 0) ? 1 : 0;
     if (getenv("SSAD_V7_NOFAST")) g.fast = 0;
+    g.nslab_shift = -1;
+    for (int k = 0; k < 16; ++k) if (g.nslab == (1 << k)) g.nslab_shift = k;
+    g.inv_upr = (65536u + (uint32_t)g.upr - 1u) / (uint32_t)g.upr;
     g.ncanvas = d.batch >= 1024 ? 1 : 2;         // per chunk; measured: fewer, longer canvas CTAs win once the grid fills the GPU
     if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
     while ((d.max_patch_h + g.ncanvas - 1) / g.ncanvas > kCanvasRows) ++g.ncanvas;
@@ -993,33 +1025,49 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
 }  // namespace v7
 }  // namespace ssad
 
-// The batch is cut into chunks that run the kernel pipeline side by side: chunk 0 on the caller's stream, the others on
-// helper streams forked from it and joined back before the call returns (events; legal under stream capture).  The short
-// latency-bound kernels of one chunk (plan, lists, canvas, finish) then overlap the streaming passes of another.
-// Chunks per call: 2 for plain launches (more would make the host the bottleneck: every chunk is 6 launches), 4 when the
-// call is being captured into a CUDA graph (one cudaGraphLaunch replays everything); SSAD_V7_SPLIT pins a number.
-static int v7_chunks(int batch, bool capturing) {
-    int n = (batch >= 256) ? (capturing ? 4 : 2) : 1;
-    if (const char* f = getenv("SSAD_V7_SPLIT")) { int v = atoi(f); if (v >= 1 && v <= 8) n = v; }
-    if (n > batch) n = batch;
-    return n < 1 ? 1 : n;
+// A call is cut into chunks that run on `lanes` streams (chunk c on lane c % lanes, one workspace region per lane, so
+// the x buffer of a lane is rewritten while it is still in the L2 and pass 2 reads it from there).  Lanes: 2 for plain
+// launches (every chunk is 6 launches: more would make the host the bottleneck), 4 when the call is being captured
+// into a CUDA graph (one cudaGraphLaunch replays everything).  Chunks: one per lane (more only on request: SSAD_V7_CHUNK_MB
+// caps a chunk's x buffer, SSAD_V7_SPLIT pins the number; both measured slower than one large chunk per lane).
+struct V7Split { int nchunk, csize, nlanes; };
+static V7Split v7_split(const SsadBatchDesc& d, bool capturing) {
+    int lanes = capturing ? 4 : 2;
+    if (const char* f = getenv("SSAD_V7_LANES")) { int v = atoi(f); if (v >= 1 && v <= 8) lanes = v; }
+    size_t mb = 0;                                // measured: smaller chunks lose more to the latency chains than the L2 gives back
+    if (const char* f = getenv("SSAD_V7_CHUNK_MB")) { int v = atoi(f); if (v >= 1 && v <= 4096) mb = (size_t)v; }
+    int n = 1;
+    if (d.batch >= 256) {
+        const size_t total = (size_t)d.height * d.width * 3 * (size_t)d.batch, lim = mb << 20;
+        const size_t by_size = lim ? (total + lim - 1) / lim : 0;
+        n = lanes;
+        if (by_size > (size_t)n) n = by_size > 64 ? 64 : (int)by_size;
+    }
+    if (const char* f = getenv("SSAD_V7_SPLIT")) { int v = atoi(f); if (v >= 1 && v <= 64) n = v; }
+    if (n > d.batch) n = d.batch;
+    if (n < 1) n = 1;
+    V7Split sp;
+    sp.csize = (d.batch + n - 1) / n;
+    sp.nchunk = (d.batch + sp.csize - 1) / sp.csize;        // no empty chunk
+    sp.nlanes = lanes < sp.nchunk ? lanes : sp.nchunk;
+    return sp;
 }
-static size_t v7_chunk_workspace(const SsadBatchDesc& d, int nchunk) {
+static size_t v7_chunk_workspace(const SsadBatchDesc& d, int csize) {
     ssad::v7::Geo7 g;
     SsadBatchDesc dc = d;
-    dc.batch = (d.batch + nchunk - 1) / nchunk;
+    dc.batch = csize;
     if (!ssad::v7::make_geo7(dc, g)) return 0;
     return g.ws_total;
 }
 
-size_t ssad_v7_workspace(const SsadBatchDesc& d) {           // enough for either number of chunks
-    const int n0 = v7_chunks(d.batch, false), n1 = v7_chunks(d.batch, true);
-    const size_t a = v7_chunk_workspace(d, n0) * (size_t)n0, b = v7_chunk_workspace(d, n1) * (size_t)n1;
+size_t ssad_v7_workspace(const SsadBatchDesc& d) {           // enough for a plain and for a captured call
+    const V7Split s0 = v7_split(d, false), s1 = v7_split(d, true);
+    const size_t a = v7_chunk_workspace(d, s0.csize) * (size_t)s0.nlanes, b = v7_chunk_workspace(d, s1.csize) * (size_t)s1.nlanes;
     return a > b ? a : b;
 }
 
 // kernels one ssad_generate call launches on this path (bench.py's gpu_launches)
-int ssad_v7_launches(int batch, bool capturing) { return 6 * v7_chunks(batch, capturing); }
+int ssad_v7_launches(const SsadBatchDesc& d, bool capturing) { return 6 * v7_split(d, capturing).nchunk; }
 
 static int launch_v7_chunk(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
                            const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
@@ -1055,20 +1103,21 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
     const bool capturing = cap == cudaStreamCaptureStatusActive;
     // programmatic dependent launch pays on plain streams; inside a graph the programmatic edges cost more than they hide
     const bool use_pdl = !capturing && getenv("SSAD_V7_NOPDL") == nullptr;
-    const int nchunk = v7_chunks(d.batch, capturing), csize = (d.batch + nchunk - 1) / nchunk;
+    const V7Split sp = v7_split(d, capturing);
+    const int nchunk = sp.nchunk, csize = sp.csize, nlanes = sp.nlanes;
     const size_t need = ssad_v7_workspace(d);
     if (need == 0) return SSAD_EUNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(src) & 15) || (d.src_pitch & 7) || (d.src_stride & 7)) return SSAD_EUNSUPPORTED;
     if (nchunk > 1 && (d.src_stride & 15)) return SSAD_EUNSUPPORTED;      // every chunk's first image must stay 16-byte aligned
     if (!workspace || workspace_bytes < need) return SSAD_EWORKSPACE;
     if (reinterpret_cast<uintptr_t>(workspace) & 255) return SSAD_EALIGN;
-    const size_t ws_chunk = v7_chunk_workspace(d, nchunk);
-    V7Streams* const HS = (nchunk > 1) ? v7_streams() : nullptr;
-    if (nchunk > 1 && !HS) return SSAD_ELAUNCH;
+    const size_t ws_chunk = v7_chunk_workspace(d, csize);
+    V7Streams* const HS = (nlanes > 1) ? v7_streams() : nullptr;
+    if (nlanes > 1 && !HS) return SSAD_ELAUNCH;
     cudaError_t e = cudaSuccess;
-    if (nchunk > 1) {
+    if (nlanes > 1) {
         e = cudaEventRecord(HS->fork, stream);
-        for (int c = 1; c < nchunk && e == cudaSuccess; ++c) e = cudaStreamWaitEvent(HS->s[c], HS->fork, 0);
+        for (int l = 1; l < nlanes && e == cudaSuccess; ++l) e = cudaStreamWaitEvent(HS->s[l], HS->fork, 0);
         if (e != cudaSuccess) return ssad_set_cuda_error(e);
     }
     const size_t npix = (size_t)d.height * d.width;
@@ -1081,18 +1130,19 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
         dc.batch = nb;
         const uint32_t* mb = mask_bits;
         if (mb && d.mask_mode == SSAD_MASK_PER_IMAGE) mb += (size_t)b0 * d.mask_stride_words;
-        cudaStream_t st = (c == 0) ? stream : HS->s[c];
+        const int lane = c % nlanes;             // chunks of a lane run one after the other and share its workspace
+        cudaStream_t st = (lane == 0) ? stream : HS->s[lane];
         rc = launch_v7_chunk(dc, params + b0, src + (size_t)b0 * d.src_stride, donor_bank, mb, norm_lut,
                              out_u8 ? out_u8 + (size_t)b0 * d.out_u8_stride : nullptr,
                              out_norm ? static_cast<uint8_t*>(out_norm) + (size_t)b0 * 3 * npix * norm_elem : nullptr,
                              y_out ? y_out + b0 : nullptr, debug ? debug + b0 : nullptr,
-                             static_cast<uint8_t*>(workspace) + (size_t)c * ws_chunk, ws_chunk, st, use_pdl);
+                             static_cast<uint8_t*>(workspace) + (size_t)lane * ws_chunk, ws_chunk, st, use_pdl);
         if (rc != SSAD_OK) break;
     }
     // join (also after a failed launch: the helper streams must not stay forked inside a capture)
-    for (int c = 1; c < nchunk; ++c) {
-        cudaError_t e2 = cudaEventRecord(HS->join[c], HS->s[c]);
-        if (e2 == cudaSuccess) e2 = cudaStreamWaitEvent(stream, HS->join[c], 0);
+    for (int l = 1; l < nlanes; ++l) {
+        cudaError_t e2 = cudaEventRecord(HS->join[l], HS->s[l]);
+        if (e2 == cudaSuccess) e2 = cudaStreamWaitEvent(stream, HS->join[l], 0);
         if (e2 != cudaSuccess && rc == SSAD_OK) rc = ssad_set_cuda_error(e2);
     }
     return rc;
