@@ -101,6 +101,20 @@ __device__ __forceinline__ int kind_of_ops(const int32_t* ops, int i0, int i1) {
 #define SSAD_V7_UPT_FAST 8
 #endif
 constexpr int UPT = SSAD_V7_UPT_FAST;
+// resident CTAs per SM the pass kernels are compiled for (4 x 256 threads = 64 registers per thread)
+// pixels per thread and round in the canvas kernel's paste loops (their loads are issued together)
+#ifndef SSAD_V7_NB_POLY
+#define SSAD_V7_NB_POLY 2
+#endif
+#ifndef SSAD_V7_NB_SCAR
+#define SSAD_V7_NB_SCAR 2
+#endif
+#ifndef SSAD_V7_P1_MINB
+#define SSAD_V7_P1_MINB 4
+#endif
+#ifndef SSAD_V7_P2_MINB
+#define SSAD_V7_P2_MINB 4
+#endif
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
@@ -452,8 +466,14 @@ lists_v7_kernel(const __grid_constant__ Geo7 g, const SsadImageParams* __restric
     #pragma unroll
     for (int ps = 0; ps < 2; ++ps) {
         const int kind = S->sk[2 * ps], pos = S->sk[2 * ps + 1];
+        // longest loop bodies first (the kinds are numbered by cost), so the short ones fill the tail of the grid;
+        // images with nothing to do in this pass (kind == NKIND) sit behind them all
         uint32_t rank = (uint32_t)pos;
+#ifdef SSAD_V7_LIGHT_FIRST
         for (int k = 0; k < kind; ++k) rank += sched->count[ps][k];
+#else
+        for (int k = 0; k < NKIND; ++k) if (kind == NKIND || k > kind) rank += sched->count[ps][k];
+#endif
         Hdr h;
         h.b = (kind < NKIND) ? b : -1;
         h.kind = kind; h.flags = flags; h.cx0 = p->crop_off[0]; h.cy0 = p->crop_off[1];
@@ -466,7 +486,7 @@ lists_v7_kernel(const __grid_constant__ Geo7 g, const SsadImageParams* __restric
 }
 
 // ================================================================ pass 1
-__global__ void __launch_bounds__(NT, 4)
+__global__ void __launch_bounds__(NT, SSAD_V7_P1_MINB)
 pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
                 const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src,
                 const uint8_t* __restrict__ donor_bank, ImgState* __restrict__ state, const Hdr* __restrict__ hdr,
@@ -722,7 +742,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
         // polygon: one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
         // thread and round, their loads issued together: the chain coverage word -> cut pixel -> old pixel is three
         // memory latencies long, and nothing else hides it.
-        constexpr int NB = 4;
+        constexpr int NB = SSAD_V7_NB_POLY;
         const int total = span_total;
         const int pl = D.paste[0][0], pt = D.paste[0][1];
         const bool read_cut = !K.flat;
@@ -830,7 +850,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     // (all pastes x canvas rows of this CTA x columns) dealt over the threads, NB items per thread and round with
     // their loads issued together
     if (y == 2) {
-        constexpr int NB = 4;
+        constexpr int NB = SSAD_V7_NB_SCAR;
         const int box = max(span_total, 1), total = npaste * span_total;
         int w_lo, w_hi;
         warp_range(total, w_lo, w_hi);
@@ -933,7 +953,7 @@ finish_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
 }
 
 // ================================================================ pass 2
-__global__ void __launch_bounds__(NT, 4)
+__global__ void __launch_bounds__(NT, SSAD_V7_P2_MINB)
 pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g, const uint8_t* __restrict__ src,
                 const ImgState* __restrict__ state, const Hdr* __restrict__ hdr, const uint8_t* xbuf,
                 const void* __restrict__ norm_lut, uint8_t* __restrict__ out_u8, void* __restrict__ out_norm) {
