@@ -1023,7 +1023,9 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.nslab_shift = -1;
     for (int k = 0; k < 16; ++k) if (g.nslab == (1 << k)) g.nslab_shift = k;
     g.inv_upr = (65536u + (uint32_t)g.upr - 1u) / (uint32_t)g.upr;
-    g.ncanvas = d.batch >= 1024 ? 1 : 2;         // per chunk; measured: fewer, longer canvas CTAs win once the grid fills the GPU
+    // canvas CTAs per image, per chunk; measured: fewer, longer canvas CTAs win once the grid fills the GPU, larger
+    // images (taller canvases) want more
+    g.ncanvas = (d.batch >= 1024 ? 1 : 2) * (d.height >= 1024 ? 2 : 1);
     if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
     while ((d.max_patch_h + g.ncanvas - 1) / g.ncanvas > kCanvasRows) ++g.ncanvas;
     g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;

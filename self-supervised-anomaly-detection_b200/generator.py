@@ -228,11 +228,13 @@ class BatchGenerator:
 
     # ------------------------------------------------------------------ host buffers in, host buffers out
     def generate_from_host(self, h_src: torch.Tensor, params: ParamBatch, h_out: torch.Tensor, h_y: torch.Tensor, *,
-                           chunks: Optional[int] = None, masks_fn=None) -> None:
+                           chunks: Optional[int] = None, masks_fn=None, wait: bool = True):
         """The end-to-end call for data that lives in (pinned) host memory: uint8 images ``h_src`` [B, Hs, Ws, 3] ->
         ``h_out`` uint8 [B, h, w, 3] and labels ``h_y`` int64 [B], all host tensors.  The batch is cut into ``chunks``
         pieces that flow through three streams -- host-to-device copy, generation (``ssad_generate``), device-to-host
-        copy -- so the two PCIe directions and the kernels overlap.  Returns when the results are in host memory.
+        copy -- so the two PCIe directions and the kernels overlap.  Returns when the results are in host memory;
+        with ``wait=False`` it returns at once with a ``torch.cuda.Event`` that completes when they are (a loader that
+        keeps the next batch in flight: call again with other host buffers, then ``event.synchronize()`` this one).
         ``masks_fn(d_src_chunk) -> packed masks`` supplies per-image masks (non-fixed classes: ``obj_mask_batch``)."""
         B = int(h_src.shape[0])
         W, H = self.cfg.work_size
@@ -243,7 +245,22 @@ class BatchGenerator:
         cur = torch.cuda.current_stream(self.device)
         for s_ in (st["up"], st["run"], st["down"]):
             s_.wait_stream(cur)
+        # the device staging buffers are shared by consecutive calls: this call's uploads follow the previous call's
+        # kernels, its kernels the previous call's downloads (both long finished unless the call was made with wait=False)
+        st["up"].wait_stream(st["run"])
+        st["run"].wait_stream(st["down"])
         bounds = [(B * c // chunks, B * (c + 1) // chunks) for c in range(chunks)]
+        # the records of the whole batch go up once, through a pinned staging buffer, ahead of the first pixels
+        rec = np.ascontiguousarray(params.records)
+        if len(rec) != B or rec.dtype != IMAGE_PARAMS_DTYPE:
+            raise ValueError("params and h_src disagree on the batch size (or the records have the wrong dtype)")
+        if np.any(rec["jit_f"] < 0) or np.any(rec["bright_f"] < 0):
+            raise ValueError("enhancement factors must be non-negative")
+        st["ev_rec"].synchronize()               # the previous call's upload has left the staging buffer
+        st["h_rec"].numpy()[...] = rec.view(np.uint8).reshape(B, IMAGE_PARAMS_DTYPE.itemsize)
+        with torch.cuda.stream(st["up"]):
+            st["d_rec"].copy_(st["h_rec"], non_blocking=True)
+            st["ev_rec"].record(st["up"])
         for c, (lo, hi) in enumerate(bounds):
             d_src, d_out, d_y = st["src"][lo:hi], st["out"][lo:hi], st["y"][lo:hi]
             with torch.cuda.stream(st["up"]):
@@ -251,16 +268,24 @@ class BatchGenerator:
                 st["ev_up"][c].record(st["up"])
             with torch.cuda.stream(st["run"]):
                 st["run"].wait_event(st["ev_up"][c])
-                sub = params.slice(lo, hi)
                 m = masks_fn(d_src) if masks_fn is not None else None
-                self.generate(d_src, sub, masks=m, want_u8=True, norm_dtype=None, out_u8=d_out, y_out=d_y)
+                if self.cfg.is_non_fixed and m is None and self.mask_bits is None:
+                    raise ValueError("non-fixed classes need per-image masks (obj_mask, datasets.py:232-233)")
+                pl = self.plan(d_src, params.slice(lo, hi), masks=m, want_u8=True, norm_dtype=None,
+                               params_dev=st["d_rec"][lo:hi], out_u8=d_out, y_out=d_y, workspace=st["ws"][c])
+                st["ws"][c] = pl.workspace       # kept: the next call's chunk reuses it
+                self.run(pl)
                 st["ev_run"][c].record(st["run"])
             with torch.cuda.stream(st["down"]):
                 st["down"].wait_event(st["ev_run"][c])
                 h_out[lo:hi].copy_(d_out, non_blocking=True)
                 h_y[lo:hi].copy_(d_y, non_blocking=True)
-        st["down"].synchronize()                 # the caller owns the results when the call returns
+        done = torch.cuda.Event()
+        done.record(st["down"])
         cur.wait_stream(st["up"]); cur.wait_stream(st["run"])
+        if wait:
+            done.synchronize()                   # the caller owns the results when the call returns
+        return done
 
     def _host_pipe(self, B: int, src_shape: tuple, chunks: int) -> dict:
         key = (B, src_shape, chunks)
@@ -272,6 +297,9 @@ class BatchGenerator:
                   "src": torch.empty((B,) + src_shape, dtype=torch.uint8, device=dev),
                   "out": torch.empty((B, H, W, 3), dtype=torch.uint8, device=dev),
                   "y": torch.empty((B,), dtype=torch.int64, device=dev),
+                  "h_rec": torch.empty((B, IMAGE_PARAMS_DTYPE.itemsize), dtype=torch.uint8).pin_memory(),
+                  "d_rec": torch.empty((B, IMAGE_PARAMS_DTYPE.itemsize), dtype=torch.uint8, device=dev),
+                  "ev_rec": torch.cuda.Event(), "ws": [None] * chunks,
                   "ev_up": [torch.cuda.Event() for _ in range(chunks)], "ev_run": [torch.cuda.Event() for _ in range(chunks)]}
             self._pipe = st
         return st

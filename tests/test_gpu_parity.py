@@ -220,3 +220,28 @@ def test_host_buffer_pipeline_matches_device_call(name, chunks):
     gen.generate_from_host(h_src, sc.params, h_out, h_y, chunks=chunks, masks_fn=masks_fn)
     assert torch.equal(h_out, ref["x_u8"].cpu())
     assert torch.equal(h_y, ref["y"].cpu())
+
+
+@pytest.mark.gpu
+def test_host_buffer_pipeline_two_batches_in_flight():
+    """generate_from_host(wait=False): a second call is issued while the first batch is still on its way; both deliver
+    the bytes of the device-resident call once their events complete (the staging buffers are shared between calls)."""
+    import gpu_utils as U
+    scs = [S.build("patch_level", 24, seed=0), S.build("patch_level", 24, seed=7)]
+    gen = U.make_generator(scs[0])               # one generator (one shared mask) serves both batches
+    W, H = scs[0].cfg.work_size
+    refs, outs, events = [], [], []
+    for sc in scs:
+        r = U.run_cuda(sc, norm_dtype=None, debug=False, gen=gen)
+        refs.append({"x_u8": r["x_u8"].cpu().clone(), "y": r["y"].cpu().clone()})
+    for k, sc in enumerate(scs):
+        h_src = torch.from_numpy(sc.images).pin_memory()
+        h_out = torch.zeros((24, H, W, 3), dtype=torch.uint8).pin_memory()
+        h_y = torch.zeros((24,), dtype=torch.int64).pin_memory()
+        events.append(gen.generate_from_host(h_src, sc.params, h_out, h_y, chunks=3, wait=False))
+        outs.append((h_src, h_out, h_y))
+    for k in range(2):
+        events[k].synchronize()
+        assert torch.equal(outs[k][1], refs[k]["x_u8"])
+        assert torch.equal(outs[k][2], refs[k]["y"])
+    assert not torch.equal(outs[0][1], outs[1][1])

@@ -8,6 +8,7 @@ for l in open(sys.argv[1]):
         print(l, end='  ')
     elif l.startswith('{'):
         d = json.loads(l)
-        print(f"{d['value']/1e6:.2f} Mimg/s  {d['ms_per_step']*1e3:.1f} us  frac {d['roofline']['frac']:.3f}  e2e {d['e2e']['value']/1e3:.0f}k")
+        r = d.get("roofline") or {"frac": float("nan")}
+        print(f"{d['value']/1e6:.4f} Mimg/s  {d['ms_per_step']*1e3:.1f} us  frac {r['frac']:.3f}  e2e {d['e2e']['value']/1e3:.0f}k")
     elif l:
         print(l[:200])
