@@ -83,11 +83,13 @@ def test_v6_cluster_sizes_match_oracle(name, csize, monkeypatch):
 
 
 @pytest.mark.parametrize("env", [{"SSAD_V7_NOFAST": "1"}, {"SSAD_V7_UPT": "3"}, {"SSAD_V7_NC": "1"}, {"SSAD_V7_NC": "16"}, {"SSAD_V7_SPLIT": "3"},
-                                 {"SSAD_V7_SPLIT": "8", "SSAD_V7_NOPDL": "1"}])
+                                 {"SSAD_V7_SPLIT": "8", "SSAD_V7_NOPDL": "1"}, {"SSAD_V7_SPLIT": "4", "SSAD_V7_LANES": "1"},
+                                 {"SSAD_V7_SPLIT": "7", "SSAD_V7_LANES": "3"}])
 @pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
 def test_v7_loop_and_grid_variants_match_oracle(name, env, monkeypatch):
     """v7's general unit loops (the fast ones need a power-of-two width and whole slabs), odd slab sizes, and the
-    number of CTAs that share an image's patch canvas, and the batch cut into chunks on helper streams."""
+    number of CTAs that share an image's patch canvas, and the batch cut into chunks that run on lanes (helper streams;
+    with more chunks than lanes a lane's workspace is reused by its next chunk)."""
     _check_against_oracle(name, 12, monkeypatch, dict(env, SSAD_KERNEL="v7"))
 
 
