@@ -93,6 +93,13 @@ def test_v7_loop_and_grid_variants_match_oracle(name, env, monkeypatch):
     _check_against_oracle(name, 12, monkeypatch, dict(env, SSAD_KERNEL="v7"))
 
 
+@pytest.mark.parametrize("name,batch", [("patch_level", 257), ("texture", 259), ("image_level_256", 3)])
+def test_default_chunking_matches_oracle(name, batch):
+    """Batches past the chunking threshold (256) with the library's own choice of lanes and chunks (odd sizes: the last
+    chunk is shorter), and a tiny batch, against the oracle image by image."""
+    _check_against_oracle(name, batch)
+
+
 @pytest.mark.parametrize("name", S.ALL)
 def test_generate_matches_reference_golden(name):
     import gpu_utils as U
