@@ -17,6 +17,7 @@
 //                      across the 32 words, until a sweep pair changes nothing.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/ssad.h"
@@ -47,19 +48,55 @@ __device__ __forceinline__ double sym13(const double* v, const double* w) {
     return t;
 }
 
+// a / c correctly rounded, with rc = RN(1 / c) at hand (smoothed / (bleed_over + eps): one of a few divisors per tile).
+// q0 = RN(a * rc) is within 1.5 ulp; one residual step makes it faithful, the second one correctly rounded (Markstein's
+// theorem: y = RN(1/b), q faithful => RN(q + y * (a - b*q)) = RN(a/b); no overflow / underflow here: a in [0, 1.1],
+// c in [0.2, 1.1]).  Five FMA-pipe instructions instead of the ~30 of a full division.
+#ifdef SSAD_CANNY_FULL_DIV
+__device__ __forceinline__ double div_by_table(double a, double c, double) { return __ddiv_rn(a, c); }
+#else
+__device__ __forceinline__ double div_by_table(double a, double c, double rc) {
+    const double q0 = __dmul_rn(a, rc);
+    const double q1 = __fma_rn(__fma_rn(-q0, c, a), rc, q0);
+    return __fma_rn(__fma_rn(-q1, c, a), rc, q1);
+}
+#endif
+
 __device__ __forceinline__ int xclass(int x, int n) { return x < 6 ? x : (x >= n - 6 ? 12 - (n - 1 - x) : 6); }
 __device__ __forceinline__ int xrep(int c, int n) { return c < 6 ? c : (c == 6 ? 6 : n - 1 - (12 - c)); }
 
 struct CannySmem {
-    double G[G_H * G_P];        // later: I (isobel) in the first CT_H * IJ_P entries
-    double V[V_H * V_P];        // later: J (jsobel)
-    double S[S_H * S_P];
-    double M[M_H * M_P];
+    double V[V_H * V_P];        // Gaussian along axis 0; later: M, the gradient magnitude (halo 1)
+    double S[S_H * S_P];        // smoothed (halo 2)
     double tbl[S_H * TBL_C];    // bleed-over + eps per (row, column class)
+    double rtbl[S_H * TBL_C];   // its correctly rounded reciprocal
     double lut[256];            // v / 255.0
+    uint8_t G8[G_H * G_W];      // L with an 8-pixel halo (0 outside the image = 0.0 after the table: mode='constant')
 };
+static_assert(M_H * M_P <= V_H * V_P, "the magnitude tile reuses the axis-0 buffer");
 
-__global__ void __launch_bounds__(CT_NT, 2)
+// ndi.sobel (mode='reflect': neighbours clamp to the image) of the smoothed tile at image pixel (y, x)
+__device__ __forceinline__ void sobel_at(const double* S, int y, int x, int y0, int x0, int H, int W, double& is, double& js) {
+    const int ru = max(y - 1, 0) - (y0 - 2), rc = y - (y0 - 2), rd = min(y + 1, H - 1) - (y0 - 2);
+    const int cl = max(x - 1, 0) - (x0 - 2), cc = x - (x0 - 2), cr = min(x + 1, W - 1) - (x0 - 2);
+    const double s_ul = S[ru * S_P + cl], s_uc = S[ru * S_P + cc], s_ur = S[ru * S_P + cr];
+    const double s_cl = S[rc * S_P + cl], s_cr = S[rc * S_P + cr];
+    const double s_dl = S[rd * S_P + cl], s_dc = S[rd * S_P + cc], s_dr = S[rd * S_P + cr];
+    // isobel: [-1,0,1] along axis 0, then [1,2,1] along axis 1
+    const double dl = __dsub_rn(s_dl, s_ul), dc = __dsub_rn(s_dc, s_uc), dr = __dsub_rn(s_dr, s_ur);
+    is = __dadd_rn(__dmul_rn(dc, 2.0), __dadd_rn(dl, dr));
+    // jsobel: [-1,0,1] along axis 1, then [1,2,1] along axis 0
+    const double eu = __dsub_rn(s_ur, s_ul), ec = __dsub_rn(s_cr, s_cl), ed = __dsub_rn(s_dr, s_dl);
+    js = __dadd_rn(__dmul_rn(ec, 2.0), __dadd_rn(eu, ed));
+}
+
+// resident CTAs per SM the kernel is compiled for: 55 KB of shared memory per CTA and 63 registers allow four
+// (measured: 2 CTAs 27.1 ms, 3 CTAs 24.9 ms, 4 CTAs 23.5 ms for 1024 images of 1024 x 1024, planes kernel included)
+#ifndef SSAD_CANNY_MINB
+#define SSAD_CANNY_MINB 4
+#endif
+
+__global__ void __launch_bounds__(CT_NT, SSAD_CANNY_MINB)
 canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* __restrict__ src, long long src_pitch,
                  long long src_stride, uint32_t* __restrict__ low_plane, uint32_t* __restrict__ high_plane, int nw,
                  long long plane_stride /* words per image between its planes' starts */) {
@@ -84,22 +121,37 @@ canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* 
             const int x = xrep(c, W);
             #pragma unroll
             for (int k = 0; k < 13; ++k) v[k] = (x + k - 6 >= 0 && x + k - 6 < W) ? a : 0.0;
-            sm.tbl[idx] = __dadd_rn(sym13(v, K.w), K.eps);   // ... then axis 1, + eps
+            const double dv = __dadd_rn(sym13(v, K.w), K.eps);   // ... then axis 1, + eps
+            sm.tbl[idx] = dv;
+            sm.rtbl[idx] = __drcp_rn(dv);
         }
     }
     __syncthreads();
 
-    // ---- L = convert('L') (Convert.c) as float in [0, 1]; 0 outside the image (mode='constant')
-    for (int i = tid; i < G_H * G_W; i += CT_NT) {
-        const int r = i / G_W, c = i - r * G_W;
-        const int y = y0 - 8 + r, x = x0 - 8 + c;
-        double v = 0.0;
-        if (y >= 0 && y < H && x >= 0 && x < W) {
-            const uint8_t* q = img + (size_t)y * src_pitch + (size_t)x * 3;
-            const uint32_t L = (19595u * q[0] + 38470u * q[1] + 7471u * q[2] + 0x8000u) >> 16;
-            v = sm.lut[L];
+    // ---- L = convert('L') (Convert.c); 0 outside the image (mode='constant'); / 255 happens at the first read
+    // (five pixels per thread and round, their byte loads issued together: at two CTAs per SM nothing else hides the
+    // memory latency of this phase)
+    constexpr int LB = 5;
+    static_assert((G_H * G_W) % (CT_NT * LB) == 0, "tile pixels are dealt in whole rounds");
+    for (int i0 = tid; i0 < G_H * G_W; i0 += CT_NT * LB) {
+        uint32_t pr[LB], pg[LB], pb[LB];
+        int at[LB];
+        #pragma unroll
+        for (int k = 0; k < LB; ++k) {
+            const int i = i0 + k * CT_NT;
+            const int r = i / G_W, c = i - r * G_W;
+            const int y = y0 - 8 + r, x = x0 - 8 + c;
+            at[k] = i;
+            pr[k] = pg[k] = pb[k] = 0;
+            if (y >= 0 && y < H && x >= 0 && x < W) {
+                const uint8_t* q = img + (size_t)y * src_pitch + (size_t)x * 3;
+                pr[k] = q[0]; pg[k] = q[1]; pb[k] = q[2];
+            }
         }
-        sm.G[r * G_P + c] = v;
+        #pragma unroll
+        for (int k = 0; k < LB; ++k) {
+            sm.G8[at[k]] = (uint8_t)((19595u * pr[k] + 38470u * pg[k] + 7471u * pb[k] + 0x8000u) >> 16);
+        }
     }
     __syncthreads();
 
@@ -108,7 +160,7 @@ canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* 
         const int c = it % G_W, seg = it / G_W;
         double v[24];
         #pragma unroll
-        for (int k = 0; k < 24; ++k) v[k] = sm.G[(seg * 12 + k) * G_P + c];
+        for (int k = 0; k < 24; ++k) v[k] = sm.lut[sm.G8[(seg * 12 + k) * G_W + c]];
         #pragma unroll
         for (int o = 0; o < 12; ++o) sm.V[(seg * 12 + o) * V_P + c] = sym13(v + o, K.w);
     }
@@ -127,37 +179,23 @@ canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* 
         for (int o = 0; o < 10; ++o) {
             const int c = c0 + o, x = x0 - 2 + c;
             if (c < S_W && x >= 0 && x < W)
-                sm.S[r * S_P + c] = __ddiv_rn(sym13(v + o, K.w), sm.tbl[r * TBL_C + xclass(x, W)]);
+                sm.S[r * S_P + c] = div_by_table(sym13(v + o, K.w), sm.tbl[r * TBL_C + xclass(x, W)], sm.rtbl[r * TBL_C + xclass(x, W)]);
         }
     }
     __syncthreads();
 
-    // ---- ndi.sobel (mode='reflect': neighbours clamp to the image) and the magnitude, halo 1
-    double* I = sm.G;
-    double* J = sm.V;
+    // ---- ndi.sobel and the magnitude, halo 1, into the axis-0 buffer (free since the barrier above)
+    double* const M = sm.V;
     for (int i = tid; i < M_H * M_W; i += CT_NT) {
         const int r = i / M_W, c = i - r * M_W;
         const int y = y0 - 1 + r, x = x0 - 1 + c;
         double mag = 0.0;
         if (y >= 0 && y < H && x >= 0 && x < W) {
-            const int ru = max(y - 1, 0) - (y0 - 2), rc = y - (y0 - 2), rd = min(y + 1, H - 1) - (y0 - 2);
-            const int cl = max(x - 1, 0) - (x0 - 2), cc = x - (x0 - 2), cr = min(x + 1, W - 1) - (x0 - 2);
-            const double s_ul = sm.S[ru * S_P + cl], s_uc = sm.S[ru * S_P + cc], s_ur = sm.S[ru * S_P + cr];
-            const double s_cl = sm.S[rc * S_P + cl], s_cr = sm.S[rc * S_P + cr];
-            const double s_dl = sm.S[rd * S_P + cl], s_dc = sm.S[rd * S_P + cc], s_dr = sm.S[rd * S_P + cr];
-            // isobel: [-1,0,1] along axis 0, then [1,2,1] along axis 1
-            const double dl = __dsub_rn(s_dl, s_ul), dc = __dsub_rn(s_dc, s_uc), dr = __dsub_rn(s_dr, s_ur);
-            const double is = __dadd_rn(__dmul_rn(dc, 2.0), __dadd_rn(dl, dr));
-            // jsobel: [-1,0,1] along axis 1, then [1,2,1] along axis 0
-            const double eu = __dsub_rn(s_ur, s_ul), ec = __dsub_rn(s_cr, s_cl), ed = __dsub_rn(s_dr, s_dl);
-            const double js = __dadd_rn(__dmul_rn(ec, 2.0), __dadd_rn(eu, ed));
+            double is, js;
+            sobel_at(sm.S, y, x, y0, x0, H, W, is, js);
             mag = __dsqrt_rn(__dadd_rn(__dmul_rn(is, is), __dmul_rn(js, js)));
-            if (r >= 1 && r <= CT_H && c >= 1 && c <= CT_W) {
-                I[(r - 1) * IJ_P + (c - 1)] = is;
-                J[(r - 1) * IJ_P + (c - 1)] = js;
-            }
         }
-        sm.M[r * M_P + c] = mag;
+        M[r * M_P + c] = mag;
     }
     __syncthreads();
 
@@ -169,14 +207,15 @@ canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* 
         const int y = y0 + r, x = x0 + c;
         bool lo = false, hi = false;
         if (y >= 1 && y <= H - 2 && x >= 1 && x <= W - 2) {        // eroded_mask: the 1-pixel border never qualifies
-            const double m = sm.M[(r + 1) * M_P + (c + 1)];
+            const double m = M[(r + 1) * M_P + (c + 1)];
             if (m >= K.low) {
-                const double is = I[r * IJ_P + c], js = J[r * IJ_P + c];
+                double is, js;                   // only the few pixels above the low threshold need the gradient again
+                sobel_at(sm.S, y, x, y0, x0, H, W, is, js);
                 const bool is_down = is <= 0.0, is_up = is >= 0.0, is_left = js <= 0.0, is_right = js >= 0.0;
                 const bool cond1 = (is_up && is_right) || (is_down && is_left);
                 const bool cond2 = (is_down && is_right) || (is_up && is_left);
                 const double ai = fabs(is), aj = fabs(js);
-                auto nb = [&](int dr, int dc) { return sm.M[(r + 1 + dr) * M_P + (c + 1 + dc)]; };
+                auto nb = [&](int dr, int dc) { return M[(r + 1 + dr) * M_P + (c + 1 + dc)]; };
                 bool have = false;
                 double w = 0.0, n11 = 0.0, n12 = 0.0, n21 = 0.0, n22 = 0.0;
                 if (cond1) {
@@ -444,6 +483,8 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
                                                                              ws + plane_words, nw, 3 * plane_words);
     e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
+    // (cutting the batch into parts so that this warp-per-image kernel overlaps the next part's canny was measured: no
+    // gain, the two kernels compete for the same issue slots)
     ssad::mask_planes_kernel<<<(batch + 3) / 4, 128, 0, st>>>(batch, height, width, nw, ws, plane_words, mask_bits, mask_pitch_words,
                                                             mask_stride_words);
     e = cudaGetLastError();
