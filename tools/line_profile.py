@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Warp instructions and stall samples per CUDA source line of one kernel of an ncu capture.
 The SASS page of the report gives per-instruction counts; nvdisasm --print-line-info of the same build's cubin gives
-the source line of every instruction (same order).   usage: line_profile.py sass.csv kernel_index cubin kernel_name [top]"""
+the source line of every instruction (same order).   usage: line_profile.py sass.csv kernel_index cubin kernel_name [top [samples]]"""
 import collections, csv, re, subprocess, sys
 sass, ki, cubin, kname = sys.argv[1], int(sys.argv[2]), sys.argv[3], sys.argv[4]
 top = int(sys.argv[5]) if len(sys.argv) > 5 else 40
@@ -30,7 +30,8 @@ for (src, ex, n), ln in zip(data, lines):
 tot = sum(d[1] for d in data); totn = sum(d[2] for d in data)
 print('total warp-instr', tot, 'samples', totn)
 srcs = {}
-for (f, ln), (ex, n, k) in sorted(agg.items(), key=lambda x: -x[1][0])[:top]:
+bysmp = len(sys.argv) > 6 and sys.argv[6] == "samples"
+for (f, ln), (ex, n, k) in sorted(agg.items(), key=lambda x: -x[1][1 if bysmp else 0])[:top]:
     if f not in srcs:
         try: srcs[f] = open('self-supervised-anomaly-detection_b200/csrc/' + f).read().splitlines()
         except OSError: srcs[f] = []
