@@ -175,11 +175,7 @@ __device__ __forceinline__ void store_norm(const uint32_t (&w)[6], void* onorm, 
                 v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
                 v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
                 v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
-#ifdef SSAD_V7_NORM_STREAM
-                __stcs(o + qq, v);               // never re-read on the GPU: evict-first keeps the x buffer in the L2
-#else
-                o[qq] = v;
-#endif
+                __stcs(o + qq, v);               // never re-read on the GPU: evict-first keeps the x buffer in the L2 (+0.5 %)
             }
         }
     } else {
@@ -194,11 +190,7 @@ __device__ __forceinline__ void store_norm(const uint32_t (&w)[6], void* onorm, 
                 uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
                 wv[qq] = lo | (hi << 16);
             }
-#ifdef SSAD_V7_NORM_STREAM
             __stcs(reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0), make_uint4(wv[0], wv[1], wv[2], wv[3]));
-#else
-            *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
-#endif
         }
     }
 }

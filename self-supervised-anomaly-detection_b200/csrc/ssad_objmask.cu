@@ -306,36 +306,7 @@ __device__ void reach(const Plane& Mp, const Plane& Rp, int ylo, int yhi, uint32
             uint32_t prev = 0;
             int y = dir == 0 ? ylo : yhi;
             const int step = dir == 0 ? 1 : -1, n = yhi - ylo + 1;
-#ifdef SSAD_PLANES_RD
-            // RD rows in flight ahead of the row being processed (rows ahead are not written before the sweep reaches them)
-            constexpr int RD = SSAD_PLANES_RD;
-            uint32_t Mq[RD], Rq[RD];
-            #pragma unroll
-            for (int k = 0; k < RD; ++k) {
-                Mq[k] = Rq[k] = 0u;
-                if (k < n) { Mq[k] = Mp.ld(y + k * step); Rq[k] = Rp.ld(y + k * step); }
-            }
-            #pragma unroll 1
-            for (int i0 = 0; i0 < n; i0 += RD) {
-                #pragma unroll
-                for (int k = 0; k < RD; ++k) {
-                    const int i = i0 + k;
-                    if (i < n) {
-                        const uint32_t M = COMPLEMENT ? (~Mq[k] & rowmask) : Mq[k];
-                        const uint32_t R = Rq[k];
-                        if (i + RD < n) { Mq[k] = Mp.ld(y + RD * step); Rq[k] = Rp.ld(y + RD * step); }
-                        const uint32_t S = R | (M & spread3(prev, lane));
-                        uint32_t Rnew = R;
-                        if (first || __any_sync(FULL, S != R)) {
-                            Rnew = flood_row(M, S, lane);
-                            if (Rnew != R) { Rp.st(y, Rnew); changed = true; }
-                        }
-                        prev = Rnew;
-                        y += step;
-                    }
-                }
-            }
-#else
+            // (six rows of loads in flight instead of one were measured: no gain, the row step itself is the chain)
             uint32_t Mn = Mp.ld(y), Rn = Rp.ld(y);
             #pragma unroll 1
             for (int i = 0; i < n; ++i, y += step) {
@@ -350,7 +321,6 @@ __device__ void reach(const Plane& Mp, const Plane& Rp, int ylo, int yhi, uint32
                 }
                 prev = Rnew;
             }
-#endif
             first = false;
         }
         if (!__any_sync(FULL, changed)) break;
