@@ -202,6 +202,33 @@ def host_cores() -> int:
 
 
 # ------------------------------------------------------------------ main
+_FULL_AFFINITY = []          # the process's CPU set before _bind_near_gpu narrowed it (restored for the CPU baseline)
+
+
+def _bind_near_gpu(index: int):
+    """Bind this process to the CPUs NVML reports as closest to GPU `index` (one process per GPU: the pinned host
+    buffers of the end-to-end leg are then first-touched on that NUMA node).  Returns the number of CPUs bound, or None."""
+    if os.environ.get("SSAD_BENCH_NO_AFFINITY"):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[index]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else index
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        full = os.sched_getaffinity(0)
+        cpus &= full
+        if cpus:
+            _FULL_AFFINITY.append(full)
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -260,6 +287,7 @@ def main():
     from ssad_b200.generator import BatchGenerator
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = _bind_near_gpu(local_rank)            # host threads + pinned buffers on the GPU's own NUMA node (e2e copies)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -400,6 +428,8 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_dt = float(t.item())
     e2e_value = world * batch * args.e2e_steps / e2e_dt
+    if _FULL_AFFINITY:                           # the CPU baseline below uses every host core again
+        os.sched_setaffinity(0, _FULL_AFFINITY[0])
 
     if rank != 0:
         if world > 1:
@@ -431,7 +461,7 @@ def main():
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s"},
         "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(images.nbytes + rec_bytes),
                 "d2h_bytes_per_step": int(h_out.numel() + h_y.numel() * 8), "steps": args.e2e_steps,
-                "in_flight": 2 if deep else 1, "host_ms_per_call": 1e3 * host_s[0] / max(args.e2e_steps, 1)},
+                "in_flight": 2 if deep else 1, "cpus_bound": numa, "host_ms_per_call": 1e3 * host_s[0] / max(args.e2e_steps, 1)},
         "gpu_launches": args.steps * launches_per_step,
         "serial": {"ms_per_step": serial_ms_per_step, "value": world * batch / (serial_ms_per_step * 1e-3),
                    "note": "the same K steps issued on ONE stream (a step starts when the previous one has finished)"},
