@@ -164,6 +164,8 @@ int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const uint8_t* s
                   int32_t mask_pitch_words, int64_t mask_stride_words, void* workspace, size_t workspace_bytes,
                   void* stream);
 size_t ssad_obj_mask_workspace(int32_t batch, int32_t height, int32_t width);
+/* Number of kernels one ssad_obj_mask call launches. */
+int ssad_obj_mask_launches(void);
 
 /* Unit entry points (parity tests of the individual reference routines). */
 

@@ -905,6 +905,9 @@ extern "C" size_t ssad_obj_mask_workspace(int32_t batch, int32_t height, int32_t
     return obj_mask_layout(batch, height, width).total;
 }
 
+// kernels one ssad_obj_mask call launches (bench.py's gpu_launches): screen, tiles, float64 canny, bit planes
+extern "C" int ssad_obj_mask_launches(void) { return 4; }
+
 extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
                              int64_t src_stride, const SsadCannyConsts* consts, uint32_t* mask_bits, int32_t mask_pitch_words,
                              int64_t mask_stride_words, void* workspace, size_t workspace_bytes, void* stream) {

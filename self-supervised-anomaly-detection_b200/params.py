@@ -151,6 +151,112 @@ def polygon_vertices(pw: int, ph: int, n_side, v):
     return pts
 
 
+def fix16_array(v: np.ndarray) -> np.ndarray:
+    """``fix16`` on a float64 array."""
+    return np.floor(v * 65536.0 + 0.5).astype(np.int64)
+
+
+def _affine_fixed_array(m0, m1, m2, m3, m4, m5) -> np.ndarray:
+    """``affine_fixed_coeffs`` on arrays -> int32 [n, 6]."""
+    out = np.stack([fix16_array(m0), fix16_array(m1), fix16_array(m2 + m0 * 0.5 + m1 * 0.5),
+                    fix16_array(m3), fix16_array(m4), fix16_array(m5 + m3 * 0.5 + m4 * 0.5)], axis=1)
+    return out.astype(np.int32)
+
+
+def random_affine_fixed(w: int, h: int, angle: np.ndarray, scale: np.ndarray) -> np.ndarray:
+    """``affine_fixed_coeffs(random_affine_matrix(w, h, angle[i], scale[i]))`` for a batch -> int32 [n, 6].
+    (In ``random_affine_matrix`` b = -0.0 - sin = -sin and d = -0.0 + cos = cos exactly, so the inverse matrix is
+    [cos, sin, 0, -sin, cos, 0] / scale before the translation terms.)"""
+    angle = np.asarray(angle, dtype=np.float64)
+    scale = np.asarray(scale, dtype=np.float64)
+    rot = [math.radians(float(a)) for a in angle]
+    cs = np.array([math.cos(r) for r in rot], dtype=np.float64)
+    sn = np.array([math.sin(r) for r in rot], dtype=np.float64)
+    cx, cy = w * 0.5, h * 0.5
+    m0, m1, m3, m4 = cs / scale, sn / scale, (-sn) / scale, cs / scale
+    m2 = 0.0 / scale
+    m5 = 0.0 / scale
+    m2 = m2 + (m0 * (-cx) + m1 * (-cy))
+    m5 = m5 + (m3 * (-cx) + m4 * (-cy))
+    m2 = m2 + cx
+    m5 = m5 + cy
+    return _affine_fixed_array(m0, m1, m2, m3, m4, m5)
+
+
+_ROT_TABLE = []
+
+
+def _rot_table() -> np.ndarray:
+    """[721, 4] float64: round(cos, 15), round(sin, 15), round(-sin, 15), round(cos, 15) of -radians(angle % 360)
+    for the integer angles -360..360 (row angle + 360), computed with math.* as PIL/Image.py does (datasets.py:342-344)."""
+    if not _ROT_TABLE:
+        rows = []
+        for ang in range(-360, 361):
+            a = -math.radians(float(ang) % 360.0)
+            rows.append((round(math.cos(a), 15), round(math.sin(a), 15), round(-math.sin(a), 15), round(math.cos(a), 15)))
+        _ROT_TABLE.append(np.array(rows, dtype=np.float64))
+    return _ROT_TABLE[0]
+
+
+def rotate_expand_fixed(w: np.ndarray, h: np.ndarray, angle: np.ndarray):
+    """``rotate_expand_matrix`` + ``affine_fixed_coeffs`` for a batch of integer angles ->
+    (int32 [n, 6] coefficients, int64 [n, 2] expanded (nw, nh))."""
+    w = np.asarray(w, dtype=np.float64)
+    h = np.asarray(h, dtype=np.float64)
+    angle = np.asarray(angle)
+    ai = angle.astype(np.int64)
+    if np.any(ai != angle) or np.any(np.abs(ai) > 360):
+        # non-integer angles: the scalar routine (not on the reference's path, kept for callers of the function API)
+        res = [rotate_expand_matrix(int(w[i]), int(h[i]), float(angle[i])) for i in range(len(w))]
+        fix = np.array([affine_fixed_coeffs(r[0]) for r in res], dtype=np.int32).reshape(len(w), 6)
+        return fix, np.array([(r[1], r[2]) for r in res], dtype=np.int64).reshape(len(w), 2)
+    t = _rot_table()[ai + 360]
+    m0, m1, m3, m4 = t[:, 0], t[:, 1], t[:, 2], t[:, 3]
+    cx, cy = w / 2, h / 2
+    m2 = (m0 * (-cx) + m1 * (-cy)) + 0.0
+    m5 = (m3 * (-cx) + m4 * (-cy)) + 0.0
+    m2 = m2 + cx
+    m5 = m5 + cy
+    zero = np.zeros_like(w)
+    xs = np.stack([m0 * x + m1 * y + m2 for x, y in ((zero, zero), (w, zero), (w, h), (zero, h))])
+    ys = np.stack([m3 * x + m4 * y + m5 for x, y in ((zero, zero), (w, zero), (w, h), (zero, h))])
+    nw = np.ceil(xs.max(axis=0)) - np.floor(xs.min(axis=0))
+    nh = np.ceil(ys.max(axis=0)) - np.floor(ys.min(axis=0))
+    tx, ty = -(nw - w) / 2.0, -(nh - h) / 2.0
+    m2, m5 = m0 * tx + m1 * ty + m2, m3 * tx + m4 * ty + m5
+    fix = _affine_fixed_array(m0, m1, m2, m3, m4, m5)
+    size = np.stack([nw, nh], axis=1).astype(np.int64)
+    ident = (ai % 360) == 0                       # Image.rotate returns a copy: identity matrix, same size
+    if np.any(ident):
+        k = int(ident.sum())
+        one, zer = np.ones(k), np.zeros(k)
+        fix[ident] = _affine_fixed_array(one, zer, zer, zer, one, zer)
+        size[ident] = np.stack([w[ident], h[ident]], axis=1).astype(np.int64)
+    return fix, size
+
+
+def polygon_vertices_batch(pw: np.ndarray, ph: np.ndarray, n_side: np.ndarray, v: np.ndarray):
+    """``polygon_vertices`` for a batch -> (uint8 [n] vertex counts, int16 [n, 8, 2] vertices in draw order)."""
+    n = len(pw)
+    pw = np.asarray(pw, dtype=np.int64)
+    ph = np.asarray(ph, dtype=np.int64)
+    a, b = v[:, :, 0].astype(np.int64), v[:, :, 1].astype(np.int64)
+    zero = np.zeros(n, dtype=np.int64)
+    # candidate points, two per side: (x, y)
+    cand = np.empty((n, 8, 2), dtype=np.int64)
+    cand[:, 0] = np.stack([zero, a[:, 0]], 1); cand[:, 1] = np.stack([zero, b[:, 0]], 1)      # left
+    cand[:, 2] = np.stack([a[:, 1], zero], 1); cand[:, 3] = np.stack([b[:, 1], zero], 1)      # top
+    cand[:, 4] = np.stack([pw, a[:, 2]], 1);   cand[:, 5] = np.stack([pw, b[:, 2]], 1)        # right
+    cand[:, 6] = np.stack([a[:, 3], ph], 1);   cand[:, 7] = np.stack([b[:, 3], ph], 1)        # bottom
+    valid = np.ones((n, 8), dtype=bool)
+    valid[:, 1::2] = np.asarray(n_side) == 2
+    pos = np.cumsum(valid, axis=1) - 1
+    out = np.zeros((n, 8, 2), dtype=np.int16)
+    rows = np.broadcast_to(np.arange(n)[:, None], (n, 8))
+    out[rows[valid], pos[valid]] = cand[valid]
+    return valid.sum(axis=1).astype(np.uint8), out
+
+
 # ------------------------------------------------------------------ the batch
 @dataclass
 class ParamBatch:
@@ -222,21 +328,26 @@ def derive_records(cfg: GeneratorConfig, draws: Dict[str, np.ndarray]) -> np.nda
     rec["rect"][:, 1] = draws["rect_t"]
     rec["rect"][:, 2] = pw
     rec["rect"][:, 3] = ph
-    # per-image Python-float derivations (math.* exactly as torchvision / PIL do)
+    # Python-float derivations, vectorised: +, -, *, / and floor on float64 arrays round exactly as the scalar Python
+    # expressions of torchvision / PIL do when written in the same order; cos / sin go through math.* (NumPy's SIMD
+    # versions may differ in the last bit), once per image for the warp and from a 91-entry table for the scar angles.
     if cfg.warp:
         ang, sc = draws["warp_angle"], draws["warp_scale"]
-        for i in range(B):
-            if ang[i] == 0.0:
-                raise ValueError("warp_angle == 0 takes Pillow's ImagingScaleAffine path, which is not modelled")
-            rec["warp_fix"][i] = affine_fixed_coeffs(random_affine_matrix(W, H, float(ang[i]), float(sc[i])))
-    for i in np.nonzero(label == 1)[0]:
-        pts = polygon_vertices(int(pw[i]), int(ph[i]), draws["poly_n_side"][i], draws["poly_v"][i])
-        rec["poly_n"][i] = len(pts)
-        rec["poly_xy"][i, :len(pts)] = pts
-    for i in np.nonzero(label == 2)[0]:
-        m, nw, nh = rotate_expand_matrix(int(pw[i]), int(ph[i]), float(draws["scar_angle"][i]))
-        rec["scar_fix"][i] = affine_fixed_coeffs(m)
-        rec["scar_size"][i] = (nw, nh)
+        if np.any(ang == 0.0):
+            raise ValueError("warp_angle == 0 takes Pillow's ImagingScaleAffine path, which is not modelled")
+        rec["warp_fix"] = random_affine_fixed(W, H, ang, sc)
+    is_poly = label == 1
+    if np.any(is_poly):
+        idx = np.nonzero(is_poly)[0]
+        n, xy = polygon_vertices_batch(pw[idx], ph[idx], draws["poly_n_side"][idx], draws["poly_v"][idx])
+        rec["poly_n"][idx] = n
+        rec["poly_xy"][idx] = xy
+    is_scar = label == 2
+    if np.any(is_scar):
+        idx = np.nonzero(is_scar)[0]
+        fix, size = rotate_expand_fixed(pw[idx], ph[idx], draws["scar_angle"][idx])
+        rec["scar_fix"][idx] = fix
+        rec["scar_size"][idx] = size
     return rec
 
 
