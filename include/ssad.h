@@ -166,6 +166,11 @@ int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const uint8_t* s
 size_t ssad_obj_mask_workspace(int32_t batch, int32_t height, int32_t width);
 /* Number of kernels one ssad_obj_mask call launches. */
 int ssad_obj_mask_launches(void);
+/* Test hook: ssad_obj_mask decides in float32 where a proven error margin allows and repeats the reference's float64
+ * sequence elsewhere (per pixel, or per 64x32 tile when a tile has many such pixels).  The knobs widen the margins
+ * (margin_scale > 1), cap the pixels a tile may list (sub_cap, 0..96) and the list entries per image (0..4096) so that
+ * the tests can drive every path; the masks must not depend on them.  Arguments out of range restore the defaults. */
+void ssad_obj_mask_test_knobs(float margin_scale, int32_t sub_cap, int32_t pix_per_image);
 
 /* Unit entry points (parity tests of the individual reference routines). */
 

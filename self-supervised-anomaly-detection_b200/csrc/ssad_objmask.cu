@@ -5,13 +5,11 @@
 //   everything), bit-packed.
 //
 // Four kernels.
-//   canny_screen_kernel float32, one CTA per 128x64 tile: the same Gaussian / Sobel chain in fast arithmetic with a proven
-//                      error bound; per 64x32 tile it records whether any pixel could reach the low / the high threshold.
-//   canny_tiles_kernel one warp per image: the tiles that can hold an edge = tiles with a possible low pixel that are
-//                      8-connected, through such tiles, to a tile with a possible high pixel (hysteresis keeps a low
-//                      pixel only when a chain of low pixels ties it to a high one) -> a work list.  On the bench
-//                      images that is 12 % of the tiles; everything else is exactly zero in both planes.
-//   canny_nms_kernel   float64, the listed 64x32 tiles only (persistent CTAs walking the list): L -> separable Gaussian (scipy correlate1d order: centre tap,
+//   canny32_kernel     float32, one CTA per 128x64 tile: the whole canny chain in fast arithmetic; a decision is taken
+//                      only when it clears the proven error of the float32 values, the few undecided pixels (near
+//                      ties) are listed -- or, when a 64x32 tile has too many, the tile.
+//   canny_resolve_kernel  float64, one warp per listed pixel: the reference's operation sequence on the pixel's window.
+//   canny_nms_kernel   float64, dense, the listed 64x32 tiles only (persistent CTAs walking the list): L -> separable Gaussian (scipy correlate1d order: centre tap,
 //                      then the symmetric pairs from the outermost inwards, every product and sum rounded on its own)
 //                      / bleed-over normalisation -> Sobel (reflect) -> magnitude -> bilinear non-maximum suppression
 //                      -> two bit planes (>= low, >= high) written with warp ballots.  FP64-pipe bound: ~125
@@ -103,7 +101,7 @@ __device__ __forceinline__ void sobel_at(const double* S, int y, int x, int y0, 
 #endif
 // warps (bands of rows) per image in the bit-plane kernel
 #ifndef SSAD_PLANES_WARPS
-#define SSAD_PLANES_WARPS 8
+#define SSAD_PLANES_WARPS 16
 #endif
 
 __global__ void __launch_bounds__(CT_NT, SSAD_CANNY_MINB)
@@ -276,36 +274,58 @@ canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* 
     }   // tile list
 }
 
-// ------------------------------------------------------------------ canny: float32 screen
-// The float64 chain costs ~125 unfusable double operations per pixel, yet hysteresis (skimage canny: ndi.label of the
-// low mask, keep the components holding a pixel >= high) can only keep a pixel whose magnitude m reaches the low
-// threshold AND that is 8-connected, through such pixels, to one reaching the high threshold.  This kernel evaluates
-// the same real-number chain (L -> 13-tap Gaussian along axis 0, along axis 1, / bleed-over -> Sobel (reflect) ->
-// |gradient|) in float32 with fused multiply-adds, in grey-level units (x 255), and flags per 64x32 tile whether any
-// pixel has m32 >= low - d resp. m32 >= high - d.
-// Error bound (grey levels; every float32 operation has relative error <= 2^-24 = 6e-8, partial sums <= 255, the taps
-// sum to 1): axis-0 pass <= 13 * 255 * 6e-8 + tap rounding 255 * 6e-8 = 2.2e-4; axis-1 pass doubles it to 4.4e-4;
-// the bleed-over factor is >= 0.63^2 = 0.4 at a corner (x 2.5 -> 1.1e-3), 1 in the interior; Sobel sums six values
-// with weights (1, 2, 1) of both signs: 8 x 1.1e-3 + its own rounding 6 * 1020 * 6e-8 = 9.2e-3 per component, so
-// |m32 - m| <= 1.9e-2 plus the square / add rounding (2e-7 relative of m <= 1443: 3e-4).  The float64 chain itself
-// differs from the real-number value by ~1e-12.  d = 0.1 grey level leaves a five-fold margin.
-constexpr int SC_W = 128, SC_H = 64, SC_NT = 448;
-constexpr int SG_W = SC_W + 16, SG_H = SC_H + 14;       // L: rows y0-7 .. y0+SC_H+6, columns x0-8 .. x0+SC_W+7
-constexpr int SV_H = SC_H + 2;                           // V (axis-0 pass): rows y0-1 .. y0+SC_H, the columns of L
-constexpr int SS_W = SC_W + 4;                           // S (smoothed): columns x0-1 .. x0+SC_W (+2: rows stay 16-byte multiples)
-constexpr float kScreenMargin = 0.1f;
+// ------------------------------------------------------------------ canny: float32 decisions
+// The float64 chain costs ~125 unfusable double operations per pixel, and every decision canny makes with it is a
+// comparison: |gradient| against the two thresholds, the signs and the order of the two gradient components, and the
+// two interpolated neighbours against the pixel (non-maximum suppression).  This kernel evaluates the same real-number
+// chain (L -> 13-tap Gaussian along axis 0, along axis 1, / bleed-over -> Sobel (reflect) -> |gradient| -> NMS) in
+// float32 with fused multiply-adds, in grey-level units (x 255), and takes a decision only when it clears the proven
+// error of the float32 values; the pixels that stay undecided (near ties, ~0.1 % of an image) are listed for
+// canny_resolve_kernel, which repeats the reference's float64 operation sequence for exactly those pixels.  A tile
+// with too many undecided pixels goes to the dense float64 kernel above instead (canny_nms_kernel, work list).
+//
+// Error bounds (grey levels; u = 2^-24; L is an exact integer <= 255; the taps are positive and sum to 1):
+//   axis-0 pass   7 rounded operations on partial sums <= 255 (the pair sums v[j] + v[12-j] are exact integers) and the
+//                 rounding of the taps:                         |V32 - V|  <= 7u 255 + u 255            = 1.22e-4
+//   axis-1 pass   8 rounded operations + the propagated error:  |S32 - S|  <= 8u 255 + u 255 + 1.22e-4 = 2.6e-4
+//   bleed-over    (tiles within 6 pixels of the image border) the divisor A(y) B(x) >= 0.4, its float32 reciprocal is
+//                 within 2.2e-6 relative:                       |S32 - S|  <= 2.5 * 2.6e-4 + 255 * 2.2e-6 = 1.2e-3
+//   Sobel         four differences of two S, weights (1, 2, 1), three roundings on sums <= 1020:
+//                 |is32 - is| <= 8 |S32 - S| + 1.8e-4           = 2.3e-3 (interior), 9.8e-3 (border)
+//   |gradient|    |m32 - m| <= sqrt(2) |is32 - is| + 3u 1443    = 3.5e-3 (interior), 1.41e-2 (border)
+// The float64 chain of the reference is within 1e-11 of the real-number values.  The constants below round these up:
+//   interior  Ec = 0.003, Em = 0.0045;   border  Ec = 0.0125, Em = 0.018.
+// Decisions (dataset_generator.py:30 -> skimage canny): m >= low, m >= high: certain when m32 is Em away from the
+// threshold; sign(is), sign(js): certain when |.| > Ec; |is| > |js|: certain when they differ by more than 2 Ec; the
+// interpolated neighbour v = (n12 num + n11 (den - num)) / den against m: compare den v with den m; the float32
+// difference is within  2 Em den + Ec (n12 + 2 n11 + m)  (+ 1e-3 second order + 1e-6 (lhs + rhs) evaluation rounding)
+// of the true one, so it is certain when it exceeds  T = 2 Em den + 2 Ec (n11 + n12 + m) + 1e-3 + 1e-6 (lhs + rhs).
+#ifndef SSAD_C32_NT
+#define SSAD_C32_NT 512
+#endif
+constexpr int SC_W = 128, SC_H = 64, SC_NT = SSAD_C32_NT;
+constexpr int SG_W = SC_W + 16, SG_H = SC_H + 16;       // L: rows y0-8 .. y0+SC_H+7, columns x0-8 .. x0+SC_W+7
+constexpr int SV_H = SC_H + 4;                           // V (axis-0 pass): rows y0-2 .. y0+SC_H+1, the columns of L
+constexpr int SS_W = SC_W + 4;                           // S (smoothed): rows of V, columns x0-2 .. x0+SC_W+1
+constexpr int SM_H = SC_H + 2, SM_W = SS_W;              // |gradient|^2: rows y0-1 .. y0+SC_H, columns x0-1 .. (130 used)
+constexpr int SUB_CAP = 96;                              // undecided pixels a 64x32 tile may list (else: dense float64 tile)
 static_assert(SG_W % 4 == 0 && SS_W % 4 == 0, "vector rows");
-static_assert(SV_H % 11 == 0 && (SV_H & 1) == 0, "axis-0 pass: 11-row segments; axis-1 pass: row pairs");
+static_assert(SM_H * SM_W <= SV_H * SG_W, "|gradient|^2 reuses the axis-0 buffer");
 
-struct ScreenK {
+struct C32K {
     float w[7];              // taps 0..6 (centre last) of the symmetric 13-tap kernel
-    float lo2, hi2;          // (255 low - d)^2, (255 high - d)^2
+    float tl, th;            // thresholds in grey levels (255 low, 255 high)
+    float ec[2], em[2];      // error bounds of a gradient component / of |gradient|: [interior, border]
+    int sub_cap;             // <= SUB_CAP
+    unsigned pix_cap;        // entries of the undecided-pixel list
 };
-struct ScreenSmem {
+struct C32Smem {
     float G[SG_H * SG_W];    // L (grey levels); reused for S once the axis-0 pass is done
-    float V[SV_H * SG_W];
+    float V[SV_H * SG_W];    // axis-0 pass; reused for |gradient|^2
     float ra[SV_H], rb[SS_W];   // 1 / bleed-over along the rows / the columns (border tiles)
-    uint32_t flags[8];       // [sub-tile 0..3][low, high]
+    uint32_t cand[SC_H * (SC_W / 32)];   // pixels whose |gradient| may reach the low threshold, one word per 32 pixels of a row
+    uint32_t sub_cnt[4];
+    uint16_t sub_list[4][SUB_CAP];
 };
 static_assert(SV_H * SS_W <= SG_H * SG_W, "S reuses the L buffer");
 
@@ -337,7 +357,6 @@ __device__ __forceinline__ om_f32x2 om_pack2(float lo, float hi) {
     asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
     return r;
 }
-__device__ __forceinline__ void om_unpack2(om_f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
 __device__ __forceinline__ om_f32x2 om_fma2(om_f32x2 a, om_f32x2 b, om_f32x2 c) {
     om_f32x2 r;
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
@@ -362,30 +381,25 @@ __device__ __forceinline__ om_f32x2 om_sym13(const om_f32x2* v, const om_f32x2 (
 }
 
 __global__ void __launch_bounds__(SC_NT, 2)
-canny_screen_kernel(const __grid_constant__ ScreenK K, int H, int W, const uint8_t* __restrict__ src, long long src_pitch,
-                    long long src_stride, uint8_t* __restrict__ tile_flags, int ntx, int nty,
-                    uint32_t* __restrict__ low_plane, uint32_t* __restrict__ high_plane, int nw, long long plane_stride) {
+canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __restrict__ src, long long src_pitch,
+               long long src_stride, uint32_t* __restrict__ low_plane, uint32_t* __restrict__ high_plane, int nw,
+               long long plane_stride, uint2* __restrict__ pix_list, uint32_t* __restrict__ pix_count,
+               uint32_t* __restrict__ tile_list, uint32_t* __restrict__ tile_count, int ntx, int nty) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    ScreenSmem& sm = *reinterpret_cast<ScreenSmem*>(smem_raw);
+    C32Smem& sm = *reinterpret_cast<C32Smem*>(smem_raw);
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * SC_W, y0 = blockIdx.y * SC_H, b = blockIdx.z;
     const uint8_t* img = src + (size_t)b * src_stride;
-    const bool border = (x0 - 8 < 6) || (y0 - 7 < 6) || (x0 + SC_W + 8 > W - 6) || (y0 + SC_H + 7 > H - 6);
+    const bool border = (x0 - 8 < 6) || (y0 - 8 < 6) || (x0 + SC_W + 8 > W - 6) || (y0 + SC_H + 8 > H - 6);
 
-    if (tid < 8) sm.flags[tid] = 0u;
-    // both planes start at zero: the float64 kernel writes the listed tiles only
-    for (int i = tid; i < SC_H * (SC_W / 32); i += SC_NT) {
-        const int r = i / (SC_W / 32), xw = (x0 >> 5) + (i - r * (SC_W / 32)), y = y0 + r;
-        if (y < H && xw < nw) {
-            low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
-            high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
-        }
-    }
+    if (tid < 4) sm.sub_cnt[tid] = 0u;
+    if (tid < SC_H * (SC_W / 32)) sm.cand[tid] = 0u;
+    static_assert(SC_H * (SC_W / 32) <= SC_NT, "one thread per candidate word");
     if (border) {
         // gaussian_filter(ones): the taps that fall inside the image, per row and per column of the tile
         for (int i = tid; i < SV_H + SS_W; i += SC_NT) {
             const bool is_row = i < SV_H;
-            const int p = is_row ? y0 - 1 + i : x0 - 1 + (i - SV_H), n = is_row ? H : W;
+            const int p = is_row ? y0 - 2 + i : x0 - 2 + (i - SV_H), n = is_row ? H : W;
             float a = 0.0f;
             #pragma unroll
             for (int k = 0; k < 13; ++k) if (p + k - 6 >= 0 && p + k - 6 < n) a += K.w[k < 7 ? k : 12 - k];
@@ -399,10 +413,10 @@ canny_screen_kernel(const __grid_constant__ ScreenK K, int H, int W, const uint8
         const bool vec_ok = ((src_pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
         constexpr int NG = SG_W / 4, NTASK = SG_H * NG, NR = (NTASK + SC_NT - 1) / SC_NT;
         uint32_t w[NR][3];
-        const bool inside = vec_ok && x0 >= 8 && y0 >= 7 && x0 + SC_W + 8 <= W && y0 + SC_H + 7 <= H;   // (uniform)
+        const bool inside = vec_ok && x0 >= 8 && y0 >= 8 && x0 + SC_W + 8 <= W && y0 + SC_H + 8 <= H;   // (uniform)
         if (inside) {
             // every pixel of the tile and its halo is in the image: no bounds, one pointer per task
-            const uint8_t* const base = img + (size_t)(y0 - 7) * src_pitch + (size_t)(x0 - 8) * 3;
+            const uint8_t* const base = img + (size_t)(y0 - 8) * src_pitch + (size_t)(x0 - 8) * 3;
             #pragma unroll
             for (int k = 0; k < NR; ++k) {
                 const int t = min(tid + k * SC_NT, NTASK - 1);
@@ -411,31 +425,31 @@ canny_screen_kernel(const __grid_constant__ ScreenK K, int H, int W, const uint8
                 w[k][0] = __ldg(q); w[k][1] = __ldg(q + 1); w[k][2] = __ldg(q + 2);
             }
         } else {
-        #pragma unroll
-        for (int k = 0; k < NR; ++k) {
-            const int t = tid + k * SC_NT;
-            const int r = t / NG, g = t - r * NG;
-            const int y = y0 - 7 + r, x = x0 - 8 + 4 * g;
-            w[k][0] = w[k][1] = w[k][2] = 0u;
-            if (t < NTASK && y >= 0 && y < H && x + 3 >= 0 && x < W) {
-                if (vec_ok && x >= 0 && x + 3 < W) {
-                    const uint32_t* q = reinterpret_cast<const uint32_t*>(img + (size_t)y * src_pitch + (size_t)x * 3);
-                    w[k][0] = __ldg(q); w[k][1] = __ldg(q + 1); w[k][2] = __ldg(q + 2);
-                } else {
-                    uint8_t bytes[12];
-                    #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int xx = x + j;
-                        const bool in = xx >= 0 && xx < W;
-                        const uint8_t* q = img + (size_t)y * src_pitch + (size_t)(in ? xx : 0) * 3;
-                        bytes[3 * j] = in ? q[0] : 0; bytes[3 * j + 1] = in ? q[1] : 0; bytes[3 * j + 2] = in ? q[2] : 0;
+            #pragma unroll
+            for (int k = 0; k < NR; ++k) {
+                const int t = tid + k * SC_NT;
+                const int r = t / NG, g = t - r * NG;
+                const int y = y0 - 8 + r, x = x0 - 8 + 4 * g;
+                w[k][0] = w[k][1] = w[k][2] = 0u;
+                if (t < NTASK && y >= 0 && y < H && x + 3 >= 0 && x < W) {
+                    if (vec_ok && x >= 0 && x + 3 < W) {
+                        const uint32_t* q = reinterpret_cast<const uint32_t*>(img + (size_t)y * src_pitch + (size_t)x * 3);
+                        w[k][0] = __ldg(q); w[k][1] = __ldg(q + 1); w[k][2] = __ldg(q + 2);
+                    } else {
+                        uint8_t bytes[12];
+                        #pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int xx = x + j;
+                            const bool in = xx >= 0 && xx < W;
+                            const uint8_t* q = img + (size_t)y * src_pitch + (size_t)(in ? xx : 0) * 3;
+                            bytes[3 * j] = in ? q[0] : 0; bytes[3 * j + 1] = in ? q[1] : 0; bytes[3 * j + 2] = in ? q[2] : 0;
+                        }
+                        #pragma unroll
+                        for (int j = 0; j < 3; ++j)
+                            w[k][j] = bytes[4 * j] | (bytes[4 * j + 1] << 8) | (bytes[4 * j + 2] << 16) | ((uint32_t)bytes[4 * j + 3] << 24);
                     }
-                    #pragma unroll
-                    for (int j = 0; j < 3; ++j)
-                        w[k][j] = bytes[4 * j] | (bytes[4 * j + 1] << 8) | (bytes[4 * j + 2] << 16) | ((uint32_t)bytes[4 * j + 3] << 24);
                 }
             }
-        }
         }
         #pragma unroll
         for (int k = 0; k < NR; ++k) {
@@ -445,22 +459,22 @@ canny_screen_kernel(const __grid_constant__ ScreenK K, int H, int W, const uint8
     }
     __syncthreads();
 
-    om_f32x2 wp[7];
-    #pragma unroll
-    for (int j = 0; j < 7; ++j) wp[j] = om_pack2(K.w[j], K.w[j]);
-
-    // ---- Gaussian along axis 0: a thread slides down 11 rows of a column pair
+    // ---- Gaussian along axis 0: a thread slides down 12 rows of a column pair (the last segment has 8)
     {
-        constexpr int NP = SG_W / 2, NSEG = SV_H / 11;
+        om_f32x2 wp[7];
+        #pragma unroll
+        for (int j = 0; j < 7; ++j) wp[j] = om_pack2(K.w[j], K.w[j]);
+        constexpr int NP = SG_W / 2, SEG = 12, NSEG = (SV_H + SEG - 1) / SEG;
         for (int t = tid; t < NP * NSEG; t += SC_NT) {
             const int seg = t / NP, pr = t - seg * NP;
-            const float* g = &sm.G[(seg * 11) * SG_W + 2 * pr];
-            om_f32x2 v[23];
+            const int r0 = seg * SEG, nrow = min(SEG, SV_H - r0);
+            const float* g = &sm.G[r0 * SG_W + 2 * pr];
+            om_f32x2 v[SEG + 12];
             #pragma unroll
-            for (int k = 0; k < 23; ++k) v[k] = *reinterpret_cast<const om_f32x2*>(g + k * SG_W);
+            for (int k = 0; k < SEG + 12; ++k) v[k] = (k < nrow + 12) ? *reinterpret_cast<const om_f32x2*>(g + k * SG_W) : 0ull;
             #pragma unroll
-            for (int o = 0; o < 11; ++o)
-                *reinterpret_cast<om_f32x2*>(&sm.V[(seg * 11 + o) * SG_W + 2 * pr]) = om_sym13(v + o, wp);
+            for (int o = 0; o < SEG; ++o)
+                if (o < nrow) *reinterpret_cast<om_f32x2*>(&sm.V[(r0 + o) * SG_W + 2 * pr]) = om_sym13(v + o, wp);
         }
     }
     __syncthreads();
@@ -469,23 +483,23 @@ canny_screen_kernel(const __grid_constant__ ScreenK K, int H, int W, const uint8
     // the row, so every 128-bit shared-memory access of a warp is a run of consecutive chunks (no bank conflicts)
     float* const S = sm.G;
     {
-        constexpr int NG = SS_W / 4;                     // 33 groups: S columns 0 .. 131 (130, 131 are padding)
+        constexpr int NG = SS_W / 4;                     // 33 groups: S columns 0 .. 131
         for (int t = tid; t < SV_H * NG; t += SC_NT) {
             const int r = t / NG, g = t - r * NG;
-            // S[r][c] = sum_k w[k] V[r][c + 1 + k]: columns 4g+1 .. 4g+16 of V, loaded as the chunks 4g .. 4g+19
+            // S[r][c] = sum_k w[k] V[r][c + k]: the chunks 4g .. 4g+15 of V
             const float4* vp = reinterpret_cast<const float4*>(&sm.V[r * SG_W + 4 * g]);
-            float v[20];
+            float v[16];
             #pragma unroll
-            for (int k = 0; k < 5; ++k) {
+            for (int k = 0; k < 4; ++k) {
                 const float4 q = vp[k];
                 v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
             }
             float o[4];
             #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                float a = v[7 + j] * K.w[6];
+                float a = v[6 + j] * K.w[6];
                 #pragma unroll
-                for (int i = 0; i < 6; ++i) a = fmaf(v[1 + j + i] + v[13 + j - i], K.w[i], a);
+                for (int i = 0; i < 6; ++i) a = fmaf(v[j + i] + v[12 + j - i], K.w[i], a);
                 o[j] = a;
             }
             if (border) {
@@ -499,118 +513,292 @@ canny_screen_kernel(const __grid_constant__ ScreenK K, int H, int W, const uint8
     __syncthreads();
     if (border) {
         // ndi.sobel mode='reflect': a neighbour outside the image is the pixel itself clamped to the image
+        // (S row r <-> image row y0 - 2 + r, column c <-> x0 - 2 + c; only the rows / columns -1 and H / W are read)
         for (int i = tid; i < SS_W; i += SC_NT) {
-            if (y0 == 0) S[i] = S[SS_W + i];
-            const int rl = H - (y0 - 1);                       // row of image row H
+            if (y0 == 0) S[1 * SS_W + i] = S[2 * SS_W + i];
+            const int rl = H - (y0 - 2);                       // row of image row H
             if (rl >= 1 && rl < SV_H) S[rl * SS_W + i] = S[(rl - 1) * SS_W + i];
         }
         __syncthreads();
         for (int i = tid; i < SV_H; i += SC_NT) {
-            if (x0 == 0) S[i * SS_W] = S[i * SS_W + 1];
-            const int cl = W - (x0 - 1);
+            if (x0 == 0) S[i * SS_W + 1] = S[i * SS_W + 2];
+            const int cl = W - (x0 - 2);
             if (cl >= 1 && cl < SS_W) S[i * SS_W + cl] = S[i * SS_W + cl - 1];
         }
         __syncthreads();
     }
 
-    // ---- Sobel and |gradient|^2 against the two thresholds: a thread takes four pixels of a row
+    // ---- Sobel, |gradient|^2 for the tile and a 1-pixel halo: a thread takes four pixels of a row; the pixels that may
+    // reach the low threshold (a few per cent of an image) are marked in the candidate words
+    float* const M2 = sm.V;          // M2[r][c] <-> pixel (y0 - 1 + r, x0 - 1 + c) from S rows r .. r+2, columns c .. c+2
+    const float Ec = K.ec[border ? 1 : 0], Em = K.em[border ? 1 : 0];
+    const float lo_no = fmaxf(K.tl - Em, 0.0f), lo_yes = K.tl + Em, hi_no = fmaxf(K.th - Em, 0.0f), hi_yes = K.th + Em;
+    const float lo_no2 = lo_no * lo_no * 0.999999f;            // (the squares' own rounding)
     {
-        const int lane = tid & 31;
-        static_assert((SC_H * (SC_W / 4)) % 32 == 0 && SC_NT % 32 == 0, "whole warps stay in the loop (ballots)");
-        for (int t = tid; t < SC_H * (SC_W / 4); t += SC_NT) {
-            const int i = t / (SC_W / 4), g = t - i * (SC_W / 4);
-            bool lo = false, hi = false;
-            if (i < SC_H && y0 + i < H) {
-                float s[3][6];
-                #pragma unroll
-                for (int r = 0; r < 3; ++r) {
-                    const float4 a = *reinterpret_cast<const float4*>(&S[(i + r) * SS_W + 4 * g]);
-                    const float2 c = *reinterpret_cast<const float2*>(&S[(i + r) * SS_W + 4 * g + 4]);
-                    s[r][0] = a.x; s[r][1] = a.y; s[r][2] = a.z; s[r][3] = a.w; s[r][4] = c.x; s[r][5] = c.y;
-                }
-                float dc[6], e[3][4];
-                #pragma unroll
-                for (int c = 0; c < 6; ++c) dc[c] = s[2][c] - s[0][c];
-                #pragma unroll
-                for (int r = 0; r < 3; ++r)
-                    #pragma unroll
-                    for (int j = 0; j < 4; ++j) e[r][j] = s[r][j + 2] - s[r][j];
-                float mx = 0.0f;
-                #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float is = fmaf(2.0f, dc[j + 1], dc[j]) + dc[j + 2];
-                    const float js = fmaf(2.0f, e[1][j], e[0][j]) + e[2][j];
-                    float m2 = fmaf(is, is, js * js);
-                    if (border && x0 + 4 * g + j >= W) m2 = 0.0f;
-                    mx = fmaxf(mx, m2);
-                }
-                lo = mx >= K.lo2; hi = mx >= K.hi2;
+        constexpr int NG = SM_W / 4;
+        for (int t = tid; t < SM_H * NG; t += SC_NT) {
+            const int r = t / NG, g = t - r * NG;
+            float s[3][6];
+            #pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float4 a = *reinterpret_cast<const float4*>(&S[(r + k) * SS_W + 4 * g]);
+                // (the last group reads two floats past the row: finite values of the next row / the V buffer, for the
+                //  unused columns 130, 131)
+                const float2 c = *reinterpret_cast<const float2*>(&S[(r + k) * SS_W + 4 * g + 4]);
+                s[k][0] = a.x; s[k][1] = a.y; s[k][2] = a.z; s[k][3] = a.w; s[k][4] = c.x; s[k][5] = c.y;
             }
-            // a warp = one row, lanes 0-15 / 16-31 = the two 64-pixel halves
-            const uint32_t bl = __ballot_sync(0xFFFFFFFFu, lo), bh = __ballot_sync(0xFFFFFFFFu, hi);
-            if (lane == 0 && i < SC_H) {
-                const int sy = i >> 5;
-                if (bl & 0x0000FFFFu) atomicOr(&sm.flags[(2 * sy) * 2], 1u);
-                if (bl & 0xFFFF0000u) atomicOr(&sm.flags[(2 * sy + 1) * 2], 1u);
-                if (bh & 0x0000FFFFu) atomicOr(&sm.flags[(2 * sy) * 2 + 1], 1u);
-                if (bh & 0xFFFF0000u) atomicOr(&sm.flags[(2 * sy + 1) * 2 + 1], 1u);
+            float dc[6], e[3][4], o[4];
+            #pragma unroll
+            for (int c = 0; c < 6; ++c) dc[c] = s[2][c] - s[0][c];
+            #pragma unroll
+            for (int k = 0; k < 3; ++k)
+                #pragma unroll
+                for (int j = 0; j < 4; ++j) e[k][j] = s[k][j + 2] - s[k][j];
+            #pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float is = fmaf(2.0f, dc[j + 1], dc[j]) + dc[j + 2];
+                const float js = fmaf(2.0f, e[1][j], e[0][j]) + e[2][j];
+                o[j] = fmaf(is, is, js * js);
+            }
+            *reinterpret_cast<float4*>(&M2[r * SM_W + 4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
+            if (fmaxf(fmaxf(o[0], o[1]), fmaxf(o[2], o[3])) >= lo_no2 && r >= 1 && r <= SC_H) {
+                const int i = r - 1, y = y0 + i;
+                #pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int j = 4 * g + k - 1, x = x0 + j;       // eroded_mask: the 1-pixel border of the image never qualifies
+                    if (o[k] >= lo_no2 && j >= 0 && j < SC_W && y >= 1 && y <= H - 2 && x >= 1 && x <= W - 2)
+                        atomicOr(&sm.cand[i * (SC_W / 32) + (j >> 5)], 1u << (j & 31));
+                }
             }
         }
     }
     __syncthreads();
-    if (tid < 4) {
-        const int tx = 2 * blockIdx.x + (tid & 1), ty = 2 * blockIdx.y + (tid >> 1);
-        if (tx < ntx && ty < nty)
-            tile_flags[((size_t)b * nty + ty) * ntx + tx] = (uint8_t)((sm.flags[2 * tid] ? 1u : 0u) | (sm.flags[2 * tid + 1] ? 2u : 0u));
+
+    // ---- words without a candidate: both planes are zero there (one thread per word)
+    if (tid < SC_H * (SC_W / 32) && sm.cand[tid] == 0u) {
+        const int i = tid >> 2, xw = (x0 >> 5) + (tid & 3), y = y0 + i;
+        if (y < H && xw < nw) {
+            low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
+            high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
+        }
+    }
+    // ---- thresholds and non-maximum suppression of the candidates, decided in float32 where the error bounds allow; a
+    // warp owns 32 pixels of a row and writes their word of the two planes
+    {
+        const int lane = tid & 31, warp = tid >> 5;
+        for (int task = warp; task < SC_H * (SC_W / 32); task += SC_NT / 32) {
+            const uint32_t cw = sm.cand[task];
+            if (cw == 0u) continue;                          // (uniform over the warp)
+            const int i = task >> 2, q = task & 3;
+            const int j = q * 32 + lane;
+            const int y = y0 + i;
+            bool lo = false, hi = false, undecided = false;
+            if ((cw >> lane) & 1u) {
+                const float m = __fsqrt_rn(M2[(i + 1) * SM_W + (j + 1)]);
+                if (m >= lo_no) {
+                    undecided = m < lo_yes;
+                    // the gradient again (S rows i+1 .. i+3 around row i+2 <-> y, columns j+1 .. j+3 around j+2 <-> x)
+                    const float* sp = &S[(i + 1) * SS_W + (j + 1)];
+                    const float s_ul = sp[0], s_uc = sp[1], s_ur = sp[2];
+                    const float s_cl = sp[SS_W], s_cr = sp[SS_W + 2];
+                    const float s_dl = sp[2 * SS_W], s_dc = sp[2 * SS_W + 1], s_dr = sp[2 * SS_W + 2];
+                    const float is = fmaf(2.0f, s_dc - s_uc, s_dl - s_ul) + (s_dr - s_ur);
+                    const float js = fmaf(2.0f, s_cr - s_cl, s_ur - s_ul) + (s_dr - s_dl);
+                    const float ai = fabsf(is), aj = fabsf(js);
+                    bool keep = false;
+                    if (!(ai > Ec) || !(aj > Ec) || !(fabsf(ai - aj) > 2.0f * Ec)) {
+                        undecided = true;
+                    } else {
+                        // neighbours along the gradient: (dr1, dc1) straight, (dr2, dc2) diagonal, and their mirrors
+                        const bool up = is > 0.0f, right = js > 0.0f, steep = ai > aj;
+                        const bool c1 = up == right;             // cond1; else cond2
+                        const int dr1 = steep ? (c1 ? 1 : -1) : 0, dc1 = steep ? 0 : 1;
+                        const int dr2 = c1 ? 1 : -1, dc2 = 1;
+                        const float num = steep ? aj : ai, den = steep ? ai : aj;
+                        const float* mp = &M2[(i + 1) * SM_W + (j + 1)];
+                        const float n11 = __fsqrt_rn(mp[dr1 * SM_W + dc1]), n12 = __fsqrt_rn(mp[dr2 * SM_W + dc2]);
+                        const float n21 = __fsqrt_rn(mp[-dr1 * SM_W - dc1]), n22 = __fsqrt_rn(mp[-dr2 * SM_W - dc2]);
+                        const float dmn = den - num, rhs = m * den;
+                        const float lp = fmaf(n12, num, n11 * dmn), lm = fmaf(n22, num, n21 * dmn);
+                        const float dp = rhs - lp, dm = rhs - lm;
+                        const float base = 2.0f * Em * den + 1e-3f;
+                        const float tp = base + 2.0f * Ec * (n11 + n12 + m) + 1e-6f * (rhs + lp);
+                        const float tm = base + 2.0f * Ec * (n21 + n22 + m) + 1e-6f * (rhs + lm);
+                        if (!(fabsf(dp) > tp) || !(fabsf(dm) > tm)) undecided = true;
+                        else keep = dp > 0.0f && dm > 0.0f;
+                    }
+                    if (!undecided && keep) {
+                        lo = true;
+                        if (m >= hi_yes) hi = true;
+                        else if (m >= hi_no) { undecided = true; lo = false; }
+                    }
+                }
+            }
+            if (undecided) {
+                const int sub = (i >> 5) * 2 + (j >> 6);
+                const uint32_t pos = atomicAdd(&sm.sub_cnt[sub], 1u);
+                if (pos < (uint32_t)K.sub_cap) sm.sub_list[sub][pos] = (uint16_t)((i << 8) | j);
+            }
+            const uint32_t wl = __ballot_sync(0xFFFFFFFFu, lo), wh = __ballot_sync(0xFFFFFFFFu, hi);
+            const int xw = (x0 >> 5) + q;
+            if (lane == 0 && y < H && xw < nw) {
+                low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = wl;
+                high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = wh;
+            }
+        }
+    }
+    __syncthreads();
+    // ---- the undecided pixels of every 64x32 tile: listed for canny_resolve_kernel, or the whole tile to the dense
+    // float64 kernel when there are too many (or the list is full)
+    {
+        const int warp = tid >> 5, lane = tid & 31;
+        if (warp < 4) {
+            const int sub = warp;
+            const uint32_t n = sm.sub_cnt[sub];
+            const int tx = 2 * blockIdx.x + (sub & 1), ty = 2 * blockIdx.y + (sub >> 1);
+            if (n > 0 && tx < ntx && ty < nty) {
+                bool dense = n > (uint32_t)K.sub_cap;
+                uint32_t base = 0;
+                if (!dense) {
+                    if (lane == 0) base = atomicAdd(pix_count, n);
+                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    if (base + n > K.pix_cap) {
+                        dense = true;                // the reservation does not fit: void the part of it inside the list
+                        for (uint32_t k = base + lane; k < min(base + n, K.pix_cap); k += 32) pix_list[k] = make_uint2(0xFFFFFFFFu, 0u);
+                    }
+                }
+                if (dense) {
+                    if (lane == 0) tile_list[atomicAdd(tile_count, 1u)] = (uint32_t)((b * nty + ty) * ntx + tx);
+                } else {
+                    for (uint32_t k = lane; k < n; k += 32) {
+                        const uint32_t c = sm.sub_list[sub][k];
+                        pix_list[base + k] = make_uint2((uint32_t)b, ((uint32_t)(y0 + (int)(c >> 8)) << 16) | (uint32_t)(x0 + (int)(c & 255u)));
+                    }
+                }
+            }
+        }
     }
 }
 
-// The tiles that can hold an edge pixel: a possible low pixel in the tile, and a chain of such tiles (8-neighbours) to a
-// tile with a possible high pixel (connected pixels lie in the same or in neighbouring tiles).  One warp per image;
-// appends the tiles to the work list of the float64 kernel.
-__global__ void __launch_bounds__(32)
-canny_tiles_kernel(int ntx, int nty, const uint8_t* __restrict__ tile_flags, uint32_t* __restrict__ tile_list,
-                   uint32_t* __restrict__ tile_count) {
-    extern __shared__ uint32_t tsm[];          // [nty + 2] low rows, [nty + 2] reached rows (one zero row above and below)
-    uint32_t* const lo = tsm + 1;
-    uint32_t* const R = tsm + (nty + 2) + 1;
-    const int lane = threadIdx.x, b = blockIdx.x;
-    const uint8_t* f = tile_flags + (size_t)b * nty * ntx;
-    if (lane == 0) { lo[-1] = lo[nty] = 0u; R[-1] = R[nty] = 0u; }
-    for (int r = lane; r < nty; r += 32) {
-        uint32_t l = 0, h = 0;
-        for (int c = 0; c < ntx; ++c) {
-            const uint32_t v = f[r * ntx + c];
-            l |= (v & 1u) << c; h |= ((v >> 1) & 1u) << c;
-        }
-        lo[r] = l; R[r] = h & l;
-    }
-    __syncwarp();
-    for (;;) {
-        bool changed = false;
-        for (int r = lane; r < nty; r += 32) {
-            uint32_t n = R[r - 1] | R[r] | R[r + 1];
-            n = (n | (n << 1) | (n >> 1)) & lo[r];
-            if (n != R[r]) { R[r] = n; changed = true; }      // (monotone: the order of the updates does not matter)
+// ------------------------------------------------------------------ canny: float64 for single pixels
+// The reference's float64 operation sequence (the same device functions as the dense kernel above) for one listed
+// pixel per warp: L on the 17x17 window -> axis-0 pass on 5 rows -> smoothed 5x5 (/ bleed-over) -> |gradient| 3x3 ->
+// thresholds and non-maximum suppression of the centre -> its bits are OR-ed into the two planes.
+constexpr int RS_NT = 256, RS_WARPS = RS_NT / 32;
+struct ResolveWarp {
+    double L[17 * 17];       // L / 255, rows y-8 .. y+8, columns x-8 .. x+8; 0 outside the image
+    double V[5 * 17];        // rows y-2 .. y+2
+    double S[5 * 5];         // rows y-2 .. y+2, columns x-2 .. x+2 (in-image entries)
+    double M[3 * 3];
+};
+
+__global__ void __launch_bounds__(RS_NT)
+canny_resolve_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* __restrict__ src, long long src_pitch,
+                     long long src_stride, uint32_t* __restrict__ low_plane, uint32_t* __restrict__ high_plane, int nw,
+                     long long plane_stride, const uint2* __restrict__ pix_list, const uint32_t* __restrict__ pix_count,
+                     unsigned pix_cap) {
+    __shared__ double lut[256];
+    __shared__ ResolveWarp wsm[RS_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    lut[tid] = __ddiv_rn((double)tid, 255.0);
+    __syncthreads();
+    ResolveWarp& R = wsm[warp];
+    const uint32_t n = min(*pix_count, pix_cap);
+    for (uint32_t item = blockIdx.x * RS_WARPS + warp; item < n; item += gridDim.x * RS_WARPS) {
+        const uint2 e = pix_list[item];
+        if (e.x == 0xFFFFFFFFu) continue;                  // voided reservation (its tile went to the dense kernel)
+        const int b = (int)e.x, y = (int)(e.y >> 16), x = (int)(e.y & 0xFFFFu);
+        const uint8_t* img = src + (size_t)b * src_stride;
+        __syncwarp();
+        for (int i = lane; i < 17 * 17; i += 32) {
+            const int r = i / 17, c = i - r * 17;
+            const int yy = y - 8 + r, xx = x - 8 + c;
+            double v = 0.0;
+            if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+                const uint8_t* q = img + (size_t)yy * src_pitch + (size_t)xx * 3;
+                v = lut[(19595u * q[0] + 38470u * q[1] + 7471u * q[2] + 0x8000u) >> 16];
+            }
+            R.L[i] = v;
         }
         __syncwarp();
-        if (!__any_sync(0xFFFFFFFFu, changed)) break;
-    }
-    for (int r0 = 0; r0 < nty; r0 += 32) {
-        const int r = r0 + lane;
-        const uint32_t bits = (r < nty) ? R[r] : 0u;
-        const int n = __popc(bits);
-        int incl = n;
-        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= o) incl += t; }
-        const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-        uint32_t base = 0;
-        if (lane == 0 && total > 0) base = atomicAdd(tile_count, (uint32_t)total);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0) + (uint32_t)(incl - n);
-        uint32_t rest = bits;
-        while (rest) {
-            const int c = __ffs(rest) - 1;
-            rest &= rest - 1;
-            tile_list[base++] = (uint32_t)((b * nty + r) * ntx + c);
+        for (int i = lane; i < 5 * 17; i += 32) {
+            const int r = i / 17, c = i - r * 17;
+            double v[13];
+            #pragma unroll
+            for (int k = 0; k < 13; ++k) v[k] = R.L[(r + k) * 17 + c];
+            R.V[i] = sym13(v, K.w);
+        }
+        __syncwarp();
+        if (lane < 25) {
+            const int r = lane / 5, c = lane - r * 5;
+            const int yy = y - 2 + r, xx = x - 2 + c;
+            double s = 0.0;
+            if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+                double v[13];
+                #pragma unroll
+                for (int k = 0; k < 13; ++k) v[k] = R.V[r * 17 + c + k];
+                const double t = sym13(v, K.w);
+                #pragma unroll
+                for (int k = 0; k < 13; ++k) v[k] = (yy + k - 6 >= 0 && yy + k - 6 < H) ? 1.0 : 0.0;
+                const double a = sym13(v, K.w);                  // gaussian_filter(ones): axis 0 ...
+                #pragma unroll
+                for (int k = 0; k < 13; ++k) v[k] = (xx + k - 6 >= 0 && xx + k - 6 < W) ? a : 0.0;
+                s = __ddiv_rn(t, __dadd_rn(sym13(v, K.w), K.eps));   // ... then axis 1, + eps
+            }
+            R.S[lane] = s;
+        }
+        __syncwarp();
+        // ndi.sobel (reflect) at image pixel (yy, xx) from the 5x5 window
+        auto sobel = [&](int yy, int xx, double& is, double& js) {
+            const int ru = max(yy - 1, 0) - (y - 2), rc = yy - (y - 2), rd = min(yy + 1, H - 1) - (y - 2);
+            const int cl = max(xx - 1, 0) - (x - 2), cc = xx - (x - 2), cr = min(xx + 1, W - 1) - (x - 2);
+            const double s_ul = R.S[ru * 5 + cl], s_uc = R.S[ru * 5 + cc], s_ur = R.S[ru * 5 + cr];
+            const double s_cl = R.S[rc * 5 + cl], s_cr = R.S[rc * 5 + cr];
+            const double s_dl = R.S[rd * 5 + cl], s_dc = R.S[rd * 5 + cc], s_dr = R.S[rd * 5 + cr];
+            const double dl = __dsub_rn(s_dl, s_ul), dc = __dsub_rn(s_dc, s_uc), dr = __dsub_rn(s_dr, s_ur);
+            is = __dadd_rn(__dmul_rn(dc, 2.0), __dadd_rn(dl, dr));
+            const double eu = __dsub_rn(s_ur, s_ul), ec = __dsub_rn(s_cr, s_cl), ed = __dsub_rn(s_dr, s_dl);
+            js = __dadd_rn(__dmul_rn(ec, 2.0), __dadd_rn(eu, ed));
+        };
+        if (lane < 9) {
+            const int r = lane / 3, c = lane - r * 3;
+            double is, js;
+            sobel(y - 1 + r, x - 1 + c, is, js);
+            R.M[lane] = __dsqrt_rn(__dadd_rn(__dmul_rn(is, is), __dmul_rn(js, js)));
+        }
+        __syncwarp();
+        if (lane == 0) {
+            const double m = R.M[4];
+            bool lo = false, hi = false;
+            if (m >= K.low) {
+                double is, js;
+                sobel(y, x, is, js);
+                const bool is_down = is <= 0.0, is_up = is >= 0.0, is_left = js <= 0.0, is_right = js >= 0.0;
+                const bool cond1 = (is_up && is_right) || (is_down && is_left);
+                const bool cond2 = (is_down && is_right) || (is_up && is_left);
+                const double ai = fabs(is), aj = fabs(js);
+                auto nb = [&](int dr, int dc) { return R.M[(1 + dr) * 3 + (1 + dc)]; };
+                bool have = false;
+                double w = 0.0, n11 = 0.0, n12 = 0.0, n21 = 0.0, n22 = 0.0;
+                if (cond1) {
+                    have = true;
+                    if (ai > aj) { w = __ddiv_rn(aj, ai); n11 = nb(1, 0); n12 = nb(1, 1); n21 = nb(-1, 0); n22 = nb(-1, -1); }
+                    else         { w = __ddiv_rn(ai, aj); n11 = nb(0, 1); n12 = nb(1, 1); n21 = nb(0, -1); n22 = nb(-1, -1); }
+                } else if (cond2) {
+                    have = true;
+                    if (ai < aj) { w = __ddiv_rn(ai, aj); n11 = nb(0, 1); n12 = nb(-1, 1); n21 = nb(0, -1); n22 = nb(1, -1); }
+                    else         { w = __ddiv_rn(aj, ai); n11 = nb(-1, 0); n12 = nb(-1, 1); n21 = nb(1, 0); n22 = nb(1, -1); }
+                }
+                if (have) {
+                    const double omw = __dsub_rn(1.0, w);
+                    const bool c_plus = __dadd_rn(__dmul_rn(n12, w), __dmul_rn(n11, omw)) <= m;
+                    const bool c_minus = __dadd_rn(__dmul_rn(n22, w), __dmul_rn(n21, omw)) <= m;
+                    if (c_plus && c_minus) { lo = m > 0.0; hi = lo && (m >= K.high); }
+                }
+            }
+            const size_t wi = (size_t)b * plane_stride + (size_t)y * nw + (x >> 5);
+            if (lo) atomicOr(&low_plane[wi], 1u << (x & 31));
+            if (hi) atomicOr(&high_plane[wi], 1u << (x & 31));
         }
     }
 }
@@ -882,8 +1070,15 @@ namespace {
 struct ObjMaskLayout {
     int nw, ntx, nty;
     long long plane_words;
-    size_t o_flags, o_list, o_count, total;
+    unsigned pix_cap;
+    size_t o_tiles, o_pix, o_count, total;
 };
+// test knobs (ssad_obj_mask_test_knobs): scale of the float32 error margins, undecided pixels a tile may list,
+// list entries per image
+float g_margin_scale = 1.0f;
+int g_sub_cap = ssad::SUB_CAP;
+int g_pix_per_image = 4096;
+
 ObjMaskLayout obj_mask_layout(int batch, int height, int width) {
     ObjMaskLayout L;
     L.nw = (width + 31) / 32;
@@ -892,9 +1087,11 @@ ObjMaskLayout obj_mask_layout(int batch, int height, int width) {
     L.plane_words = (long long)height * L.nw;
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
     const size_t ntile = (size_t)batch * L.ntx * L.nty;
-    L.o_flags = up((size_t)batch * 3 * (size_t)L.plane_words * sizeof(uint32_t));
-    L.o_list = L.o_flags + up(ntile);
-    L.o_count = L.o_list + up(ntile * sizeof(uint32_t));
+    const size_t cap = (size_t)batch * 4096;              // (the workspace is sized for the default knob)
+    L.pix_cap = cap > 0x7FFFFFFFull ? 0x7FFFFFFFu : (unsigned)cap;
+    L.o_tiles = up((size_t)batch * 3 * (size_t)L.plane_words * sizeof(uint32_t));
+    L.o_pix = L.o_tiles + up(ntile * sizeof(uint32_t));
+    L.o_count = L.o_pix + up((size_t)L.pix_cap * sizeof(uint2));
     L.total = L.o_count + 256;
     return L;
 }
@@ -905,8 +1102,18 @@ extern "C" size_t ssad_obj_mask_workspace(int32_t batch, int32_t height, int32_t
     return obj_mask_layout(batch, height, width).total;
 }
 
-// kernels one ssad_obj_mask call launches (bench.py's gpu_launches): screen, tiles, float64 canny, bit planes
+// kernels one ssad_obj_mask call launches (bench.py's gpu_launches): float32 canny, dense float64 tiles, float64 pixels,
+// bit planes
 extern "C" int ssad_obj_mask_launches(void) { return 4; }
+
+// Test hook (tests/test_gpu_objmask.py): widen the float32 error margins by `margin_scale` (more pixels take the
+// float64 paths), cap the undecided pixels a tile may list (0: every tile with one goes to the dense kernel) and the
+// list entries per image.  Arguments <= 0 restore the defaults.  Results must not depend on any of them.
+extern "C" void ssad_obj_mask_test_knobs(float margin_scale, int32_t sub_cap, int32_t pix_per_image) {
+    g_margin_scale = margin_scale > 0.0f ? margin_scale : 1.0f;
+    g_sub_cap = (sub_cap >= 0 && sub_cap <= ssad::SUB_CAP) ? sub_cap : ssad::SUB_CAP;
+    g_pix_per_image = (pix_per_image >= 0 && pix_per_image <= 4096) ? pix_per_image : 4096;
+}
 
 extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
                              int64_t src_stride, const SsadCannyConsts* consts, uint32_t* mask_bits, int32_t mask_pitch_words,
@@ -915,7 +1122,7 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
     if (src_pitch < 3ll * width || mask_pitch_words < (width + 31) / 32) return SSAD_EINVAL;
     if (batch == 0) return SSAD_OK;
     if (width > 1024 || width < 13 || height < 13) return SSAD_EUNSUPPORTED;   // one lane per row word; 6-pixel border classes
-    if (batch > 65535) return SSAD_EUNSUPPORTED;
+    if (batch > 65535 || height > 65535) return SSAD_EUNSUPPORTED;
     const ObjMaskLayout L = obj_mask_layout(batch, height, width);
     if ((unsigned long long)batch * L.ntx * L.nty > 0xFFFFFFFFull) return SSAD_EUNSUPPORTED;
     if (!workspace || workspace_bytes < L.total) return SSAD_EWORKSPACE;
@@ -924,20 +1131,23 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
     ssad::CannyK K;
     for (int i = 0; i < 13; ++i) K.w[i] = consts->gauss_w[i];
     K.low = consts->low; K.high = consts->high; K.eps = consts->eps;
-    ssad::ScreenK SK;
-    for (int i = 0; i < 7; ++i) SK.w[i] = (float)consts->gauss_w[i];
+    ssad::C32K FK;
+    for (int i = 0; i < 7; ++i) FK.w[i] = (float)consts->gauss_w[i];
+    FK.tl = (float)(consts->low * 255.0); FK.th = (float)(consts->high * 255.0);
+    FK.ec[0] = 0.003f * g_margin_scale; FK.em[0] = 0.0045f * g_margin_scale;
+    FK.ec[1] = 0.0125f * g_margin_scale; FK.em[1] = 0.018f * g_margin_scale;
+    FK.sub_cap = g_sub_cap;
     {
-        const float lo = (float)(consts->low * 255.0) - ssad::kScreenMargin, hi = (float)(consts->high * 255.0) - ssad::kScreenMargin;
-        SK.lo2 = lo > 0.0f ? lo * lo : 0.0f;
-        SK.hi2 = hi > 0.0f ? hi * hi : 0.0f;
+        const unsigned long long cap = (unsigned long long)batch * (unsigned)g_pix_per_image;
+        FK.pix_cap = cap < L.pix_cap ? (unsigned)cap : L.pix_cap;
     }
     const int nw = L.nw;
     const long long plane_words = L.plane_words;
     uint8_t* const wsb = static_cast<uint8_t*>(workspace);
     uint32_t* ws = static_cast<uint32_t*>(workspace);
-    uint8_t* const flags = wsb + L.o_flags;
-    uint32_t* const list = reinterpret_cast<uint32_t*>(wsb + L.o_list);
-    uint32_t* const count = reinterpret_cast<uint32_t*>(wsb + L.o_count);
+    uint32_t* const tiles = reinterpret_cast<uint32_t*>(wsb + L.o_tiles);
+    uint2* const pix = reinterpret_cast<uint2*>(wsb + L.o_pix);
+    uint32_t* const count = reinterpret_cast<uint32_t*>(wsb + L.o_count);     // [0] undecided pixels, [1] dense tiles
     static int sm_count[64];                       // SMs per device, read once
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -949,21 +1159,22 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
         if (e != cudaSuccess) return ssad_set_cuda_error(e);
         e = cudaFuncSetAttribute(ssad::canny_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ssad::CannySmem));
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(ssad::canny_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ssad::ScreenSmem));
+            e = cudaFuncSetAttribute(ssad::canny32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ssad::C32Smem));
         if (e != cudaSuccess) return ssad_set_cuda_error(e);
         sm_count[dev] = n > 0 ? n : 1;
     }
-    e = cudaMemsetAsync(count, 0, sizeof(uint32_t), st);
+    e = cudaMemsetAsync(count, 0, 2 * sizeof(uint32_t), st);
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
-    // 1. float32 screen: which 64x32 tiles can hold a pixel at the low / the high threshold (also zeroes both planes)
+    // 1. float32 canny: both planes for every pixel it can decide, the undecided pixels / tiles listed
     dim3 sgrid((width + ssad::SC_W - 1) / ssad::SC_W, (height + ssad::SC_H - 1) / ssad::SC_H, batch);
-    ssad::canny_screen_kernel<<<sgrid, ssad::SC_NT, sizeof(ssad::ScreenSmem), st>>>(SK, height, width, src, src_pitch, src_stride, flags,
-                                                                                L.ntx, L.nty, ws, ws + plane_words, nw, 3 * plane_words);
-    // 2. tiles connected to a high tile -> work list
-    ssad::canny_tiles_kernel<<<batch, 32, (size_t)(2 * (L.nty + 2)) * sizeof(uint32_t), st>>>(L.ntx, L.nty, flags, list, count);
-    // 3. float64 canny + non-maximum suppression on the listed tiles
+    ssad::canny32_kernel<<<sgrid, ssad::SC_NT, sizeof(ssad::C32Smem), st>>>(FK, height, width, src, src_pitch, src_stride, ws,
+                                                                          ws + plane_words, nw, 3 * plane_words, pix, count,
+                                                                          tiles, count + 1, L.ntx, L.nty);
+    // 2. dense float64 canny on the listed tiles (usually none), 3. float64 for the listed pixels
     ssad::canny_nms_kernel<<<sm_count[dev] * SSAD_CANNY_MINB, ssad::CT_NT, sizeof(ssad::CannySmem), st>>>(
-        K, height, width, src, src_pitch, src_stride, ws, ws + plane_words, nw, 3 * plane_words, list, count, L.ntx, L.nty);
+        K, height, width, src, src_pitch, src_stride, ws, ws + plane_words, nw, 3 * plane_words, tiles, count + 1, L.ntx, L.nty);
+    ssad::canny_resolve_kernel<<<sm_count[dev] * 4, ssad::RS_NT, 0, st>>>(K, height, width, src, src_pitch, src_stride, ws,
+                                                                        ws + plane_words, nw, 3 * plane_words, pix, count, FK.pix_cap);
     e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     // 4. hysteresis, morphology, hole filling, largest component on the bit planes: a CTA per image, a band of rows per warp

@@ -69,3 +69,25 @@ def test_spiral_needs_many_sweeps():
 
 def test_1024_single():
     _check(synth.screw_images(1, 1024, 1024, 77), "screw 1024")
+
+
+@pytest.mark.parametrize("knobs", [(30.0, -1, -1), (1.0, 0, -1), (8.0, 4, -1), (30.0, -1, 1), (300.0, -1, -1)],
+                         ids=["wide_margins", "tiles_only", "small_tile_lists", "list_overflow", "everything_undecided"])
+def test_float64_fallback_paths_give_the_same_masks(knobs):
+    """ssad_obj_mask decides in float32 where its error margins allow, per pixel or per tile in float64 elsewhere: the
+    masks must not depend on where a pixel was decided.  The knobs push pixels onto every path."""
+    from ssad_b200 import _native
+    lib = _native.load()
+    try:
+        lib.ssad_obj_mask_test_knobs(*knobs)
+        _check(synth.screw_images(3, 192, 256, 91), "screw 192x256 " + str(knobs))
+        _check(synth.texture_images(2, 160, 224, 7), "texture " + str(knobs))
+        rng = np.random.default_rng(5)
+        blocks = np.kron(rng.integers(0, 2, (2, 12, 15, 1), dtype=np.uint8), np.ones((1, 10, 10, 3), np.uint8)) * 200 + 20
+        _check(blocks.astype(np.uint8), "checker blocks " + str(knobs))
+    finally:
+        lib.ssad_obj_mask_test_knobs(-1.0, -1, -1)
+
+
+def test_1024_batch_of_three():
+    _check(synth.screw_images(3, 1024, 1024, 78), "screw 1024 x3")
