@@ -59,16 +59,16 @@ def test_rotation_covers_every_scar_angle_and_identity():
             assert tuple(size[i]) == (nw, nh), (ang, i)
 
 
-def test_sampler_rate_is_batch_bound_not_image_bound():
-    """No per-image Python work is left on the sampler path: 8x the batch costs far less than 8x the time."""
+def test_sampler_has_no_per_image_python_loop():
+    """The per-image Python loop of round 1 drew 52 k records/s at best; the vectorised derivations are several times
+    faster at large batches (generous bound: the CPU test box is shared)."""
     import time
     cfg = GeneratorConfig(**CONFIGS[1])
     rng = np.random.default_rng(0)
     P.sample_params(cfg, 64, rng)
-
-    def cost(b, reps=5):
+    best = 0.0
+    for _ in range(5):
         t = time.perf_counter()
-        for _ in range(reps):
-            P.sample_params(cfg, b, rng)
-        return (time.perf_counter() - t) / reps
-    assert cost(4096) < 5.0 * cost(512)
+        P.sample_params(cfg, 4096, rng)
+        best = max(best, 4096 / (time.perf_counter() - t))
+    assert best > 100e3, f"{best:.0f} records/s"
