@@ -63,7 +63,7 @@ typedef struct SsadImageParams {
     int16_t  donor_off[2];     /* 164: x,y of the donor window (RandomCrop, datasets.py:253) inside the donor image */
     int16_t  crop_off[2];      /* 168: x,y of the working window inside src and mask (datasets.py:243-252) */
     int16_t  donor_idx;        /* 172: index into the donor bank (datasets.py:226); -1 = the image itself */
-    uint8_t  label;            /* 174: 0 good, 1 polygon cut-paste, 2 scar (datasets.py:215) */
+    uint8_t  label;            /* 174: 0 good, 1 polygon cut-paste, 2 scar, 3 long line (datasets.py:215,357-388) */
     uint8_t  warp_en;          /* 175 */
     uint8_t  src_variant;      /* 176: 0 cut, 1 average colour, 2 random colour (datasets.py:270-293) */
     uint8_t  scar_k;           /* 177: number of scar pastes, 2..5 (datasets.py:341) */
@@ -71,7 +71,8 @@ typedef struct SsadImageParams {
     uint8_t  rnd_rgb[3];       /* 179 */
     uint8_t  jit_order[4];     /* 182: ColorJitter fn_idx permutation (0 b, 1 c, 2 s, 3 hue/no-op) */
     uint8_t  jit_en;           /* 186: bit0 brightness, bit1 contrast, bit2 saturation; 0 = no jitter */
-    uint8_t  reserved[5];      /* 187 */
+    uint8_t  line_n;           /* 187: label 3: points of the smoothed poly-line in SsadBatchDesc.line_xy (datasets.py:357-388) */
+    uint32_t src_index;        /* 188: image of `src` this record works on when SsadBatchDesc.src_indexed is set */
 } SsadImageParams;
 
 /* Batch constants (host struct, passed by pointer, copied at call time). */
@@ -98,8 +99,16 @@ typedef struct SsadBatchDesc {
     int64_t out_u8_pitch;      /* bytes per output row (>= 3 * width) */
     int64_t out_u8_stride;     /* bytes per output image */
     int32_t any_warp;          /* 1: some records have warp_en set (sizes the workspace: x is materialised once per batch) */
-    float   sat_factor_max;    /* upper bound of the enabled ColorJitter saturation factors jit_f[2] over the batch (the table-driven
-                                  kernel serves factors <= 1.25; larger ones take the arithmetic kernels) */
+    float   sat_factor_max;    /* upper bound of the enabled ColorJitter saturation factors jit_f[2] over the batch (the kernels'
+                                  tables serve factors <= 2, torchvision's whole range for saturation <= 1) */
+    int32_t src_indexed;       /* 1: record b reads source image params[b].src_index of a resident set of src_count images
+                                  (the batch is never gathered: datasets.py:211 becomes an index); 0: image b of `src` */
+    int32_t src_count;         /* images in `src` when src_indexed (SSAD_MASK_PER_IMAGE masks are then per SOURCE image:
+                                  obj_mask depends on the original only, datasets.py:232-233) */
+    int32_t line_width;        /* label 3: ImageDraw.line width, 3 image-level / 1 patch mode (datasets.py:383-388) */
+    int32_t line_max;          /* points per image in line_xy */
+    const int16_t* line_xy;    /* device [batch][line_max][2]: the poly-line vertices (x, y) of label-3 records, as ints the way
+                                  ImageDraw.line truncates them; NULL when no record has label 3 */
 } SsadBatchDesc;
 
 /* Optional per-image trace of the data-dependent decisions, for parity tests. */
@@ -140,6 +149,22 @@ int ssad_generate(const SsadBatchDesc* desc, const SsadImageParams* params, cons
                   const uint8_t* donor_bank, const uint32_t* mask_bits, const void* norm_lut,
                   uint8_t* out_u8, void* out_norm, int64_t* y_out, SsadDebug* debug,
                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* Contexts.  ssad_generate cuts a large batch into chunks that run side by side on helper streams; those streams and
+ * their fork / join events belong to a context.  ssad_generate uses one default context per device (created on first
+ * use under a lock), so calls from ONE host thread per device need nothing else.  Host threads that drive the same
+ * device concurrently (the reference runs 8 loader workers, datasets.py:501-508) each create their own context for the
+ * current device and call ssad_generate_ctx: the library keeps no other mutable state, so such calls are independent.
+ * A context must be used on the device it was created on. */
+typedef struct SsadContext SsadContext;
+int ssad_context_create(SsadContext** out);
+void ssad_context_destroy(SsadContext* ctx);
+int ssad_generate_ctx(SsadContext* ctx, const SsadBatchDesc* desc, const SsadImageParams* params, const uint8_t* src,
+                      const uint8_t* donor_bank, const uint32_t* mask_bits, const void* norm_lut,
+                      uint8_t* out_u8, void* out_norm, int64_t* y_out, SsadDebug* debug,
+                      void* workspace, size_t workspace_bytes, void* stream);
+/* The library reads its tuning environment (SSAD_V7_*) once, at the first call; tests that change it call this. */
+void ssad_reload_env(void);
 size_t ssad_generate_workspace(const SsadBatchDesc* desc);
 /* Number of kernels one ssad_generate call launches for this descriptor (the kernel pipeline cuts large batches into
  * chunks that run side by side on helper streams forked from, and joined back to, the caller's stream; a call that
@@ -196,11 +221,17 @@ int ssad_select_kth(const uint32_t* mask_bits, int32_t mask_pitch_words, int32_t
                     int32_t* out_xy /* [n][2] device */, int32_t* count_out, void* stream);
 
 /* paste_patch: image.paste(patch, (left, top), mask) (dataset_generator.py:268-275), in place on one dense uint8 RGB image.
- * patch [ph][pw][channels], channels in {3, 4}; mask [ph][pw] uint8 (0 keeps the image, non-zero takes the patch) or NULL:
+ * patch [ph][pw][channels], channels in {3, 4}; mask [ph][pw] uint8 (0 keeps the image, 255 takes the patch, values in
+ * between blend as Pillow's Paste.c does) or NULL:
  * then the alpha band of a 4-channel patch (the rotated scar pasted with itself as mask, datasets.py:354), else opaque.
  * The box is clipped to the image as Pillow does. */
 int ssad_paste(uint8_t* image, int32_t width, int32_t height, const uint8_t* patch, int32_t pw, int32_t ph, int32_t channels,
                const uint8_t* mask, int32_t left, int32_t top, void* stream);
+
+/* check_color_similarity (dataset_generator.py:147-159): cosine of the mean colours (float64, sklearn's normalise-then-dot
+ * order) of two dense uint8 RGB images of n_image / n_patch pixels -> out[0] (device double).  The generator's own
+ * decision (cosine > 0.99, datasets.py:295) is taken inside ssad_generate and reported in SsadDebug.cosine. */
+int ssad_color_similarity(const uint8_t* image, int32_t n_image, const uint8_t* patch, int32_t n_patch, double* out, void* stream);
 
 /* ToTensor(original) (datasets.py:394): uint8 HWC -> f32 NCHW / 255. */
 int ssad_to_tensor(int32_t n, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,

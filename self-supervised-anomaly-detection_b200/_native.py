@@ -28,6 +28,8 @@ class SsadBatchDesc(C.Structure):
         ("out_norm_dtype", C.c_int32), ("crop_align16", C.c_int32),
         ("out_u8_pitch", C.c_int64), ("out_u8_stride", C.c_int64),
         ("any_warp", C.c_int32), ("sat_factor_max", C.c_float),
+        ("src_indexed", C.c_int32), ("src_count", C.c_int32),
+        ("line_width", C.c_int32), ("line_max", C.c_int32), ("line_xy", C.c_void_p),
     ]
 
 
@@ -44,6 +46,10 @@ EXPORTS = {
     "ssad_sizeof_desc": (C.c_size_t, []),
     "ssad_sizeof_debug": (C.c_size_t, []),
     "ssad_generate": (C.c_int, [C.POINTER(SsadBatchDesc)] + [C.c_void_p] * 10 + [C.c_size_t, C.c_void_p]),
+    "ssad_generate_ctx": (C.c_int, [C.c_void_p, C.POINTER(SsadBatchDesc)] + [C.c_void_p] * 10 + [C.c_size_t, C.c_void_p]),
+    "ssad_context_create": (C.c_int, [C.POINTER(C.c_void_p)]),
+    "ssad_context_destroy": (None, [C.c_void_p]),
+    "ssad_reload_env": (None, []),
     "ssad_generate_workspace": (C.c_size_t, [C.POINTER(SsadBatchDesc)]),
     "ssad_generate_launches": (C.c_int, [C.POINTER(SsadBatchDesc), C.c_int]),
     "ssad_obj_mask": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
@@ -58,6 +64,7 @@ EXPORTS = {
     "ssad_select_kth": (C.c_int, [C.c_void_p] + [C.c_int32] * 6 + [C.c_void_p] * 4),
     "ssad_paste": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                              C.c_int32, C.c_int32, C.c_void_p]),
+    "ssad_color_similarity": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "ssad_to_tensor": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
 }
 

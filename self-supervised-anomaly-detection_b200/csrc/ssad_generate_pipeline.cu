@@ -1,4 +1,4 @@
-// ssad_generate, B200 path v7: the v6 arithmetic as a pipeline of five kernels on one stream.
+// ssad_generate: the kernel pipeline (six kernels per chunk of the batch).
 //
 // v6 runs the whole of PretextTaskDataset.__getitem__ (datasets.py:209-394) for one image inside one cluster; ncu shows
 // that kernel issue-bound with 39 % of every CTA's life spent in its short serial phases (geometry, decisions, canvas,
@@ -27,7 +27,9 @@
 #include <stdlib.h>
 #include <string.h>
 
-#include "ssad_v6_common.cuh"
+#include <mutex>
+
+#include "ssad_pipeline_common.cuh"
 
 int ssad_set_cuda_error(cudaError_t e);
 
@@ -56,7 +58,8 @@ struct alignas(16) Hdr {
     int32_t flags;               // HF_*
     int32_t cx0, cy0;            // crop window
     float fs;                    // Saturation factor of the pass's program
-    int32_t pad[2];
+    int32_t si;                  // source image (the record's src_index, or the image itself)
+    int32_t pad;
 };
 enum { HF_WARP = 1, HF_PRE = 2, HF_DEFECT = 4, HF_LUMA = 8 };
 
@@ -69,6 +72,7 @@ struct Geo7 {
     int nslab_shift;                                        // log2(nslab), or -1
     uint32_t inv_upr;                                       // ceil(2^16 / upr): tid / upr == tid * inv_upr >> 16 for tid < 256
     uint32_t smem_plan;                                     // dynamic shared memory of the plan kernel (row prefix)
+    int src_indexed;                                        // records carry their source image (else: image b of the chunk)
 };
 
 // Programmatic dependent launch: every kernel lets its successor's CTAs start as soon as its own have all started
@@ -323,7 +327,7 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
     const int cx0 = P.crop_off[0], cy0 = P.crop_off[1];
     const uint32_t* mrow0 = nullptr;
     if (d.mask_mode != SSAD_MASK_ALL)
-        mrow0 = mask_bits + (d.mask_mode == SSAD_MASK_PER_IMAGE ? (size_t)b * d.mask_stride_words : 0);
+        mrow0 = mask_bits + (d.mask_mode == SSAD_MASK_PER_IMAGE ? (size_t)(d.src_indexed ? (int)P.src_index : b) * d.mask_stride_words : 0);
     const bool defect = P.label != 0;
     const int pw = P.rect[2], ph = P.rect[3];
     if (defect && d.mask_mode != SSAD_MASK_ALL) {
@@ -480,7 +484,7 @@ lists_v7_kernel(const __grid_constant__ Geo7 g, const SsadImageParams* __restric
         float fs = 1.0f;                 // factor of the Saturation inside the pass's program, if any
         const int i0 = (ps == 0) ? 0 : (D.s_in_pre ? D.cpos : 0), i1 = (ps == 0) ? max(D.cpos, 0) : D.nops;
         for (int i = i0; i < i1; ++i) if (D.ops[i] == 2) fs = D.fac[i];
-        h.fs = fs; h.pad[0] = h.pad[1] = 0;
+        h.fs = fs; h.si = g.src_indexed ? (int32_t)p->src_index : b; h.pad = 0;
         hdr[(size_t)ps * g.batch + rank] = h;
     }
 }
@@ -501,7 +505,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     const int4 h0 = __ldg(reinterpret_cast<const int4*>(hdr + j));                  // b, kind, flags, cx0
     const int b = h0.x, kind = h0.y, flags = h0.z;
     if (b < 0) return;                           // images with nothing to do in pass 1 sit behind the lists
-    const int2 h1 = __ldg(reinterpret_cast<const int2*>(hdr + j) + 2);              // cy0, fs
+    const int4 h1 = __ldg(reinterpret_cast<const int4*>(hdr + j) + 1);              // cy0, fs, source image
     const int H = g.H, W = g.W, npix = H * W;
     ImgState* const S = state + b;
     const bool warped = (flags & HF_WARP) != 0, defect = (flags & HF_DEFECT) != 0, need_luma = (flags & HF_LUMA) != 0;
@@ -509,7 +513,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     const bool store_raw = defect && !store_pre && !warped;          // the pastes are written into x
     const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
     const int nunits = (r1 - r0) * g.upr;
-    const uint8_t* const sbase = src + (size_t)b * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;
+    const uint8_t* const sbase = src + (size_t)h1.z * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;
     const int spitch = (int)d.src_pitch;
     uint8_t* const xb = xbuf + (size_t)b * npix * 3;
     const int xpitch = W * 3;
@@ -574,7 +578,7 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
         // RGB sums of the would-be cut (dataset_generator.py:202-207 / 147-159): rows dealt over the image's warps
         if (defect && P.src_variant != 2) {
             // the cut box dealt pixel by pixel over the threads of the image's slabs, four loads in flight per channel
-            const Donor dn = donor_of(d, src, donor_bank, b, P);
+            const Donor dn = donor_of(d, src, donor_bank, h1.z, P);
             const int bw = max(dn.u_hi, 0), total = bw * max(dn.v_hi, 0);
             const uint32_t inv_bw = 0xFFFFFFFFu / (uint32_t)max(bw, 2) + 1u;
             const int stride = g.nslab * NT;
@@ -633,7 +637,7 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     uint32_t* const canvas = canvas_all + (size_t)b * g.canvas_stride;
     uint8_t* const xb = xbuf + (size_t)b * npix * 3;
     const int pitchw = (int)g.cov_pitch;
-    const Donor dn = donor_of(d, src, donor_bank, b, P);
+    const Donor dn = donor_of(d, src, donor_bank, g.src_indexed ? (int)P.src_index : b, P);
 
     // ---- check_color_similarity + variant colours (every CTA of the image decides the same; part 0 records it)
     if (tid == 0) {
@@ -965,7 +969,7 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     pdl_launch_dependents();
     pdl_wait();
     const int4 h0 = __ldg(reinterpret_cast<const int4*>(hdr + j));                  // b, kind, flags, cx0
-    const int2 h1 = __ldg(reinterpret_cast<const int2*>(hdr + j) + 2);              // cy0, fs
+    const int4 h1 = __ldg(reinterpret_cast<const int4*>(hdr + j) + 1);              // cy0, fs, source image
     const int b = h0.x, kind = h0.y;
     if (b < 0) return;
     const int H = g.H, W = g.W, npix = H * W;
@@ -973,7 +977,7 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
     const int nunits = (r1 - r0) * g.upr;
     const uint8_t* const in2 = stored ? xbuf + (size_t)b * npix * 3
-                                      : src + (size_t)b * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;
+                                      : src + (size_t)h1.z * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;
     const int in2_pitch = stored ? W * 3 : (int)d.src_pitch;
     // the first loads of the stream leave before the tables arrive
     FastCol F;
@@ -1007,26 +1011,51 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     }
 }
 
+// Tuning knobs from the environment (experiments, tests), read once at the first call (ssad_reload_env re-reads them)
+struct PipeEnv {
+    int upt, nofast, nc, lanes, chunk_mb, split, nopdl;
+};
+static PipeEnv g_env;
+static std::once_flag g_env_once;
+static void load_env() {
+    auto geti = [](const char* name, int lo, int hi) { const char* f = getenv(name); if (!f) return 0; int v = atoi(f); return (v >= lo && v <= hi) ? v : 0; };
+    g_env.upt = geti("SSAD_V7_UPT", 1, 64);
+    g_env.nofast = getenv("SSAD_V7_NOFAST") ? 1 : 0;
+    g_env.nc = geti("SSAD_V7_NC", 1, 32);
+    g_env.lanes = geti("SSAD_V7_LANES", 1, 8);
+    g_env.chunk_mb = geti("SSAD_V7_CHUNK_MB", 1, 4096);
+    g_env.split = geti("SSAD_V7_SPLIT", 1, 64);
+    g_env.nopdl = getenv("SSAD_V7_NOPDL") ? 1 : 0;
+}
+static const PipeEnv& env() {
+    std::call_once(g_env_once, load_env);
+    return g_env;
+}
+extern "C" void ssad_reload_env(void) {
+    (void)env();
+    load_env();
+}
+
 static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
+    const PipeEnv& E = env();
     g.H = d.height; g.W = d.width; g.batch = d.batch;
     if (g.W % 8 != 0 || g.W < 8) return false;
     if (!(d.sat_factor_max <= kSatMax)) return false;       // the table after Saturation covers factors up to kSatMax
     g.upr = g.W / 8;
-    int upt = UPT;                                          // units per thread and slab
-    if (const char* f = getenv("SSAD_V7_UPT")) { int v = atoi(f); if (v > 0 && v <= 64) upt = v; }
+    const int upt = E.upt > 0 ? E.upt : UPT;                // units per thread and slab
     g.rows_slab = (NT * upt + g.upr - 1) / g.upr;
     if (g.rows_slab < 1) g.rows_slab = 1;
     if (g.rows_slab > g.H) g.rows_slab = g.H;
     g.nslab = (g.H + g.rows_slab - 1) / g.rows_slab;
     g.fast = (NT % g.upr == 0 && upt == UPT && g.rows_slab * g.upr == NT * UPT && g.H % g.rows_slab == 0) ? 1 : 0;
-    if (getenv("SSAD_V7_NOFAST")) g.fast = 0;
+    if (E.nofast) g.fast = 0;
     g.nslab_shift = -1;
     for (int k = 0; k < 16; ++k) if (g.nslab == (1 << k)) g.nslab_shift = k;
     g.inv_upr = (65536u + (uint32_t)g.upr - 1u) / (uint32_t)g.upr;
     // canvas CTAs per image, per chunk; measured: fewer, longer canvas CTAs win once the grid fills the GPU, larger
     // images (taller canvases) want more
     g.ncanvas = (d.batch >= 1024 ? 1 : 2) * (d.height >= 1024 ? 2 : 1);
-    if (const char* f = getenv("SSAD_V7_NC")) { int v = atoi(f); if (v > 0 && v <= 32) g.ncanvas = v; }
+    if (E.nc > 0) g.ncanvas = E.nc;
     while ((d.max_patch_h + g.ncanvas - 1) / g.ncanvas > kCanvasRows) ++g.ncanvas;
     g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;
     g.cov_rows = (uint32_t)d.max_patch_h;
@@ -1041,6 +1070,7 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.o_hdr = g.o_sched + up(sizeof(Sched));
     g.ws_total = g.o_hdr + up((size_t)2 * d.batch * sizeof(Hdr));
     g.smem_plan = (((uint32_t)g.H + 1u) * 4u + 15u) & ~15u;
+    g.src_indexed = d.src_indexed ? 1 : 0;
     return true;
 }
 
@@ -1054,10 +1084,10 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
 // caps a chunk's x buffer, SSAD_V7_SPLIT pins the number; both measured slower than one large chunk per lane).
 struct V7Split { int nchunk, csize, nlanes; };
 static V7Split v7_split(const SsadBatchDesc& d, bool capturing) {
+    const ssad::v7::PipeEnv& E = ssad::v7::env();
     int lanes = capturing ? 4 : 2;
-    if (const char* f = getenv("SSAD_V7_LANES")) { int v = atoi(f); if (v >= 1 && v <= 8) lanes = v; }
-    size_t mb = 0;                                // measured: smaller chunks lose more to the latency chains than the L2 gives back
-    if (const char* f = getenv("SSAD_V7_CHUNK_MB")) { int v = atoi(f); if (v >= 1 && v <= 4096) mb = (size_t)v; }
+    if (E.lanes > 0) lanes = E.lanes;
+    const size_t mb = (size_t)E.chunk_mb;         // measured: smaller chunks lose more to the latency chains than the L2 gives back
     int n = 1;
     if (d.batch >= 256) {
         const size_t total = (size_t)d.height * d.width * 3 * (size_t)d.batch, lim = mb << 20;
@@ -1065,7 +1095,7 @@ static V7Split v7_split(const SsadBatchDesc& d, bool capturing) {
         n = lanes;
         if (by_size > (size_t)n) n = by_size > 64 ? 64 : (int)by_size;
     }
-    if (const char* f = getenv("SSAD_V7_SPLIT")) { int v = atoi(f); if (v >= 1 && v <= 64) n = v; }
+    if (E.split > 0) n = E.split;
     if (n > d.batch) n = d.batch;
     if (n < 1) n = 1;
     V7Split sp;
@@ -1082,60 +1112,67 @@ static size_t v7_chunk_workspace(const SsadBatchDesc& d, int csize) {
     return g.ws_total;
 }
 
-size_t ssad_v7_workspace(const SsadBatchDesc& d) {           // enough for a plain and for a captured call
+size_t ssad_pipeline_workspace(const SsadBatchDesc& d) {           // enough for a plain and for a captured call
     const V7Split s0 = v7_split(d, false), s1 = v7_split(d, true);
     const size_t a = v7_chunk_workspace(d, s0.csize) * (size_t)s0.nlanes, b = v7_chunk_workspace(d, s1.csize) * (size_t)s1.nlanes;
     return a > b ? a : b;
 }
 
-// kernels one ssad_generate call launches on this path (bench.py's gpu_launches)
-int ssad_v7_launches(const SsadBatchDesc& d, bool capturing) { return 6 * v7_split(d, capturing).nchunk; }
+// kernels one ssad_generate call launches (bench.py's gpu_launches)
+int ssad_pipeline_launches(const SsadBatchDesc& d, bool capturing) { return 6 * v7_split(d, capturing).nchunk; }
 
 static int launch_v7_chunk(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
                            const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
                            SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream, bool use_pdl);
 
-struct V7Streams {               // helper streams and fork/join events of one device, created on first use
+// A context: the helper streams and fork / join events of one device (ssad_context_create).
+struct SsadContext {
+    int device;
     cudaStream_t s[8];
     cudaEvent_t fork, join[8];
-    bool ok;
 };
-static V7Streams* v7_streams() {
-    static V7Streams per_dev[64];
-    static bool made[64];
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    V7Streams& S = per_dev[dev];
-    if (!made[dev]) {
-        made[dev] = true;
-        S.ok = cudaEventCreateWithFlags(&S.fork, cudaEventDisableTiming) == cudaSuccess;
-        for (int i = 1; i < 8 && S.ok; ++i)
-            S.ok = cudaStreamCreateWithFlags(&S.s[i], cudaStreamNonBlocking) == cudaSuccess &&
-                   cudaEventCreateWithFlags(&S.join[i], cudaEventDisableTiming) == cudaSuccess;
-    }
-    return S.ok ? &S : nullptr;
+void ssad_pipeline_context_delete(SsadContext* c);
+SsadContext* ssad_pipeline_context_new(int device) {
+    SsadContext* c = new SsadContext();
+    memset(c, 0, sizeof(*c));
+    c->device = device;
+    bool ok = cudaEventCreateWithFlags(&c->fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 1; i < 8 && ok; ++i)
+        ok = cudaStreamCreateWithFlags(&c->s[i], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&c->join[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { ssad_pipeline_context_delete(c); return nullptr; }
+    return c;
 }
+void ssad_pipeline_context_delete(SsadContext* c) {
+    if (!c) return;
+    for (int i = 1; i < 8; ++i) {
+        if (c->s[i]) cudaStreamDestroy(c->s[i]);
+        if (c->join[i]) cudaEventDestroy(c->join[i]);
+    }
+    if (c->fork) cudaEventDestroy(c->fork);
+    delete c;
+}
+int ssad_pipeline_context_device(const SsadContext* c) { return c->device; }
 
-// returns SSAD_OK when launched, SSAD_EUNSUPPORTED when the caller should use another kernel
-int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src, const uint8_t* donor_bank,
-                   const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm, int64_t* y_out,
-                   SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+// returns SSAD_OK when launched, SSAD_EUNSUPPORTED for a request this library cannot serve
+int ssad_pipeline_launch(SsadContext* HS, const SsadBatchDesc& d, const SsadImageParams* params, const uint8_t* src,
+                         const uint8_t* donor_bank, const uint32_t* mask_bits, const void* norm_lut, uint8_t* out_u8, void* out_norm,
+                         int64_t* y_out, SsadDebug* debug, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) { cap = cudaStreamCaptureStatusNone; (void)cudaGetLastError(); }
     const bool capturing = cap == cudaStreamCaptureStatusActive;
     // programmatic dependent launch pays on plain streams; inside a graph the programmatic edges cost more than they hide
-    const bool use_pdl = !capturing && getenv("SSAD_V7_NOPDL") == nullptr;
+    const bool use_pdl = !capturing && !ssad::v7::env().nopdl;
     const V7Split sp = v7_split(d, capturing);
     const int nchunk = sp.nchunk, csize = sp.csize, nlanes = sp.nlanes;
-    const size_t need = ssad_v7_workspace(d);
-    if (need == 0) return SSAD_EUNSUPPORTED;
+    const size_t need = ssad_pipeline_workspace(d);
+    if (need == 0) return SSAD_EUNSUPPORTED;                 // width not a multiple of 8, or a Saturation factor above 2
+    if (((long long)d.height * d.width) % 8 != 0) return SSAD_EUNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(src) & 15) || (d.src_pitch & 7) || (d.src_stride & 7)) return SSAD_EUNSUPPORTED;
     if (nchunk > 1 && (d.src_stride & 15)) return SSAD_EUNSUPPORTED;      // every chunk's first image must stay 16-byte aligned
     if (!workspace || workspace_bytes < need) return SSAD_EWORKSPACE;
     if (reinterpret_cast<uintptr_t>(workspace) & 255) return SSAD_EALIGN;
     const size_t ws_chunk = v7_chunk_workspace(d, csize);
-    V7Streams* const HS = (nlanes > 1) ? v7_streams() : nullptr;
-    if (nlanes > 1 && !HS) return SSAD_ELAUNCH;
     cudaError_t e = cudaSuccess;
     if (nlanes > 1) {
         e = cudaEventRecord(HS->fork, stream);
@@ -1150,11 +1187,12 @@ int ssad_launch_v7(const SsadBatchDesc& d, const SsadImageParams* params, const 
         if (nb <= 0) break;
         SsadBatchDesc dc = d;
         dc.batch = nb;
+        if (dc.line_xy) dc.line_xy += (size_t)b0 * d.line_max * 2;
         const uint32_t* mb = mask_bits;
-        if (mb && d.mask_mode == SSAD_MASK_PER_IMAGE) mb += (size_t)b0 * d.mask_stride_words;
+        if (mb && d.mask_mode == SSAD_MASK_PER_IMAGE && !d.src_indexed) mb += (size_t)b0 * d.mask_stride_words;
         const int lane = c % nlanes;             // chunks of a lane run one after the other and share its workspace
         cudaStream_t st = (lane == 0) ? stream : HS->s[lane];
-        rc = launch_v7_chunk(dc, params + b0, src + (size_t)b0 * d.src_stride, donor_bank, mb, norm_lut,
+        rc = launch_v7_chunk(dc, params + b0, d.src_indexed ? src : src + (size_t)b0 * d.src_stride, donor_bank, mb, norm_lut,
                              out_u8 ? out_u8 + (size_t)b0 * d.out_u8_stride : nullptr,
                              out_norm ? static_cast<uint8_t*>(out_norm) + (size_t)b0 * 3 * npix * norm_elem : nullptr,
                              y_out ? y_out + b0 : nullptr, debug ? debug + b0 : nullptr,

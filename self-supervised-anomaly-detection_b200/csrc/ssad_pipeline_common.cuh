@@ -1,4 +1,4 @@
-// Device code shared by the v6 (one cluster per image) and v7 (streaming kernel pipeline) generator paths:
+// Device code of the generator pipeline (ssad_generate_pipeline.cu):
 // per-image plan and tables, 8-pixel-unit stages (tables, Saturation, luma / RGB sums), paste on the fly, the two unit loops.
 #pragma once
 #include <cuda.h>
@@ -16,21 +16,12 @@ using namespace u8x;
 
 constexpr int NT = 256;
 constexpr int NWARP = NT / 32;
-constexpr int MAXC = 8;
 // table after Saturation: index = bits(2^23 + t, rounded toward zero) - 0x4B000000 + TB_OFF.  t < 0 lands in the
-// binade below 2^23 (half steps): offsets down to -2 * 64; t < 255 * kSatMax above.  Valid for Saturation factors <= kSatMax.
-constexpr int TB_OFF = 128;
-constexpr int TB_SIZE = TB_OFF + 320;                  // t < 255 * kSatMax
-constexpr float kSatMax = 1.25f;
-
-struct Geom {
-    int H, W, C, rows_cta;
-    int upr, upr_shift;                 // units per row (log2 when a power of two, else -1)
-    uint32_t cov_pitch, cov_rows;       // coverage canvas: words per row, rows
-    uint32_t canvas_pitch;              // colour canvas (global): words per row
-    size_t canvas_stride, o_canvas, ws_total;   // words per image; workspace offsets / size in bytes
-    uint32_t o_rowpre, o_cov, o_flags, o_lut, total;
-};
+// binade below 2^23 (half steps): offsets down to -2 * 255 (kSatMax - 1); t < 255 * kSatMax above.  Valid for Saturation
+// factors <= kSatMax = 2: the whole range of torchvision's ColorJitter(saturation <= 1).
+constexpr int TB_OFF = 512;
+constexpr int TB_SIZE = TB_OFF + 512;                  // t < 255 * kSatMax
+constexpr float kSatMax = 2.0f;
 
 // one stage program: bytes -> bytes
 enum { PK_COPY = 0, PK_BYTELUT = 1, PK_SAT = 2 };
@@ -104,46 +95,8 @@ __device__ inline void build_prog(Prog& G, Tables& T, const int32_t* ops, const 
 }
 
 // ------------------------------------------------------------------ small helpers
-__device__ __forceinline__ void st_cluster_u32(const void* local_ptr, uint32_t rank, uint32_t v) {
-    uint32_t remote;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(rank));
-    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(remote), "r"(v) : "memory");
-}
-
-__device__ __forceinline__ f32x2 fma2_rn(f32x2 a, f32x2 b, f32x2 c) {
-    f32x2 r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-    return r;
-}
-
-// 24 bytes at p (any alignment) -> 6 words.  nc = read-only path (source images); plain loads for the x buffer.
-template <bool NC>
-__device__ __forceinline__ uint2 ld8(const uint2* q) {
-    if (NC) return __ldg(q);
-    return *q;
-}
-template <bool NC>
-__device__ __forceinline__ void load24(const uint8_t* __restrict__ p, uint32_t (&w)[6]) {
-    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
-    const uint32_t mis = (uint32_t)(a & 7u);
-    const uint2* q = reinterpret_cast<const uint2*>(a - mis);
-    if (mis == 0) {
-        const uint2 A = ld8<NC>(q), B = ld8<NC>(q + 1), C = ld8<NC>(q + 2);
-        w[0] = A.x; w[1] = A.y; w[2] = B.x; w[3] = B.y; w[4] = C.x; w[5] = C.y;
-    } else {
-        const uint2 A = ld8<NC>(q), B = ld8<NC>(q + 1), C = ld8<NC>(q + 2), D = ld8<NC>(q + 3);
-        const uint32_t sh = (mis & 3u) * 8u;
-        if (mis < 4) {
-            w[0] = __funnelshift_r(A.x, A.y, sh); w[1] = __funnelshift_r(A.y, B.x, sh); w[2] = __funnelshift_r(B.x, B.y, sh);
-            w[3] = __funnelshift_r(B.y, C.x, sh); w[4] = __funnelshift_r(C.x, C.y, sh); w[5] = __funnelshift_r(C.y, D.x, sh);
-        } else {
-            w[0] = __funnelshift_r(A.y, B.x, sh); w[1] = __funnelshift_r(B.x, B.y, sh); w[2] = __funnelshift_r(B.y, C.x, sh);
-            w[3] = __funnelshift_r(C.x, C.y, sh); w[4] = __funnelshift_r(C.y, D.x, sh); w[5] = __funnelshift_r(D.x, D.y, sh);
-        }
-    }
-}
-
-// the same load split in two for software pipelining: raw 8-byte-aligned loads now, the byte shift later
+// 24 bytes at any alignment -> 6 words, split in two for software pipelining: raw 8-byte-aligned loads now, the byte
+// shift later
 struct Raw { uint2 a, b, c, d; };
 __device__ __forceinline__ void ld_raw(const uint8_t* q /* 8-byte aligned */, bool four, bool nc, Raw& r) {
     const uint2* p = reinterpret_cast<const uint2*>(q);
@@ -198,58 +151,6 @@ __device__ __forceinline__ uint32_t dp2a_hi(uint32_t a16x2, uint32_t b8x4, uint3
     asm("dp2a.hi.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a16x2), "r"(b8x4), "r"(c));
     return d;
 }
-__device__ __forceinline__ void luma_words(const uint32_t (&w)[6], uint32_t (&L)[8]) {
-    constexpr uint32_t kRG = (38470u << 16) | 19595u, kB0 = 7471u;          // pixel at bytes 0,1,2 of a word
-    constexpr uint32_t k0R = (19595u << 16), kGB = (7471u << 16) | 38470u;  // pixel at bytes 1,2,3 of a word
-    #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-        const uint32_t w0 = w[3 * q], w1 = w[3 * q + 1], w2 = w[3 * q + 2];
-        const uint32_t p1 = __byte_perm(w0, w1, 0x0543);     // pixel 1: byte 3 of w0, bytes 0,1 of w1
-        const uint32_t p2 = __byte_perm(w1, w2, 0x0432);     // pixel 2: bytes 2,3 of w1, byte 0 of w2
-        L[4 * q + 0] = dp2a_hi(kB0, w0, dp2a_lo(kRG, w0, 0x8000u)) >> 16;
-        L[4 * q + 1] = dp2a_hi(kB0, p1, dp2a_lo(kRG, p1, 0x8000u)) >> 16;
-        L[4 * q + 2] = dp2a_hi(kB0, p2, dp2a_lo(kRG, p2, 0x8000u)) >> 16;
-        L[4 * q + 3] = dp2a_hi(kGB, w2, dp2a_lo(k0R, w2, 0x8000u)) >> 16;
-    }
-}
-__device__ __forceinline__ uint32_t luma_sum_words(const uint32_t (&w)[6]) {
-    uint32_t L[8];
-    luma_words(w, L);
-    return ((L[0] + L[1]) + (L[2] + L[3])) + ((L[4] + L[5]) + (L[6] + L[7]));
-}
-// ... leaving out the pixels whose bit is set in `skip`
-__device__ __forceinline__ uint32_t luma_sum_words_skip(const uint32_t (&w)[6], uint32_t skip) {
-    uint32_t L[8];
-    luma_words(w, L);
-    uint32_t s = 0;
-    #pragma unroll
-    for (int p = 0; p < 8; ++p) s += ((skip >> p) & 1u) ? 0u : L[p];
-    return s;
-}
-
-// sum NV values over the CTA; result valid in every thread
-template <int NV>
-__device__ __forceinline__ void block_sum_vec(uint32_t (&v)[NV], uint32_t* red /* NWARP * 8 + 8 words */) {
-    #pragma unroll
-    for (int i = 0; i < NV; ++i)
-        for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xFFFFFFFFu, v[i], o);
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) {
-        #pragma unroll
-        for (int i = 0; i < NV; ++i) red[(threadIdx.x >> 5) * 8 + i] = v[i];
-    }
-    __syncthreads();
-    if (threadIdx.x < NV) {
-        uint32_t t = 0;
-        #pragma unroll
-        for (int w = 0; w < NWARP; ++w) t += red[w * 8 + threadIdx.x];
-        red[NWARP * 8 + threadIdx.x] = t;
-    }
-    __syncthreads();
-    #pragma unroll
-    for (int i = 0; i < NV; ++i) v[i] = red[NWARP * 8 + i];
-}
-
 // ------------------------------------------------------------------ donor / cut source, patch colours
 // donor / cut source of image b (datasets.py:225-228, 253): patch pixel (u, v) = donor window pixel (rl + u, rt + v)
 struct Donor {
@@ -280,31 +181,6 @@ struct Colour {
     uint32_t frgb[3];
     float bf1, bf2;
 };
-__device__ __forceinline__ void patch_colour(const Colour& K, const Donor& dn, int u, int v, uint32_t& r, uint32_t& g, uint32_t& bl) {
-    if (K.flat) { r = K.frgb[0]; g = K.frgb[1]; bl = K.frgb[2]; return; }
-    r = g = bl = 0;
-    if (u < dn.u_hi && v < dn.v_hi) {
-        const uint8_t* q = dn.base + (size_t)v * dn.pitch + 3 * u;
-        r = __ldg(q); g = __ldg(q + 1); bl = __ldg(q + 2);
-    }
-    if (K.sim) {        // two successive ImageEnhance.Brightness, each re-quantised (datasets.py:298-299)
-        r = brightness_u8(brightness_u8(r, K.bf1), K.bf2);
-        g = brightness_u8(brightness_u8(g, K.bf1), K.bf2);
-        bl = brightness_u8(brightness_u8(bl, K.bf1), K.bf2);
-    }
-}
-
-// ------------------------------------------------------------------ paste on the fly
-// 8 coverage bits of canvas row `crow` starting at canvas x = u0 (u0 may be negative or run past bw: those bits are 0)
-__device__ __forceinline__ uint32_t cov_bits8(const uint32_t* __restrict__ crow, int u0, int pitch_words) {
-    const int lo = max(u0, 0);
-    const int wi = lo >> 5;
-    uint32_t a = crow[wi];
-    uint32_t b = (wi + 1 < pitch_words) ? crow[wi + 1] : 0u;
-    uint32_t bits = __funnelshift_r(a, b, lo & 31) & 0xFFu;          // bits for canvas x = lo .. lo + 7
-    return (u0 < 0) ? (bits << (-u0)) & 0xFFu : bits;                 // pixel PIX <-> canvas x = u0 + PIX
-}
-
 // ------------------------------------------------------------------ stages on 8-pixel units
 __device__ __forceinline__ uint32_t min_relu_s16x2(uint32_t a, uint32_t b) {
     uint32_t d;
@@ -342,7 +218,7 @@ __device__ __forceinline__ void stage_in(Unit8& u, const uint32_t (&w)[6], uint3
 
 // ImageEnhance.Color on a unit, result left unclipped as RZ(2^23 + t)
 __device__ __forceinline__ void unit_saturation_raw(Unit8& u, float f) {
-    const f32x2 F = pack2(f, f), MAG = pack2(kMagic, kMagic);
+    const f32x2 MAG = pack2(kMagic, kMagic);
     #pragma unroll
     for (int k = 0; k < 4; ++k) {
         float r0, r1, g0, g1, b0, b1;
@@ -355,7 +231,12 @@ __device__ __forceinline__ void unit_saturation_raw(Unit8& u, float f) {
         const f32x2 NLF = add2_rn(NML, MAG);                // -(float)L, exact
         #pragma unroll
         for (int ch = 0; ch < 3; ++ch) {
-            const f32x2 p = mul2_rn(F, add2_rn(u.v[ch][k], NML));     // alpha * (v - L)
+            // alpha * (v - L), rounded on its own as Blend.c rounds it: two scalar mul.rn -- ptxas contracts a packed
+            // mul.rn.f32x2 followed by a packed add / sub into one FFMA2 (a single rounding), which differs from Pillow
+            // whenever alpha (v - L) lies within an ulp of an integer
+            float d0, d1;
+            unpack2(add2_rn(u.v[ch][k], NML), d0, d1);
+            const f32x2 p = pack2(__fmul_rn(f, d0), __fmul_rn(f, d1));
             f32x2 t;
             asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(p), "l"(NLF));   // L + p (same rounding as Pillow's A + p)
             u.v[ch][k] = add2_rz(t, MAG);
@@ -451,50 +332,6 @@ __device__ __forceinline__ void apply_prog(uint32_t (&w)[6], const ProgRegs& R) 
     if (LK == LK_SAT_LL) unit_sat_prog<SA_LUT, SB_LUT>(w, R.fs, R.ta, R.tbc);
 }
 
-struct Boxes {                 // paste geometry of one image, in registers inside the unit loops
-    const uint32_t* cov;       // coverage bit rows of the canvas (shared memory)
-    const uint32_t* canvas;    // packed (r, g, b, L) per canvas pixel (global, written by this CTA)
-    int pitch, cpitch, bw, bh, npaste;
-};
-
-// union of the coverage of all pastes over the 8 pixels of a unit (pass 1: those pixels are replaced later)
-__device__ __forceinline__ uint32_t covered_bits8(const Plan& D, const Boxes& B, uint32_t rowflag, int yy, int x0) {
-    uint32_t m = 0;
-    for (int k = 0; k < B.npaste; ++k) {
-        if (!((rowflag >> k) & 1u)) continue;
-        const int u0 = x0 - D.paste[k][0], v = yy - D.paste[k][1];
-        if (u0 + 8 <= 0 || u0 >= B.bw) continue;
-        m |= cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
-    }
-    return m;
-}
-
-// replace pixel PIX of the unit by the (r, g, b) bytes of a packed canvas word
-template <int PIX>
-__device__ __forceinline__ void put_pixel_c(uint32_t (&w)[6], uint32_t c) {
-    constexpr int b0 = 3 * PIX, b1 = b0 + 1, b2 = b0 + 2;
-    constexpr uint32_t keep = 0x3210u;
-    w[b0 >> 2] = __byte_perm(w[b0 >> 2], c, (keep & ~(0xFu << (4 * (b0 & 3)))) | (4u << (4 * (b0 & 3))));
-    w[b1 >> 2] = __byte_perm(w[b1 >> 2], c, (keep & ~(0xFu << (4 * (b1 & 3)))) | (5u << (4 * (b1 & 3))));
-    w[b2 >> 2] = __byte_perm(w[b2 >> 2], c, (keep & ~(0xFu << (4 * (b2 & 3)))) | (6u << (4 * (b2 & 3))));
-}
-
-// paste_patch / scar pastes (dataset_generator.py:268-275, datasets.py:340-355) applied to the 8 pixels of a unit:
-// covered pixels take the canvas colour; pastes in order, later ones overwrite earlier ones
-__device__ __forceinline__ void paste_unit(const Plan& D, const Boxes& B, uint32_t rowflag, int yy, int x0, uint32_t (&w)[6]) {
-    for (int k = 0; k < B.npaste; ++k) {
-        if (!((rowflag >> k) & 1u)) continue;
-        const int u0 = x0 - D.paste[k][0], v = yy - D.paste[k][1];
-        if (u0 + 8 <= 0 || u0 >= B.bw) continue;
-        const uint32_t bits = cov_bits8(B.cov + (size_t)v * B.pitch, u0, B.pitch);
-        if (!bits) continue;
-        const uint32_t* crow = B.canvas + (ptrdiff_t)v * B.cpitch + u0;
-        #define SSAD_PASTE(PIX) if (bits & (1u << PIX)) put_pixel_c<PIX>(w, crow[PIX]);
-        SSAD_PASTE(0) SSAD_PASTE(1) SSAD_PASTE(2) SSAD_PASTE(3) SSAD_PASTE(4) SSAD_PASTE(5) SSAD_PASTE(6) SSAD_PASTE(7)
-        #undef SSAD_PASTE
-    }
-}
-
 // u in [0, n) with 0 <= base + u * step < limit (int64: no wrap) -> [lo, hi] inclusive (empty: lo > hi)
 __device__ __forceinline__ long long floor_div(long long a, long long b) {     // b > 0
     long long q = a / b;
@@ -546,95 +383,6 @@ __device__ __forceinline__ Slab make_slab(int r0, int nunits, int upr, int tid) 
     if (nlin_ < (S).nunits) ld_raw(in0a_ + nrr_ * (in_pitch) + ncu_ * 24, mis_ != 0, in_nc, nx_);             \
     uint32_t w[6];                                                                                            \
     raw_to_words(cur_, mis_, w);
-
-// pass 1: RGB sums of x; the program ahead of Contrast; sum of L over the pixels no paste replaces; keep the bytes
-template <int LK>
-__device__ __forceinline__ void pass1_loop(const Slab& S, const uint8_t* in, int in_pitch, bool in_nc, uint8_t* xb, int xpitch,
-                                           bool store, bool need_rgb, bool need_luma, const ProgRegs& R, const Plan& D,
-                                           const Boxes& BX, const uint8_t* flags, uint32_t (&acc)[7]) {
-    uint32_t s0 = 0, s1 = 0, s2 = 0, sl = 0;
-    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
-    uint8_t* const xb0 = xb + (size_t)S.r0 * xpitch;           // dense rows: unit `lin` of the slab sits at lin * 24
-    SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc) {
-        SSAD_PIPELINED_STEP(S, in_pitch, in_nc)
-        if (need_rgb) {
-            uint32_t s[3] = {s0, s1, s2};
-            rgb_sums(w, s);
-            s0 = s[0]; s1 = s[1]; s2 = s[2];
-        }
-        if (need_luma) {
-            apply_prog<LK>(w, R);
-            // sum of L of what Contrast will see, minus the pixels a paste replaces (their L comes from the canvas)
-            const uint32_t rf = D.y != 0 ? (uint32_t)flags[rr] : 0u;
-            const uint32_t skip = rf ? covered_bits8(D, BX, rf, yy, x0) : 0u;
-            sl += skip ? luma_sum_words_skip(w, skip) : luma_sum_words(w);
-            if (store) {                        // the x buffer keeps pre(x): pass 2 starts from there
-                uint2* const o = reinterpret_cast<uint2*>(xb0 + lin * 24);
-                o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
-            }
-        }
-    }
-    acc[0] += s0; acc[1] += s1; acc[2] += s2; acc[3] += sl;
-}
-
-// pass 2: paste on the fly, the rest of the chain, stores
-template <int LK>
-__device__ __forceinline__ void pass2_loop(const Slab& S, const uint8_t* in, int in_pitch, bool in_nc, const ProgRegs& R,
-                                           const Plan& D, const Boxes& BX, const uint8_t* flags, int W, int npix,
-                                           uint8_t* obase, void* onorm, int norm_dtype, const uint8_t* lutbase) {
-    const uint8_t* const in0 = in + (size_t)S.r0 * in_pitch;
-    const size_t pbase = (size_t)S.r0 * W;                     // dense outputs: unit `lin` starts at pixel pbase + lin * 8
-    SSAD_PIPELINED_LOOP(S, in0, in_pitch, in_nc) {
-        SSAD_PIPELINED_STEP(S, in_pitch, in_nc)
-        if (D.y != 0) {
-            const uint32_t rf = flags[rr];
-            if (rf) paste_unit(D, BX, rf, yy, x0, w);
-        }
-        apply_prog<LK>(w, R);
-        const size_t p0 = pbase + (size_t)lin * 8;
-        if (obase) {
-            uint2* o = reinterpret_cast<uint2*>(obase + p0 * 3);
-            o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
-        }
-        if (onorm) {
-            // ToTensor + Normalize (datasets.py:392-393): exact table per channel, NCHW planes
-            uint32_t e[24];
-            #pragma unroll
-            for (int i = 0; i < 24; ++i) e[i] = (w[i >> 2] >> (8 * (i & 3))) & 0xFFu;      // byte i = pixel i / 3, channel i % 3
-            if (norm_dtype == SSAD_NORM_F32) {
-                const float* lut = reinterpret_cast<const float*>(lutbase);
-                float* ob = reinterpret_cast<float*>(onorm);
-                #pragma unroll
-                for (int ch = 0; ch < 3; ++ch) {
-                    float4* o = reinterpret_cast<float4*>(ob + (size_t)ch * npix + p0);
-                    #pragma unroll
-                    for (int qq = 0; qq < 2; ++qq) {
-                        float4 v;
-                        v.x = lut[ch * 256 + e[3 * (4 * qq + 0) + ch]];
-                        v.y = lut[ch * 256 + e[3 * (4 * qq + 1) + ch]];
-                        v.z = lut[ch * 256 + e[3 * (4 * qq + 2) + ch]];
-                        v.w = lut[ch * 256 + e[3 * (4 * qq + 3) + ch]];
-                        o[qq] = v;
-                    }
-                }
-            } else {
-                const uint16_t* lut = reinterpret_cast<const uint16_t*>(lutbase);
-                uint16_t* ob = reinterpret_cast<uint16_t*>(onorm);
-                #pragma unroll
-                for (int ch = 0; ch < 3; ++ch) {
-                    uint32_t wv[4];
-                    #pragma unroll
-                    for (int qq = 0; qq < 4; ++qq) {
-                        uint32_t lo = lut[ch * 256 + e[3 * (2 * qq) + ch]];
-                        uint32_t hi = lut[ch * 256 + e[3 * (2 * qq + 1) + ch]];
-                        wv[qq] = lo | (hi << 16);
-                    }
-                    *reinterpret_cast<uint4*>(ob + (size_t)ch * npix + p0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
-                }
-            }
-        }
-    }
-}
 
 }  // namespace v6
 }  // namespace ssad

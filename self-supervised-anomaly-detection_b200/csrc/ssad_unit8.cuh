@@ -1,9 +1,9 @@
 // 8-pixel register unit of the jitter chain + the similarity decision, shared by the generator kernels.
 //
 // A unit is 8 consecutive pixels of one row (24 bytes = 6 words) held as 12 packed f32x2 values in "magic" form
-// (2^23 + v): ColorJitter's Brightness / Contrast / Saturation (torchvision _functional_pil.py:71-97 ->
-// ImageEnhance -> Blend.c) run as FADD2 / FMUL2 / FADD2.RZ with every product and sum rounded on its own, which is
-// bit-identical to Pillow's float32 code; RGB -> L is Convert.c's integer formula.
+// (2^23 + v).  ColorJitter's Saturation (torchvision _functional_pil.py:71-97 -> ImageEnhance.Color -> Blend.c) runs on
+// them in ssad_pipeline_common.cuh with every product and sum rounded on its own (bit-identical to Pillow's float32
+// code); Brightness / Contrast are 256-entry tables; RGB -> L is Convert.c's integer formula.
 #pragma once
 #include "ssad_device.cuh"
 #include "ssad_sm100.cuh"
@@ -46,87 +46,9 @@ __device__ __forceinline__ void unit_pack(const Unit8& u, uint2& a, uint2& b, ui
     c = make_uint2(w[4], w[5]);
 }
 
-template <bool CLAMP>
-__device__ __forceinline__ f32x2 quantize2(f32x2 t) {
-    if (CLAMP) {
-        float lo, hi;
-        unpack2(t, lo, hi);
-        t = pack2(fminf(fmaxf(lo, 0.0f), 255.0f), fminf(fmaxf(hi, 0.0f), 255.0f));
-    }
-    return add2_rz(t, pack2(kMagic, kMagic));
-}
-template <bool CLAMP>
-__device__ __forceinline__ void unit_brightness(Unit8& u, float f) {
-    const f32x2 F = pack2(f, f), NEG = pack2(-kMagic, -kMagic), MAG = pack2(kMagic, kMagic);
-    #pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-        #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            f32x2 t = mul2_rn(F, add2_rn(u.v[ch][k], NEG));
-            if (CLAMP) {                                   // values >= 0: only the upper clip can bind
-                float lo, hi;
-                unpack2(t, lo, hi);
-                t = pack2(fminf(lo, 255.0f), fminf(hi, 255.0f));
-            }
-            u.v[ch][k] = add2_rz(t, MAG);
-        }
-    }
-}
-template <bool CLAMP>
-__device__ __forceinline__ void unit_contrast(Unit8& u, float f, int mean) {
-    const float nm = -(kMagic + (float)mean), af = (float)mean;
-    const f32x2 F = pack2(f, f), NMA = pack2(nm, nm), AF = pack2(af, af);
-    #pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-        #pragma unroll
-        for (int k = 0; k < 4; ++k)
-            u.v[ch][k] = quantize2<CLAMP>(add2_rn(AF, mul2_rn(F, add2_rn(u.v[ch][k], NMA))));
-    }
-}
 __device__ __forceinline__ uint32_t luma_bits(uint32_t r, uint32_t g, uint32_t b) {
     return 19595u * r + 38470u * g + 7471u * b + 0x8000u;     // on magic bit patterns: the 0x4B000000 offsets cancel mod 2^32
 }
-template <bool CLAMP>
-__device__ __forceinline__ void unit_saturation(Unit8& u, float f) {
-    const f32x2 F = pack2(f, f), MAG = pack2(kMagic, kMagic);
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        float r0, r1, g0, g1, b0, b1;
-        unpack2(u.v[0][k], r0, r1); unpack2(u.v[1][k], g0, g1); unpack2(u.v[2][k], b0, b1);
-        const uint32_t a0 = luma_bits(__float_as_uint(r0), __float_as_uint(g0), __float_as_uint(b0));
-        const uint32_t a1 = luma_bits(__float_as_uint(r1), __float_as_uint(g1), __float_as_uint(b1));
-        // -(2^23 + L): bit pattern 0xCB0000LL
-        const f32x2 NML = pack2(__uint_as_float(__byte_perm(a0, 0xCB000000u, 0x7542)),
-                                __uint_as_float(__byte_perm(a1, 0xCB000000u, 0x7542)));
-        const f32x2 NLF = add2_rn(NML, MAG);                // -(float)L, exact
-        #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            f32x2 p = mul2_rn(F, add2_rn(u.v[ch][k], NML)); // alpha * (v - L)
-            f32x2 t;
-            asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(p), "l"(NLF));   // L + p (same rounding as Pillow's A + p)
-            u.v[ch][k] = quantize2<CLAMP>(t);
-        }
-    }
-}
-__device__ __forceinline__ uint32_t unit_luma_sum(const Unit8& u) {
-    uint32_t s = 0;
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        float r0, r1, g0, g1, b0, b1;
-        unpack2(u.v[0][k], r0, r1); unpack2(u.v[1][k], g0, g1); unpack2(u.v[2][k], b0, b1);
-        s += luma_bits(__float_as_uint(r0), __float_as_uint(g0), __float_as_uint(b0)) >> 16;
-        s += luma_bits(__float_as_uint(r1), __float_as_uint(g1), __float_as_uint(b1)) >> 16;
-    }
-    return s;
-}
-__device__ __forceinline__ void unit_apply(Unit8& u, int op, float f) {
-    if (op == 0) {
-        if (f > 1.0f) unit_brightness<true>(u, f); else unit_brightness<false>(u, f);
-    } else {
-        if (blend_needs_clip(f)) unit_saturation<true>(u, f); else unit_saturation<false>(u, f);
-    }
-}
-
 // check_color_similarity(...) > 0.99 from exact integer channel sums (dataset_generator.py:147-159): the cheap
 // cosine <s1,s2>/sqrt(<s1,s1><s2,s2>) decides unless it is within 1e-9 of the threshold; then the reference's own
 // operation order (mean / 255, normalise, dot) is evaluated.

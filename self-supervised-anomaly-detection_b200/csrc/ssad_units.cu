@@ -142,10 +142,43 @@ paste_kernel(uint8_t* __restrict__ img, int W, int H, const uint8_t* __restrict_
     const int X = left + u, Y = top + v;
     if (X < 0 || Y < 0 || X >= W || Y >= H) return;            // the box is clipped to the image
     const uint32_t a = mask ? mask[i] : (ch == 4 ? patch[(size_t)i * 4 + 3] : 255u);
-    if (a == 0) return;                                        // on this path alpha is 0 or 255
+    if (a == 0) return;
     uint8_t* q = img + 3 * ((size_t)Y * W + X);
     const uint8_t* s = patch + (size_t)i * ch;
-    q[0] = s[0]; q[1] = s[1]; q[2] = s[2];
+    if (a == 255) { q[0] = s[0]; q[1] = s[1]; q[2] = s[2]; return; }      // (on the dataset's path alpha is 0 or 255)
+    // Paste.c BLEND8 for a soft mask: DIV255(out * (255 - a) + in * a), DIV255(t) = ((t + 128) >> 8) + (t + 128) >> 8
+    #pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t t = (uint32_t)q[c] * (255u - a) + (uint32_t)s[c] * a + 128u;
+        q[c] = (uint8_t)(((t >> 8) + t) >> 8);
+    }
+}
+
+// ---- check_color_similarity (dataset_generator.py:147-159): cosine of the mean colours of two images
+__global__ void __launch_bounds__(256)
+color_similarity_kernel(const uint8_t* __restrict__ a, int na, const uint8_t* __restrict__ b, int nb, double* __restrict__ out) {
+    __shared__ unsigned long long acc[6];
+    const int tid = threadIdx.x;
+    if (tid < 6) acc[tid] = 0ull;
+    __syncthreads();
+    unsigned long long s[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = tid; i < na; i += 256) { s[0] += a[3 * (size_t)i]; s[1] += a[3 * (size_t)i + 1]; s[2] += a[3 * (size_t)i + 2]; }
+    for (int i = tid; i < nb; i += 256) { s[3] += b[3 * (size_t)i]; s[4] += b[3 * (size_t)i + 1]; s[5] += b[3 * (size_t)i + 2]; }
+    #pragma unroll
+    for (int k = 0; k < 6; ++k) atomicAdd(&acc[k], s[k]);
+    __syncthreads();
+    if (tid == 0) {
+        // np.mean(axis=(0,1)) / 255 per channel, then sklearn cosine_similarity: float64 throughout
+        double u[3], v[3];
+        for (int k = 0; k < 3; ++k) { u[k] = ((double)acc[k] / (double)na) / 255.0; v[k] = ((double)acc[3 + k] / (double)nb) / 255.0; }
+        const double nu = sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]), nv = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        double c = 0.0;
+        if (nu > 0.0 && nv > 0.0) {
+            const double un[3] = {u[0] / nu, u[1] / nu, u[2] / nu}, vn[3] = {v[0] / nv, v[1] / nv, v[2] / nv};
+            c = un[0] * vn[0] + un[1] * vn[1] + un[2] * vn[2];
+        }
+        out[0] = c;
+    }
 }
 }  // namespace ssad
 
@@ -211,6 +244,14 @@ extern "C" int ssad_paste(uint8_t* image, int32_t width, int32_t height, const u
     const int n = pw * ph;
     ssad::paste_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(image, width, height, patch, pw, ph, channels,
                                                                                    mask, left, top);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_color_similarity(const uint8_t* image, int32_t n_image, const uint8_t* patch, int32_t n_patch, double* out,
+                                     void* stream) {
+    if (!image || !patch || !out || n_image <= 0 || n_patch <= 0) return SSAD_EINVAL;
+    ssad::color_similarity_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(image, n_image, patch, n_patch, out);
     SSAD_CHECK_LAUNCH();
     return SSAD_OK;
 }

@@ -121,13 +121,36 @@ def obj_mask(image, device=None):
     return m
 
 
+# ---------------------------------------------------------------------- check_color_similarity
+def check_color_similarity(patch, defect, device=None) -> float:
+    """dataset_generator.py:147-159 on the device: cosine similarity of the mean colours of two images (PIL or uint8
+    [H, W, 3] arrays of any sizes), float64.  The dataset path takes the same decision inside ``ssad_generate``
+    (``cosine > 0.99`` -> the patch is brightened twice, datasets.py:295-299)."""
+    import ctypes as C
+    from . import _native as N
+    a, _ = _to_u8_hwc(patch)
+    b, _ = _to_u8_hwc(defect)
+    dev = _device(device)
+    lib = N.load()
+    with torch.cuda.device(dev):
+        ta, tb = torch.from_numpy(np.ascontiguousarray(a)).to(dev), torch.from_numpy(np.ascontiguousarray(b)).to(dev)
+        out = torch.zeros((1,), dtype=torch.float64, device=dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        N.check(lib.ssad_color_similarity(C.c_void_p(ta.data_ptr()), a.shape[0] * a.shape[1], C.c_void_p(tb.data_ptr()),
+                                          b.shape[0] * b.shape[1], C.c_void_p(out.data_ptr()), C.c_void_p(stream)),
+                "ssad_color_similarity")
+        return float(out.item())
+
+
 # ---------------------------------------------------------------------- generate_patch / rect2poly / paste_patch
 def generate_patch(image, area_ratio: Tuple[float, float] = (0.02, 0.15),
                    aspect_ratio: Tuple[Tuple[float, float], Tuple[float, float]] = ((0.3, 1), (1, 3.3)),
-                   colorized: bool = False, color_type: str = "random", rng: Optional[np.random.Generator] = None):
+                   augs=None, colorized: bool = False, color_type: str = "random",
+                   rng: Optional[np.random.Generator] = None):
     """dataset_generator.py:164-210: rectangle of ``area_ratio`` / ``aspect_ratio`` at a uniform position; its content
     is the crop (colorized=False), the crop's ``int(mean)`` colour ('average') or a random colour ('random').
-    Host-side: this is parameter sampling plus a crop of at most a few thousand pixels (reference: 0.02 ms)."""
+    Host-side: this is parameter sampling plus a crop of at most a few thousand pixels (reference: 0.02 ms).
+    ``augs`` keeps the reference's positional slot; the reference never uses it."""
     a, is_pil = _to_u8_hwc(image)
     rng = np.random.default_rng() if rng is None else rng
     H, W = a.shape[:2]
@@ -211,19 +234,20 @@ def paste_patch(image, patch, coords: tuple, mask=None, device=None):
             m = m[..., 3] if m.shape[2] == 4 else m[..., 0]
         if m.shape != p.shape[:2]:
             raise ValueError("images do not match")            # Pillow's own message
-        m = np.ascontiguousarray(m.astype(np.uint8))
+        m = np.ascontiguousarray(m.astype(np.uint8) * 255 if m.dtype == bool else m.astype(np.uint8))   # mode '1': set = opaque
     elif p.shape[2] == 4:
         p = p[..., :3]                                           # paste without a mask ignores the source alpha
     dev = _device(device)
     lib = N.load()
-    d_img = torch.from_numpy(a.copy()).to(dev)
-    d_patch = torch.from_numpy(np.ascontiguousarray(p)).to(dev)
-    d_mask = torch.from_numpy(m).to(dev) if m is not None else None
-    stream = torch.cuda.current_stream(dev).cuda_stream
-    N.check(lib.ssad_paste(C.c_void_p(d_img.data_ptr()), a.shape[1], a.shape[0], C.c_void_p(d_patch.data_ptr()),
-                           p.shape[1], p.shape[0], p.shape[2], C.c_void_p(d_mask.data_ptr()) if d_mask is not None else None,
-                           int(coords[0]), int(coords[1]), C.c_void_p(stream)), "ssad_paste")
-    return _from_u8_hwc(d_img.cpu().numpy(), is_pil)
+    with torch.cuda.device(dev):
+        d_img = torch.from_numpy(a.copy()).to(dev)
+        d_patch = torch.from_numpy(np.ascontiguousarray(p)).to(dev)
+        d_mask = torch.from_numpy(m).to(dev) if m is not None else None
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        N.check(lib.ssad_paste(C.c_void_p(d_img.data_ptr()), a.shape[1], a.shape[0], C.c_void_p(d_patch.data_ptr()),
+                               p.shape[1], p.shape[0], p.shape[2], C.c_void_p(d_mask.data_ptr()) if d_mask is not None else None,
+                               int(coords[0]), int(coords[1]), C.c_void_p(stream)), "ssad_paste")
+        return _from_u8_hwc(d_img.cpu().numpy(), is_pil)
 
 
 # ---------------------------------------------------------------------- do_patch / do_scar

@@ -111,10 +111,16 @@ class PretextTaskDataset:
             else:
                 f000 = os.path.join(dataset_dir, subject, "train/good/000.png")
                 first = torch.from_numpy(load_image(f000, self.imsize)[None]).to(self.device) if os.path.exists(f000) else self.images[:1]
-                # (cable: the reference averages SLIC super-pixels first, datasets.py:201-205 -- one-time host step,
-                #  out of scope: pass fixed_segmentation= for that class)
+                # cable: the reference averages SLIC super-pixels first (datasets.py:201-205, skimage.segmentation.slic
+                # -- a one-time host step outside the hot path, not built): without fixed_segmentation= the mask is the
+                # obj_mask of the raw image, which differs from the reference's -- say so instead of doing it silently
+                if subject == "cable":
+                    import warnings
+                    warnings.warn("cable: the reference builds its fixed mask from SLIC super-pixels (datasets.py:201-205); "
+                                  "pass fixed_segmentation= to reproduce it -- using obj_mask of the raw image 000", stacklevel=2)
                 mask = unpack_mask_bits(obj_mask_batch(first).cpu().numpy(), W)[0]
         self.fixed_segmentation = mask
+        self._src_masks = None
         self.gen = BatchGenerator(self.cfg, self.device, mask=mask, donors=donors if is_texture else None)
 
     def __len__(self) -> int:
@@ -123,20 +129,32 @@ class PretextTaskDataset:
     def sample(self, batch: int, labels: Optional[np.ndarray] = None) -> ParamBatch:
         return sample_params(self.cfg, batch, self.rng, labels=labels)
 
+    def source_masks(self) -> Optional[torch.Tensor]:
+        """Non-fixed classes: ``obj_mask(original)`` (datasets.py:232-233) of every resident image, built on first use.
+        The reference recomputes it on every ``__getitem__``; it depends on the un-warped original only, so one mask per
+        distinct file is the same result."""
+        if not self.cfg.is_non_fixed:
+            return None
+        if self._src_masks is None:
+            self._src_masks = obj_mask_batch(self.images)
+        return self._src_masks
+
     def get_batch(self, indices: Sequence[int], params: Optional[ParamBatch] = None):
-        """items ``indices`` -> (x [B,3,h,w], y [B] int64, original [B,3,H,W] f32 | None), all on the device."""
-        idx = torch.as_tensor(self.index[np.asarray(indices)], device=self.device)
-        src = self.images.index_select(0, idx)
+        """items ``indices`` -> (x [B,3,h,w], y [B] int64, original [B,3,H,W] f32 | None), all on the device.  The
+        resident images are never gathered: every record carries the row of its source image (``src_index``)."""
+        rows = self.index[np.asarray(indices)]
         if params is None:
-            params = self.sample(len(indices))
-        masks = obj_mask_batch(src) if self.cfg.is_non_fixed else None
+            params = self.sample(len(rows))
+        masks = self.source_masks()
         if self.transform:
-            out = self.gen.generate(src, params, masks=masks, want_u8=False, norm_dtype=self.out_dtype)
+            out = self.gen.generate(self.images, params, masks=masks, want_u8=False, norm_dtype=self.out_dtype, src_index=rows)
             x = out["x"]
         else:       # no transform in the reference = the PIL image; here the uint8 tensor [B,h,w,3]
-            out = self.gen.generate(src, params, masks=masks, want_u8=True)
+            out = self.gen.generate(self.images, params, masks=masks, want_u8=True, src_index=rows)
             x = out["x_u8"]
-        original = to_tensor(src) if self.return_original else None
+        original = None
+        if self.return_original:                    # ToTensor(original), datasets.py:394 (unused by training_step, models.py:257)
+            original = to_tensor(self.images.index_select(0, torch.as_tensor(rows, device=self.device)))
         return x, out["y"], original
 
     def __getitem__(self, index: int):
@@ -155,11 +173,28 @@ class BatchLoader:
         return n // self.batch_size if self.drop_last else (n + self.batch_size - 1) // self.batch_size
 
     def __iter__(self) -> Iterator:
+        """The parameter records of batch i+1 are drawn on a background thread while batch i is generated and consumed
+        (the sampler is the host-side limiter)."""
+        import threading
         n = len(self.dataset)
-        order = self.dataset.rng.permutation(n) if self.shuffle else np.arange(n)
-        for b in range(len(self)):
-            sel = order[b * self.batch_size:(b + 1) * self.batch_size]
-            yield self.dataset.get_batch(sel)
+        ds = self.dataset
+        order = ds.rng.permutation(n) if self.shuffle else np.arange(n)
+        sels = [order[b * self.batch_size:(b + 1) * self.batch_size] for b in range(len(self))]
+        box = {}
+
+        def draw(k):
+            box[k] = ds.sample(len(sels[k]))
+        th = None
+        if sels:
+            th = threading.Thread(target=draw, args=(0,), daemon=True)
+            th.start()
+        for k, sel in enumerate(sels):
+            th.join()
+            params = box.pop(k)
+            if k + 1 < len(sels):
+                th = threading.Thread(target=draw, args=(k + 1,), daemon=True)
+                th.start()
+            yield ds.get_batch(sel, params)
 
 
 class PretextTaskDatamodule:

@@ -90,16 +90,54 @@ class BatchGenerator:
         return self._luts[dtype]
 
     # ------------------------------------------------------------------
-    def upload_params(self, params: ParamBatch) -> torch.Tensor:
+    def validate_records(self, rec: np.ndarray, src_shape, n_src: Optional[int] = None) -> None:
+        """Host-side check of every record field the kernels index memory with (the library itself trusts the records):
+        raises ValueError instead of letting a bad record read out of bounds on the device."""
+        cfg = self.cfg
+        if rec.dtype != IMAGE_PARAMS_DTYPE:
+            raise ValueError("records have the wrong dtype")
+        if len(rec) == 0:
+            return
+        W, H = cfg.work_size
+        sh, sw = int(src_shape[0]), int(src_shape[1])
+        if np.any(rec["jit_f"] < 0) or np.any(rec["bright_f"] < 0):
+            raise ValueError("enhancement factors must be non-negative")
+        if int(rec["label"].max()) > 3:
+            raise ValueError("labels must be in {0, 1, 2, 3}")
+        if int(rec["poly_n"].max()) > 8:
+            raise ValueError("a polygon has at most 8 vertices")
+        nd = 0 if self.donors is None else int(self.donors.shape[0])
+        dmin, dmax = int(rec["donor_idx"].min()), int(rec["donor_idx"].max())
+        if dmin < -1 or (dmax >= 0 and dmax >= nd):
+            raise ValueError("donor_idx outside the donor bank")
+        co = rec["crop_off"].astype(np.int64)
+        if co.min() < 0 or (co[:, 0] + W).max() > sw or (co[:, 1] + H).max() > sh:
+            raise ValueError("crop window outside the source image")
+        do = rec["donor_off"].astype(np.int64)
+        dW, dH = cfg.donor_window
+        if do.min() < 0 or (do[:, 0] + dW).max() > sw or (do[:, 1] + dH).max() > sh:
+            raise ValueError("donor window outside the donor image")
+        r = rec["rect"].astype(np.int64)
+        if r[:, :2].min() < 0 or r[:, 2:].min() < 0:
+            raise ValueError("patch rectangle must be non-negative")
+        scar = rec["label"] == 2
+        if np.any(scar) and (int(rec["scar_k"][scar].min()) < 1 or int(rec["scar_k"][scar].max()) > 5):
+            raise ValueError("scar_k must be in 1..5")
+        if n_src is not None and int(rec["src_index"].max()) >= n_src:
+            raise ValueError("src_index outside the resident set")
+
+    def upload_params(self, params: ParamBatch, src_index=None) -> torch.Tensor:
         rec = np.ascontiguousarray(params.records)
         if rec.dtype != IMAGE_PARAMS_DTYPE:
             raise ValueError("records have the wrong dtype")
-        if np.any(rec["jit_f"] < 0) or np.any(rec["bright_f"] < 0):
-            raise ValueError("enhancement factors must be non-negative")
+        if src_index is not None:
+            rec = rec.copy()
+            rec["src_index"] = np.asarray(src_index, dtype=np.uint32)
         t = torch.from_numpy(rec.view(np.uint8).reshape(len(rec), IMAGE_PARAMS_DTYPE.itemsize))
         return t.to(self.device, non_blocking=True)
 
-    def describe(self, batch: int, src: torch.Tensor, max_pw: int, max_ph: int, masks, norm_dtype, crop_aligned=False) -> N.SsadBatchDesc:
+    def describe(self, batch: int, src: torch.Tensor, max_pw: int, max_ph: int, masks, norm_dtype, crop_aligned=False,
+                 indexed: bool = False) -> N.SsadBatchDesc:
         cfg = self.cfg
         W, H = cfg.work_size
         d = N.SsadBatchDesc()
@@ -130,25 +168,54 @@ class BatchGenerator:
         d.out_u8_pitch, d.out_u8_stride = 3 * W, 3 * W * H
         d.crop_align16 = int(crop_aligned)
         d.any_warp = int(cfg.warp)
+        d.src_indexed = int(indexed)
+        d.src_count = int(src.shape[0]) if indexed else 0
+        d.line_width = 1 if cfg.patch_localization else 3          # datasets.py:383-388
         return d
 
-    def plan(self, src: torch.Tensor, params: ParamBatch, *, masks=None, want_u8=True, norm_dtype=None, debug=False,
-             params_dev=None, out_u8=None, out_norm=None, y_out=None, workspace=None) -> "Plan":
-        """Validate once and freeze descriptor + device pointers of one ssad_generate call; ``run(plan)``
-        then costs one FFI call (steady-state loops, CUDA-graph capture)."""
-        cfg = self.cfg
-        B = int(src.shape[0])
-        W, H = cfg.work_size
-        rec = params.records
-        if params_dev is None:
-            params_dev = self.upload_params(params)
+    @staticmethod
+    def batch_hints(rec: np.ndarray):
+        """Batch-wide bounds the descriptor carries: (crop offsets 16-byte aligned, canvas width, canvas height, largest
+        enabled Saturation factor).  The polygon lives on pw x ph, the rotated scar on scar_size (datasets.py:344)."""
         crop_aligned = bool(np.all((rec["crop_off"][:, 0].astype(np.int64) * 3) % 16 == 0))
-        # canvas bounds: the polygon lives on pw x ph, the rotated scar on scar_size (datasets.py:344)
         max_w = max(int(rec["rect"][:, 2].max(initial=1)), int(rec["scar_size"][:, 0].max(initial=1)))
         max_h = max(int(rec["rect"][:, 3].max(initial=1)), int(rec["scar_size"][:, 1].max(initial=1)))
-        d = self.describe(B, src, max_w, max_h, masks, norm_dtype, crop_aligned)
         sat_on = (rec["jit_en"] & 4) != 0
-        d.sat_factor_max = float(rec["jit_f"][:, 2][sat_on].max(initial=0.0))
+        return crop_aligned, max_w, max_h, float(rec["jit_f"][:, 2][sat_on].max(initial=0.0))
+
+    def plan(self, src: torch.Tensor, params: ParamBatch, *, masks=None, want_u8=True, norm_dtype=None, debug=False,
+             params_dev=None, out_u8=None, out_norm=None, y_out=None, workspace=None, src_index=None,
+             context=None, validated: bool = False, hints=None) -> "Plan":
+        """Validate once and freeze descriptor + device pointers of one ssad_generate call; ``run(plan)``
+        then costs one FFI call (steady-state loops, CUDA-graph capture).  ``src_index``: item i works on
+        ``src[src_index[i]]`` (``src`` = the resident set, never gathered); per-image ``masks`` are then per source image.
+        ``context``: a handle from ``new_context()`` for a host thread that shares the device with other threads."""
+        cfg = self.cfg
+        B = len(params)
+        W, H = cfg.work_size
+        rec = params.records
+        indexed = src_index is not None
+        if not indexed and int(src.shape[0]) != B:
+            raise ValueError("params and src disagree on the batch size")
+        if indexed and len(src_index) != B:
+            raise ValueError("params and src_index disagree on the batch size")
+        if not validated:
+            self.validate_records(rec, src.shape[1:3])
+        if indexed and (int(np.min(src_index)) < 0 or int(np.max(src_index)) >= int(src.shape[0])):
+            raise ValueError("src_index outside the resident set")
+        if params_dev is None:
+            params_dev = self.upload_params(params, src_index)
+        if hints is None:
+            hints = self.batch_hints(rec)
+        crop_aligned, max_w, max_h, sat_max = hints
+        d = self.describe(B, src, max_w, max_h, masks, norm_dtype, crop_aligned, indexed)
+        line_xy = getattr(params, "line_xy", None)
+        line_dev = None
+        if line_xy is not None and int(rec["line_n"].max(initial=0)) > 0:
+            line_dev = torch.from_numpy(np.ascontiguousarray(line_xy, dtype=np.int16)).to(self.device)
+            d.line_max = int(line_xy.shape[1])
+            d.line_xy = line_dev.data_ptr()
+        d.sat_factor_max = sat_max
         if want_u8 and out_u8 is None:
             out_u8 = torch.empty((B, H, W, 3), dtype=torch.uint8, device=self.device)
         if norm_dtype is not None and out_norm is None:
@@ -162,6 +229,7 @@ class BatchGenerator:
         if workspace is None or workspace.numel() * workspace.element_size() < need:
             workspace = torch.empty((max(need, 256),), dtype=torch.uint8, device=self.device)
         pl = Plan()
+        pl.line_dev, pl.context = line_dev, context
         pl.workspace = workspace
         pl.desc, pl.params_dev, pl.src, pl.mask_t, pl.lut = d, params_dev, src, mask_t, lut
         pl.out_u8, pl.out_norm, pl.y_out, pl.dbg = (out_u8 if want_u8 else None), out_norm, y_out, dbg
@@ -170,13 +238,27 @@ class BatchGenerator:
                    workspace.numel() * workspace.element_size())
         return pl
 
+    def new_context(self):
+        """A library context (its own helper streams) for a host thread that drives this device next to other threads."""
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            N.check(self.lib.ssad_context_create(C.byref(h)), "ssad_context_create")
+        return h
+
+    def free_context(self, ctx) -> None:
+        self.lib.ssad_context_destroy(ctx)
+
+    def _call(self, plan: "Plan") -> None:
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            N.check(self.lib.ssad_generate_ctx(plan.context, *plan.args, C.c_void_p(stream)), "ssad_generate")
+
     def run(self, plan: "Plan") -> None:
         graph = getattr(plan, "graph", None)
         if graph is not None:
             graph.replay()
             return
-        stream = torch.cuda.current_stream(self.device).cuda_stream
-        N.check(self.lib.ssad_generate(*plan.args, C.c_void_p(stream)), "ssad_generate")
+        self._call(plan)
 
     def capture(self, plan: "Plan") -> "Plan":
         """Record the plan's ssad_generate call (a handful of kernels, forked over helper streams) into a CUDA graph:
@@ -187,16 +269,17 @@ class BatchGenerator:
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                stream = torch.cuda.current_stream(self.device).cuda_stream
-                N.check(self.lib.ssad_generate(*plan.args, C.c_void_p(stream)), "ssad_generate")
+                self._call(plan)
             plan.graph = g
         return plan
 
     def generate(self, src: torch.Tensor, params: ParamBatch, *, masks: Optional[torch.Tensor] = None,
                  want_u8: bool = True, norm_dtype: Optional[torch.dtype] = None, debug: bool = False,
                  params_dev: Optional[torch.Tensor] = None, out_u8: Optional[torch.Tensor] = None,
-                 out_norm: Optional[torch.Tensor] = None, y_out: Optional[torch.Tensor] = None):
-        """src: uint8 [B, Hs, Ws, 3] on the device (the decoded, resized originals).
+                 out_norm: Optional[torch.Tensor] = None, y_out: Optional[torch.Tensor] = None,
+                 src_index=None, context=None):
+        """src: uint8 [B, Hs, Ws, 3] on the device (the decoded, resized originals); with ``src_index`` the resident set
+        [N, Hs, Ws, 3] that item i indexes as ``src[src_index[i]]``.
         masks: int32/uint32-packed [B, Hs, ceil(Ws/32)] per-image mask bits (non-fixed classes).
         Returns dict(x_u8, x, y, debug) -- entries present per the want_* flags."""
         cfg = self.cfg
@@ -204,8 +287,8 @@ class BatchGenerator:
             raise ValueError("src must be a uint8 [B, H, W, 3] tensor on the generator's device")
         if src.stride(3) != 1 or src.stride(2) != 3:
             raise ValueError("src pixels must be interleaved RGB with unit channel stride")
-        B = int(src.shape[0])
-        if len(params) != B:
+        B = len(params)
+        if src_index is None and int(src.shape[0]) != B:
             raise ValueError("params and src disagree on the batch size")
         iW, iH = cfg.imsize
         if (int(src.shape[1]), int(src.shape[2])) != (iH, iW):
@@ -213,7 +296,8 @@ class BatchGenerator:
         if cfg.is_non_fixed and masks is None and self.mask_bits is None:
             raise ValueError("non-fixed classes need per-image masks (obj_mask, datasets.py:232-233)")
         plan = self.plan(src, params, masks=masks, want_u8=want_u8, norm_dtype=norm_dtype, debug=debug,
-                         params_dev=params_dev, out_u8=out_u8, out_norm=out_norm, y_out=y_out)
+                         params_dev=params_dev, out_u8=out_u8, out_norm=out_norm, y_out=y_out, src_index=src_index,
+                         context=context)
         self.run(plan)
         out_u8, out_norm, y_out, dbg = plan.out_u8, plan.out_norm, plan.y_out, plan.dbg
         out = {"y": y_out}
@@ -254,8 +338,8 @@ class BatchGenerator:
         rec = np.ascontiguousarray(params.records)
         if len(rec) != B or rec.dtype != IMAGE_PARAMS_DTYPE:
             raise ValueError("params and h_src disagree on the batch size (or the records have the wrong dtype)")
-        if np.any(rec["jit_f"] < 0) or np.any(rec["bright_f"] < 0):
-            raise ValueError("enhancement factors must be non-negative")
+        self.validate_records(rec, h_src.shape[1:3])
+        hints = self.batch_hints(rec)            # one set of bounds for every piece of the batch
         st["ev_rec"].synchronize()               # the previous call's upload has left the staging buffer
         st["h_rec"].numpy()[...] = rec.view(np.uint8).reshape(B, IMAGE_PARAMS_DTYPE.itemsize)
         with torch.cuda.stream(st["up"]):
@@ -272,7 +356,8 @@ class BatchGenerator:
                 if self.cfg.is_non_fixed and m is None and self.mask_bits is None:
                     raise ValueError("non-fixed classes need per-image masks (obj_mask, datasets.py:232-233)")
                 pl = self.plan(d_src, params.slice(lo, hi), masks=m, want_u8=True, norm_dtype=None,
-                               params_dev=st["d_rec"][lo:hi], out_u8=d_out, y_out=d_y, workspace=st["ws"][c])
+                               params_dev=st["d_rec"][lo:hi], out_u8=d_out, y_out=d_y, workspace=st["ws"][c], validated=True,
+                               hints=hints)
                 st["ws"][c] = pl.workspace       # kept: the next call's chunk reuses it
                 self.run(pl)
                 st["ev_run"][c].record(st["run"])

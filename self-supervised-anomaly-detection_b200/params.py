@@ -49,7 +49,8 @@ IMAGE_PARAMS_DTYPE = np.dtype([
     ("rnd_rgb", "u1", (3,)),         # 179
     ("jit_order", "u1", (4,)),       # 182
     ("jit_en", "u1"),                # 186  bit0 brightness, bit1 contrast, bit2 saturation
-    ("reserved", "u1", (5,)),        # 187
+    ("line_n", "u1"),                # 187  label 3: points of the poly-line
+    ("src_index", "<u4"),            # 188  source image when the batch is indexed into a resident set
 ], align=False)
 assert IMAGE_PARAMS_DTYPE.itemsize == 192
 

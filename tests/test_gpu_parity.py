@@ -18,6 +18,19 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
+def _reload_env():
+    from ssad_b200 import _native
+    _native.load().ssad_reload_env()
+
+
+@pytest.fixture(autouse=True)
+def _default_env_after_each_test():
+    yield
+    for k in [k for k in os.environ if k.startswith("SSAD_V7_")]:
+        del os.environ[k]
+    _reload_env()
+
+
 def _check_against_oracle(name, batch, monkeypatch=None, env=None):
     import gpu_utils as U
     from oracle import generator as og
@@ -26,6 +39,7 @@ def _check_against_oracle(name, batch, monkeypatch=None, env=None):
     if env:
         for k, v in env.items():
             monkeypatch.setenv(k, v)
+    _reload_env()                                # the library reads its tuning environment once
     out = U.run_cuda(sc)
     x = out["x_u8"].cpu().numpy()
     y = out["y"].cpu().numpy()
@@ -53,33 +67,8 @@ def test_generate_matches_oracle(name):
 
 @pytest.mark.parametrize("name", S.BIG)
 def test_generate_big_images_match_oracle(name):
-    """Images whose rows do not fit one CTA's shared memory: clusters of eight CTAs, rows resident (512) or
-    streamed through TMA chunk buffers once per pass (768, 1024)."""
+    """512 / 768 / 1024-pixel images: several slabs per image, taller canvases (two canvas CTAs per image at 1024)."""
     _check_against_oracle(name, 5)
-
-
-@pytest.mark.parametrize("kernel", ["v7", "v6", "v5", "v4", "v3", "cluster", "generic"])
-@pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture"])
-def test_every_kernel_variant_matches_oracle(name, kernel, monkeypatch):
-    _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": kernel})
-
-
-@pytest.mark.parametrize("csize", ["1", "2", "4", "8"])
-@pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed"])
-def test_v3_cluster_sizes_match_oracle(name, csize, monkeypatch):
-    _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v3", "SSAD_V3_C": csize})
-
-
-@pytest.mark.parametrize("csize", ["1", "2", "4", "8"])
-@pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
-def test_v5_cluster_sizes_match_oracle(name, csize, monkeypatch):
-    _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v5", "SSAD_V5_C": csize})
-
-
-@pytest.mark.parametrize("csize", ["1", "2", "4", "8"])
-@pytest.mark.parametrize("name", ["image_level", "image_level_256", "patch_level", "non_fixed", "texture"])
-def test_v6_cluster_sizes_match_oracle(name, csize, monkeypatch):
-    _check_against_oracle(name, 12, monkeypatch, {"SSAD_KERNEL": "v6", "SSAD_V6_C": csize})
 
 
 @pytest.mark.parametrize("env", [{"SSAD_V7_NOFAST": "1"}, {"SSAD_V7_UPT": "3"}, {"SSAD_V7_NC": "1"}, {"SSAD_V7_NC": "16"}, {"SSAD_V7_SPLIT": "3"},
@@ -90,7 +79,7 @@ def test_v7_loop_and_grid_variants_match_oracle(name, env, monkeypatch):
     """v7's general unit loops (the fast ones need a power-of-two width and whole slabs), odd slab sizes, and the
     number of CTAs that share an image's patch canvas, and the batch cut into chunks that run on lanes (helper streams;
     with more chunks than lanes a lane's workspace is reused by its next chunk)."""
-    _check_against_oracle(name, 12, monkeypatch, dict(env, SSAD_KERNEL="v7"))
+    _check_against_oracle(name, 12, monkeypatch, env)
 
 
 @pytest.mark.parametrize("name,batch", [("patch_level", 257), ("texture", 259), ("image_level_256", 3)])
@@ -184,8 +173,8 @@ def test_graph_replay_matches_plain_launch(name, split, monkeypatch):
     """BatchGenerator.capture(): the whole ssad_generate call (kernels on the caller's stream and on the helper
     streams of the chunked pipeline) recorded in a CUDA graph; replays on fresh inputs equal plain launches."""
     import gpu_utils as U
-    monkeypatch.setenv("SSAD_KERNEL", "v7")
     monkeypatch.setenv("SSAD_V7_SPLIT", split)
+    _reload_env()
     sc = S.build(name, 12)
     gen = U.make_generator(sc)
     src = torch.from_numpy(sc.images).cuda()
@@ -254,3 +243,84 @@ def test_host_buffer_pipeline_two_batches_in_flight():
         assert torch.equal(outs[k][1], refs[k]["x_u8"])
         assert torch.equal(outs[k][2], refs[k]["y"])
     assert not torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture", "non_fixed"])
+def test_indexed_sources_match_gathered_batch(name):
+    """SsadBatchDesc.src_indexed: the records carry the index of their source image in a resident set (no gather of the
+    batch, datasets.py:211 becomes an index; per-image masks are then per source image) -- same bytes as running the
+    gathered batch."""
+    import gpu_utils as U
+    sc = S.build(name, 12)
+    gen = U.make_generator(sc)
+    ref = U.run_cuda(sc, norm_dtype=torch.float32, debug=False, gen=gen)
+    rng = np.random.default_rng(4)
+    perm = rng.permutation(12)
+    resident = torch.from_numpy(sc.images[perm]).cuda()           # resident[k] = image perm[k]; item i reads row inv[i]
+    inv = np.argsort(perm)
+    masks = U.per_image_masks(sc)
+    if masks is not None:
+        masks = masks[torch.as_tensor(perm).cuda()].contiguous()
+    out = gen.generate(resident, sc.params, masks=masks, want_u8=True, norm_dtype=torch.float32, src_index=inv)
+    torch.cuda.synchronize()
+    assert torch.equal(out["x_u8"], ref["x_u8"])
+    assert torch.equal(out["x"], ref["x"])
+    assert torch.equal(out["y"], ref["y"])
+    # a batch larger than the resident set (duplicated filenames, functional.py:64-68) and the chunked path
+    big = np.concatenate([inv] * 25)[:290]
+    pb = S.ssad_b200.params_from_draws(sc.cfg, {k: np.concatenate([v] * 25)[:290] for k, v in sc.params.draws.items()})
+    out2 = gen.generate(resident, pb, masks=masks, want_u8=True, src_index=big)
+    torch.cuda.synchronize()
+    assert torch.equal(out2["x_u8"][:12], ref["x_u8"]) and torch.equal(out2["x_u8"][276:288], ref["x_u8"])
+
+
+def test_two_host_threads_with_their_own_contexts():
+    """ssad_context_create: two host threads drive the same device at once, each through its own context (its own helper
+    streams); both get the bytes of a single-threaded call."""
+    import threading
+    import gpu_utils as U
+    scs = [S.build("patch_level", 300, seed=1), S.build("image_level_256", 280, seed=2)]
+    gens = [U.make_generator(sc) for sc in scs]
+    refs = [U.run_cuda(sc, norm_dtype=None, debug=False, gen=g)["x_u8"].clone() for sc, g in zip(scs, gens)]
+    outs, errs = [None, None], []
+
+    def work(k):
+        try:
+            torch.cuda.set_device(0)
+            ctx = gens[k].new_context()
+            stream = torch.cuda.Stream()
+            src = torch.from_numpy(scs[k].images).cuda()
+            with torch.cuda.stream(stream):
+                for _ in range(6):
+                    o = gens[k].generate(src, scs[k].params, masks=U.per_image_masks(scs[k]), want_u8=True, context=ctx)
+                stream.synchronize()
+            outs[k] = o["x_u8"]
+            gens[k].free_context(ctx)
+        except Exception as e:           # noqa: BLE001
+            errs.append(e)
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    for k in range(2):
+        assert torch.equal(outs[k], refs[k])
+
+
+def test_saturation_factors_up_to_two_match_oracle():
+    """The table after Saturation serves factors up to 2 (torchvision ColorJitter(saturation <= 1)); beyond that the
+    library refuses the batch instead of falling back to another kernel."""
+    import gpu_utils as U
+    sc = S.build("image_level", 12)
+    draws = {k: v.copy() for k, v in sc.params.draws.items()}
+    draws["jit_s"] = np.linspace(0.0, 2.0, 12).astype(np.float32).astype(np.float64)
+    draws["jit_b"] = np.linspace(0.5, 1.5, 12).astype(np.float32).astype(np.float64)
+    sc.params = S.ssad_b200.params_from_draws(sc.cfg, draws)
+    out = U.run_cuda(sc, norm_dtype=None)
+    x = out["x_u8"].cpu().numpy()
+    for i in range(12):
+        ox, oy, _ = S.run_oracle(sc, i)
+        assert np.array_equal(x[i], ox), i
+    draws["jit_s"][3] = 2.5
+    sc.params = S.ssad_b200.params_from_draws(sc.cfg, draws)
+    with pytest.raises(RuntimeError):
+        U.run_cuda(sc, norm_dtype=None)

@@ -159,6 +159,35 @@ def test_paste_patch_matches_pillow():
 
 
 @pytest.mark.gpu
+def test_paste_patch_soft_mask_blends_like_pillow():
+    """A mask with values between 0 and 255 (the reference's commented-out GaussianBlur mask is one): Paste.c blends."""
+    from PIL import Image
+    from ssad_b200 import dataset_generator as dg
+    rng = np.random.default_rng(8)
+    img = Image.fromarray(rng.integers(0, 256, (48, 48, 3), dtype=np.uint8))
+    patch = Image.fromarray(rng.integers(0, 256, (20, 31, 3), dtype=np.uint8))
+    soft = Image.fromarray(rng.integers(0, 256, (20, 31), dtype=np.uint8), mode="L")
+    ref = img.copy()
+    ref.paste(patch, (9, -4), mask=soft)
+    assert np.array_equal(np.array(dg.paste_patch(img, patch, (9, -4), soft)), np.array(ref))
+
+
+@pytest.mark.gpu
+def test_check_color_similarity_matches_reference_formula():
+    """dataset_generator.py:147-159: numpy mean / 255 per channel, sklearn cosine_similarity."""
+    from sklearn.metrics.pairwise import cosine_similarity
+    from ssad_b200 import dataset_generator as dg
+    rng = np.random.default_rng(12)
+    for _ in range(20):
+        a = rng.integers(0, 256, (int(rng.integers(2, 90)), int(rng.integers(2, 90)), 3), dtype=np.uint8)
+        b = rng.integers(0, int(rng.integers(2, 256)), (int(rng.integers(2, 40)), int(rng.integers(2, 40)), 3), dtype=np.uint8)
+        v1 = (a.mean(axis=(0, 1)) / 255)[None, :]
+        v2 = (b.mean(axis=(0, 1)) / 255)[None, :]
+        want = float(cosine_similarity(v1, v2).squeeze())
+        assert abs(dg.check_color_similarity(a, b) - want) < 1e-12
+
+
+@pytest.mark.gpu
 def test_obj_mask_pil_in_pil_out():
     from PIL import Image
     from oracle import objmask as om
