@@ -109,6 +109,9 @@ typedef struct SsadBatchDesc {
     int32_t line_max;          /* points per image in line_xy */
     const int16_t* line_xy;    /* device [batch][line_max][2]: the poly-line vertices (x, y) of label-3 records, as ints the way
                                   ImageDraw.line truncates them; NULL when no record has label 3 */
+    int32_t max_scar_w, max_scar_h; /* upper bounds of scar_size over the batch (sizes the rotated-scar colour canvas);
+                                  0: use max_patch_w / max_patch_h.  With label-3 records max_patch_w / max_patch_h must
+                                  also cover the bounding box of every poly-line (at most the working image). */
 } SsadBatchDesc;
 
 /* Optional per-image trace of the data-dependent decisions, for parity tests. */
@@ -203,6 +206,13 @@ void ssad_obj_mask_test_knobs(float margin_scale, int32_t sub_cap, int32_t pix_p
  * out: [n][max_h][max_w] uint8 0/255 (rows/cols beyond (pw, ph) are zero). */
 int ssad_polygon_mask(int32_t n, const int16_t* poly_xy /* [n][8][2] */, const uint8_t* poly_n /* [n] */,
                       const int16_t* size /* [n][2] pw, ph */, uint8_t* out, int32_t max_w, int32_t max_h, void* stream);
+
+/* ImageDraw.line(points, fill, width) without joints (datasets.py:383-388, label 3): n poly-lines of npts[i] <= 32 integer
+ * vertices xy[i][k] = (x, y) (ImageDraw truncates the floats it is given) drawn with `line_width` (1: Bresenham segments
+ * + the last point; > 1: one polygon per segment, Draw.c ImagingDrawWideLine) on width x height canvases.
+ * out: [n][height][width] uint8 0 / 255.  All pointers device. */
+int ssad_line_mask(int32_t n, const int16_t* xy, const uint8_t* npts, int32_t max_pts, int32_t line_width, uint8_t* out,
+                   int32_t width, int32_t height, void* stream);
 
 /* Image.transform(size, AFFINE, NEAREST) with affine_fixed coefficients (Image.rotate(expand=True) at
  * datasets.py:344, RandomAffine at datasets.py:221): channels in {3,4}; outside -> 0. */

@@ -240,6 +240,40 @@ def apply_scar(x: Image.Image, image_for_cutting: Image.Image, coords_map: np.nd
     return x
 
 
+def apply_line(x: Image.Image, coords_map: np.ndarray, d: Dict, patch_localization: bool, info: Dict) -> Image.Image:
+    """Label 3 "long line", datasets.py:357-388 statement by statement with the draws made explicit
+    (``random.randint(a, b)`` = a + ((r * (b - a + 1)) >> 32) with the 32-bit draw r, as for the centre picks).
+    An empty mask makes the reference raise IndexError (``coords_map[0]``); here the image stays as it is."""
+    from PIL import ImageDraw
+    from scipy.signal import savgol_filter
+    if len(coords_map) == 0:
+        info["line_points"] = []
+        return x
+    draw = ImageDraw.Draw(x)
+    side = ['left', 'top'][int(d["line_side"])]
+    n = 60 if not patch_localization else 30
+    points = []
+    c = 0
+    for i in range(n):
+        offset = i / n
+        hi = int(len(coords_map) * offset)
+        index = c + ((int(d["line_r"][i]) * (hi - c + 1)) >> 32)
+        p = coords_map[index]
+        points.append(tuple(p))
+        c = index
+    rgb = ['black', 'white', 'silver'][int(d["line_rgb"])]
+    if side == 'left':
+        points.sort(key=lambda tup: tup[0])
+    points = savgol_filter(points, 10, 2, axis=0)
+    if not patch_localization:
+        p_splits = np.array_split(points, 10)
+        points = p_splits[int(d["line_k"])]
+    points = [tuple(p) for p in points]
+    info["line_points"] = points
+    draw.line(points, fill=rgb, width=1 if patch_localization else 3)
+    return x
+
+
 def color_jitter(x: Image.Image, d: Dict) -> Image.Image:
     """``CPP.jitter_transforms(x)`` -- datasets.py:44-47,391; torchvision
     ColorJitter.forward with explicit fn_idx and factors (hue is None)."""
@@ -312,8 +346,8 @@ def generate_item(original: Image.Image, d: Dict, cfg, donors: Optional[List[Ima
             x = apply_polygon(x, image_for_cutting, coords_map, d, cfg.patch_area_ratio, factor_patch, info)
         elif y == 2:
             x = apply_scar(x, image_for_cutting, coords_map, d, cfg.scar_area_ratio, factor_scar, info)
-        else:
-            raise NotImplementedError("label 3 (long line, datasets.py:357-388) is a 'next' row of SURVEY 8(f)")
+        elif y == 3:
+            x = apply_line(x, coords_map, d, cfg.patch_localization, info)
     if getattr(cfg, "jitter", True):
         x = color_jitter(x, d)
     return x, y, info
@@ -352,3 +386,12 @@ def do_scar(img: Image.Image, image_for_cutting: Image.Image, segmentation: Imag
     x = img.copy()
     coordinates = coords_map_of(segmentation)
     return apply_scar(x, image_for_cutting, coordinates, d, None, factor, info)
+
+
+def do_swirl(img: Image.Image, image_for_cutting: Image.Image, segmentation: Image.Image, patch_loc: bool,
+             d: Dict, info: Optional[Dict] = None) -> Image.Image:
+    """test_artificial_transformations.py:125-164 (same body as the dataset's label 3)."""
+    info = {} if info is None else info
+    x = img.copy()
+    coordinates = coords_map_of(segmentation)
+    return apply_line(x, coordinates, d, patch_loc, info)

@@ -246,6 +246,104 @@ def polygon_mask(points: Sequence[Tuple[int, int]], w: int, h: int) -> np.ndarra
 
 
 # --------------------------------------------------------------------------
+# A.3b  ImageDraw.line(points, fill, width) -- Draw.c ImagingDrawLine / ImagingDrawWideLine
+#       datasets.py:383-388 (label 3 "long line": width 3 image-level, 1 in patch mode)
+# --------------------------------------------------------------------------
+def line_segment_pixels(x0: int, y0: int, x1: int, y1: int):
+    """Draw.c line8/line32: the pixels of one width-1 segment, in drawing order.  The end point itself is not drawn
+    (the next segment of a poly-line starts there; ``_draw_lines`` draws the last point of the poly-line itself)."""
+    out = []
+    dx = x1 - x0
+    xs = 1
+    if dx < 0:
+        dx, xs = -dx, -1
+    dy = y1 - y0
+    ys = 1
+    if dy < 0:
+        dy, ys = -dy, -1
+    if dx == 0:
+        for _ in range(dy):
+            out.append((x0, y0)); y0 += ys
+    elif dy == 0:
+        for _ in range(dx):
+            out.append((x0, y0)); x0 += xs
+    elif dx > dy:
+        n = dx
+        dy += dy
+        e = dy - dx
+        dx += dx
+        for _ in range(n):
+            out.append((x0, y0))
+            if e >= 0:
+                y0 += ys
+                e -= dx
+            e += dy
+            x0 += xs
+    else:
+        n = dy
+        dx += dx
+        e = dx - dy
+        dy += dy
+        for _ in range(n):
+            out.append((x0, y0))
+            if e >= 0:
+                x0 += xs
+                e -= dy
+            e += dx
+            y0 += ys
+    return out
+
+
+def wide_line_quad(x0: int, y0: int, x1: int, y1: int, width: int):
+    """Draw.c ImagingDrawWideLine: the four vertices of the polygon drawn for a segment of ``width`` > 1 (None for a
+    zero-length segment, which draws the single point)."""
+    dx, dy = x1 - x0, y1 - y0
+    if dx == 0 and dy == 0:
+        return None
+    big = math.hypot(dx, dy)
+    small = (width - 1) / 2.0
+    ratio_max = _round_up_d(small) / big
+    ratio_min = _round_down_d(small) / big
+    dxmin = _round_down_d(ratio_min * dy)
+    dxmax = _round_down_d(ratio_max * dy)
+    dymin = _round_up_d(ratio_min * dx)
+    dymax = _round_up_d(ratio_max * dx)
+    return [(x0 - dxmin, y0 + dymax), (x1 - dxmin, y1 + dymax), (x1 + dxmax, y1 - dymin), (x0 + dxmax, y0 - dymin)]
+
+
+def _round_up_d(f: float) -> int:          # Draw.c ROUND_UP on a double
+    return int(math.floor(f + 0.5)) if f >= 0.0 else -int(math.floor(abs(f) + 0.5))
+
+
+def _round_down_d(f: float) -> int:        # Draw.c ROUND_DOWN on a double
+    return int(math.ceil(f - 0.5)) if f >= 0.0 else -int(math.ceil(abs(f) - 0.5))
+
+
+def line_mask(points: Sequence[Tuple[float, float]], width: int, w: int, h: int) -> np.ndarray:
+    """``ImageDraw.line(points, fill, width)`` (joint=None) on a ``w x h`` canvas -> bool[h, w] of the pixels set.
+    Coordinates are truncated to int as ``_draw_lines`` does (``(int)p[0]`` ...)."""
+    out = np.zeros((h, w), dtype=bool)
+    pts = [(int(x), int(y)) for x, y in points]            # C cast: toward zero
+    for (x0, y0), (x1, y1) in zip(pts[:-1], pts[1:]):
+        if width <= 1:
+            for x, y in line_segment_pixels(x0, y0, x1, y1):
+                if 0 <= x < w and 0 <= y < h:
+                    out[y, x] = True
+        else:
+            quad = wide_line_quad(x0, y0, x1, y1, width)
+            if quad is None:
+                if 0 <= x0 < w and 0 <= y0 < h:
+                    out[y0, x0] = True
+            else:
+                out |= polygon_mask(quad, w, h)
+    if width <= 1 and len(pts) >= 2:                        # _imaging.c _draw_lines: "draw last point"
+        x, y = pts[-1]
+        if 0 <= x < w and 0 <= y < h:
+            out[y, x] = True
+    return out
+
+
+# --------------------------------------------------------------------------
 # A.4  colour ops: Blend.c, Convert.c (RGB->L), ImageEnhance, ColorJitter
 #      datasets.py:44-47,298-299,338-339,391
 # --------------------------------------------------------------------------

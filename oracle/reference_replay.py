@@ -274,6 +274,34 @@ def _defect_program(t: Tape, req, y: int, n_coords: int, box):
     return req
 
 
+def _randint_from_draw(r, args):
+    a, b = args
+    return a + ((int(r) * (b - a + 1)) >> 32)
+
+
+def _randint_to_draw(v, args):
+    a, b = args
+    n = b - a + 1
+    r = -((-(int(v) - a) << 32) // n)          # ceil((v - a) * 2^32 / n)
+    assert a + ((r * n) >> 32) == v and r < (1 << 32)
+    return r
+
+
+def _line_program(t: Tape, req, n_coords: int, patch_localization: bool):
+    """Draws of the y == 3 branch (datasets.py:357-388): side, n index picks, colour, (image-level) split pick."""
+    req = yield t.val(req, "line_side", want="choice", to_draw=lambda v, a: _index_of(a[0], v),
+                      from_draw=lambda s, a: a[0][int(s)])
+    n = 30 if patch_localization else 60
+    for i in range(n):
+        req = yield t.val(req, "line_r", i, want="randint", check=lambda a, i=i: a[1] == int(n_coords * (i / n)),
+                          to_draw=_randint_to_draw, from_draw=_randint_from_draw)
+    req = yield t.val(req, "line_rgb", want="choice", to_draw=lambda v, a: _index_of(a[0], v),
+                      from_draw=lambda s, a: a[0][int(s)])
+    if not patch_localization:
+        req = yield t.val(req, "line_k", want="randint", check=lambda a: a == (0, 9))
+    return req
+
+
 def _no_more(req):
     raise AssertionError(f"unexpected extra draw {req[0]}{req[1]}")
 
@@ -391,6 +419,8 @@ def run_getitem(cfg, original_png: str, draws: Dict, donors, fixed_segmentation,
         y = int(t.draws["label"]) if effective_label is None else effective_label
         if y in (1, 2):
             req = yield from _defect_program(t, req, y, n_coords, box1 if y == 1 else box2)
+        elif y == 3:
+            req = yield from _line_program(t, req, n_coords, cfg.patch_localization)
         _no_more(req)
 
     tape = Tape(program, draws, record)

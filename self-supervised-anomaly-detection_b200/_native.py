@@ -30,6 +30,7 @@ class SsadBatchDesc(C.Structure):
         ("any_warp", C.c_int32), ("sat_factor_max", C.c_float),
         ("src_indexed", C.c_int32), ("src_count", C.c_int32),
         ("line_width", C.c_int32), ("line_max", C.c_int32), ("line_xy", C.c_void_p),
+        ("max_scar_w", C.c_int32), ("max_scar_h", C.c_int32),
     ]
 
 
@@ -58,6 +59,7 @@ EXPORTS = {
     "ssad_obj_mask_launches": (C.c_int, []),
     "ssad_obj_mask_test_knobs": (None, [C.c_float, C.c_int32, C.c_int32]),
     "ssad_polygon_mask": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "ssad_line_mask": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "ssad_affine_nearest": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.c_void_p,
                                       C.c_int32, C.c_int32, C.c_void_p]),
     "ssad_color_jitter": (C.c_int, [C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 6),

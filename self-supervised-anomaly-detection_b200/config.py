@@ -50,7 +50,7 @@ class GeneratorConfig:
     imsize: Tuple[int, int] = (256, 256)
     patch_localization: bool = False
     patch_size: int = 64
-    num_labels: int = 3                     # 3-class contract {0,1,2}; HEAD draws randint(0,3)
+    num_labels: int = 3                     # 3-class contract {0,1,2}; 4 = HEAD's randint(0,3) incl. label 3 "long line"
     jitter: bool = True
     n_donors: int = 0                       # len(images_for_cut) (textures only)
     patch_area_ratio: Optional[Tuple[float, float]] = None
@@ -61,11 +61,11 @@ class GeneratorConfig:
     # geometry without the pre-warp and, with patch_loc=True, with container factor 1
     force_warp: Optional[bool] = None
     force_container_factor: Optional[float] = None
+    force_line_patch_mode: Optional[bool] = None   # do_swirl(patch_loc=True): 30 points, width 1, no split (script :131,:152-164)
 
     def __post_init__(self):
-        if not 1 <= int(self.num_labels) <= 3:
-            # label 3 ("long line", datasets.py:357-388) is SURVEY.md section 8(f) "next": not built
-            raise ValueError("num_labels must be in 1..3: label 3 of the reference is not implemented")
+        if not 1 <= int(self.num_labels) <= 4:
+            raise ValueError("num_labels must be in 1..4 (datasets.py:215 draws randint(0, 3))")
         if self.patch_area_ratio is None:   # datasets.py:184-185
             self.patch_area_ratio = CPP.rectangle_area_ratio_patch if self.patch_localization else CPP.rectangle_area_ratio
         if self.scar_area_ratio is None:
@@ -88,6 +88,13 @@ class GeneratorConfig:
         if self.force_warp is not None:
             return bool(self.force_warp)
         return (not self.patch_localization) and (not self.is_non_fixed)
+
+    @property
+    def line_patch_mode(self) -> bool:
+        """Label 3: 30 picks / width 1 / no split (patch mode) or 60 picks / width 3 / one tenth (datasets.py:360,374-388)."""
+        if self.force_line_patch_mode is not None:
+            return bool(self.force_line_patch_mode)
+        return bool(self.patch_localization)
 
     # -- geometry
     @property

@@ -241,6 +241,116 @@ __device__ inline void polygon_fill_row(const Polygon& P, int y, int w, uint32_t
     }
 }
 
+// ------------------------------------------------------------------ ImageDraw.line (Draw.c ImagingDrawLine / ImagingDrawWideLine)
+// Label 3 "long line" (datasets.py:383-388): a poly-line of integer vertices (ImageDraw truncates the floats it is given),
+// width 1 (patch mode) or 3.  The line is rasterised once into coverage bit rows over its bounding box (clipped to the
+// image); the generator then pastes a flat colour behind that coverage like a polygon patch.
+struct LineBox {
+    int x0, y0, w, h;            // box of every pixel the poly-line can touch, inside the image (w <= 0: nothing)
+};
+__device__ __forceinline__ int draw_round_up(double f) {      // Draw.c ROUND_UP on a double
+    return (f >= 0.0) ? (int)floor(f + 0.5) : -(int)floor(fabs(f) + 0.5);
+}
+__device__ __forceinline__ int draw_round_down(double f) {    // Draw.c ROUND_DOWN on a double
+    return (f >= 0.0) ? (int)ceil(f - 0.5) : -(int)ceil(fabs(f) - 0.5);
+}
+__device__ inline LineBox line_box(const int16_t* __restrict__ xy, int n, int width, int W, int H) {
+    LineBox B = {0, 0, 0, 0};
+    if (n < 2) return B;                                      // fewer than two points: _draw_lines draws nothing
+    int xmin = 32767, xmax = -32768, ymin = 32767, ymax = -32768;
+    for (int i = 0; i < n; ++i) {
+        xmin = min(xmin, (int)xy[2 * i]); xmax = max(xmax, (int)xy[2 * i]);
+        ymin = min(ymin, (int)xy[2 * i + 1]); ymax = max(ymax, (int)xy[2 * i + 1]);
+    }
+    const int m = width > 1 ? width / 2 + 1 : 0;             // the quad of a wide segment reaches ROUND_UP((width-1)/2) further
+    const int x0 = max(xmin - m, 0), x1 = min(xmax + m, W - 1), y0 = max(ymin - m, 0), y1 = min(ymax + m, H - 1);
+    if (x1 < x0 || y1 < y0) return B;
+    B.x0 = x0; B.y0 = y0; B.w = x1 - x0 + 1; B.h = y1 - y0 + 1;
+    return B;
+}
+__device__ __forceinline__ void line_set(uint32_t* cov, int pitch, const LineBox& B, int x, int y) {
+    x -= B.x0; y -= B.y0;
+    if ((unsigned)x < (unsigned)B.w && (unsigned)y < (unsigned)B.h) atomicOr(&cov[(size_t)y * pitch + (x >> 5)], 1u << (x & 31));
+}
+// line8 / line32: one width-1 segment, its end point excluded
+__device__ inline void line_segment(uint32_t* cov, int pitch, const LineBox& B, int x0, int y0, int x1, int y1) {
+    int dx = x1 - x0, dy = y1 - y0, xs = 1, ys = 1;
+    if (dx < 0) { dx = -dx; xs = -1; }
+    if (dy < 0) { dy = -dy; ys = -1; }
+    if (dx == 0) {
+        for (int i = 0; i < dy; ++i) { line_set(cov, pitch, B, x0, y0); y0 += ys; }
+    } else if (dy == 0) {
+        for (int i = 0; i < dx; ++i) { line_set(cov, pitch, B, x0, y0); x0 += xs; }
+    } else if (dx > dy) {
+        const int n = dx;
+        dy += dy;
+        int e = dy - dx;
+        dx += dx;
+        for (int i = 0; i < n; ++i) {
+            line_set(cov, pitch, B, x0, y0);
+            if (e >= 0) { y0 += ys; e -= dx; }
+            e += dy; x0 += xs;
+        }
+    } else {
+        const int n = dy;
+        dx += dx;
+        int e = dx - dy;
+        dy += dy;
+        for (int i = 0; i < n; ++i) {
+            line_set(cov, pitch, B, x0, y0);
+            if (e >= 0) { x0 += xs; e -= dy; }
+            e += dx; y0 += ys;
+        }
+    }
+}
+// ImagingDrawWideLine: the polygon of one wide segment, in box coordinates; false: zero-length segment (a single point)
+__device__ inline bool wide_line_polygon(Polygon& P, const LineBox& B, int x0, int y0, int x1, int y1, int width) {
+    const int dx = x1 - x0, dy = y1 - y0;
+    if (dx == 0 && dy == 0) return false;
+    // hypot(dx, dy): dx^2 + dy^2 is an exact integer, its correctly rounded root is what a correctly rounded hypot returns
+    // (and no ratio below can sit within an ulp of the .5 the roundings turn on: dy / big = 1/2 needs dx^2 = 3 dy^2)
+    const double big = __dsqrt_rn((double)((long long)dx * dx + (long long)dy * dy)), small = (width - 1) / 2.0;
+    const double ratio_max = draw_round_up(small) / big, ratio_min = draw_round_down(small) / big;
+    const int dxmin = draw_round_down(ratio_min * dy), dxmax = draw_round_down(ratio_max * dy);
+    const int dymin = draw_round_up(ratio_min * dx), dymax = draw_round_up(ratio_max * dx);
+    int16_t v[4][2] = {{(int16_t)(x0 - dxmin - B.x0), (int16_t)(y0 + dymax - B.y0)}, {(int16_t)(x1 - dxmin - B.x0), (int16_t)(y1 + dymax - B.y0)},
+                       {(int16_t)(x1 + dxmax - B.x0), (int16_t)(y1 - dymin - B.y0)}, {(int16_t)(x0 + dxmax - B.x0), (int16_t)(y0 - dymin - B.y0)}};
+    polygon_setup(P, v, 4, B.h);
+    return true;
+}
+// The whole poly-line into `cov` (B.h rows of `pitch` words, zeroed by the caller, visible to every thread: a barrier
+// lies between the zeroing and this call); `quads`: shared scratch for n - 1 polygons (width > 1).  Every thread of the
+// CTA calls it; the caller synchronises before reading `cov`.
+__device__ inline void line_rasterize(const int16_t* __restrict__ xy, int n, int width, const LineBox& B, uint32_t* cov, int pitch,
+                                      Polygon* quads, int tid, int nt) {
+    if (B.w <= 0 || n < 2) return;
+    const int nseg = n - 1;
+    if (width <= 1) {
+        for (int s = tid; s < nseg; s += nt) line_segment(cov, pitch, B, xy[2 * s], xy[2 * s + 1], xy[2 * s + 2], xy[2 * s + 3]);
+        if (tid == 0) line_set(cov, pitch, B, xy[2 * nseg], xy[2 * nseg + 1]);       // _draw_lines: "draw last point"
+        return;
+    }
+    for (int s = tid; s < nseg; s += nt) {
+        if (!wide_line_polygon(quads[s], B, xy[2 * s], xy[2 * s + 1], xy[2 * s + 2], xy[2 * s + 3], width)) {
+            quads[s].n = -1;
+            line_set(cov, pitch, B, xy[2 * s], xy[2 * s + 1]);
+        }
+    }
+    __syncthreads();
+    for (int item = tid; item < nseg * B.h; item += nt) {
+        const int s = item / B.h, v = item - s * B.h;
+        const Polygon& P = quads[s];
+        if (P.n < 0) continue;
+        bool touches = v >= P.ymin && v <= P.ymax;
+        for (int i = 0; i < P.n && !touches; ++i) touches = P.e[i].ymin == P.e[i].ymax && P.e[i].ymin == v;
+        if (!touches) continue;
+        uint32_t row[32];                                                            // W <= 1024
+        for (int j = 0; j < pitch; ++j) row[j] = 0u;
+        polygon_fill_row(P, v, B.w, row);
+        for (int j = 0; j < pitch; ++j) if (row[j]) atomicOr(&cov[(size_t)v * pitch + j], row[j]);
+    }
+}
+
 // ------------------------------------------------------------------ block reductions
 template <int NT>
 __device__ __forceinline__ uint32_t block_sum_u32(uint32_t v, uint32_t* scratch /* >= NT/32 words */) {

@@ -312,6 +312,8 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
     __shared__ Plan D;
     __shared__ Polygon G;
     __shared__ Tables TP;
+    __shared__ Polygon quads[31];                // label 3: the polygons of the wide segments (at most 32 points)
+    __shared__ LineBox LB;
     uint32_t* const rowpre = reinterpret_cast<uint32_t*>(smem);
     const int tid = threadIdx.x, b = blockIdx.x;
     const int H = g.H, W = g.W, npix = H * W;
@@ -354,9 +356,21 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
     const int n_coords = (d.mask_mode == SSAD_MASK_ALL) ? npix : (defect ? (int)rowpre[H] : 0);
     int y = P.label;
     if (defect && d.coverage_min3 > 0 && 3 * n_coords < d.coverage_min3) y = 0;   // datasets.py:258-259
-    const int npaste = (y == 0) ? 0 : (y == 1 ? 1 : P.scar_k);
-    const int bw = (y == 1) ? pw : P.scar_size[0], bh = (y == 1) ? ph : P.scar_size[1];
-    if (tid < npaste) {
+    // label 3 "long line" (datasets.py:357-388): a flat colour behind the coverage of the poly-line, one "paste" of its
+    // bounding box at the box's own position
+    const int16_t* const lxy = (y == 3 && d.line_xy) ? d.line_xy + (size_t)b * d.line_max * 2 : nullptr;
+    const int ln = lxy ? min((int)P.line_n, d.line_max) : 0;
+    if (y == 3) {
+        if (tid == 0) {
+            LB = line_box(lxy, ln, d.line_width, W, H);
+            if ((uint32_t)LB.w > g.cov_pitch * 32u || (uint32_t)LB.h > g.cov_rows) LB.w = LB.h = 0;    // (cannot happen: the host sizes the rows)
+            D.paste[0][0] = LB.x0; D.paste[0][1] = LB.y0;
+        }
+        __syncthreads();
+    }
+    const int npaste = (y == 0) ? 0 : (y == 1 ? 1 : (y == 3 ? (LB.w > 0 ? 1 : 0) : P.scar_k));
+    const int bw = (y == 1) ? pw : (y == 3 ? LB.w : P.scar_size[0]), bh = (y == 1) ? ph : (y == 3 ? LB.h : P.scar_size[1]);
+    if (y != 3 && tid < npaste) {
         // centres + container clamp (dataset_generator.py:104-144, 259-265): one thread per paste
         int cx, cy;
         if (n_coords == 0) {
@@ -375,7 +389,7 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
         int pl, pt;
         clamp_to_container(y == 1 ? d.box_poly : d.box_scar, bw, bh, cx, cy, pl, pt);
         D.paste[tid][0] = pl; D.paste[tid][1] = pt;
-    } else if (tid < 5) {
+    } else if (tid < 5 && !(y == 3 && tid == 0)) {
         D.paste[tid][0] = 0; D.paste[tid][1] = 0;
     }
     if (y == 1 && tid == 32) polygon_setup(G, P.poly_xy, P.poly_n, ph);
@@ -420,6 +434,10 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
             affine_span((long long)P.scar_fix[5] + (long long)v * P.scar_fix[4], P.scar_fix[3], (long long)ph << 16, lo, hi);
             if (lo <= hi) row_set_bits(row, lo, hi);
         }
+    } else if (y == 3 && npaste) {
+        for (int i = tid; i < bh * pitchw; i += NT) cov[i] = 0;
+        __syncthreads();
+        line_rasterize(lxy, ln, d.line_width, LB, cov, pitchw, quads, tid, NT);
     }
     if (tid == 0) {
         // work lists: pass 1 runs the ops ahead of Contrast (and may have nothing to do at all), pass 2 the rest
@@ -647,15 +665,18 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
         int flat = 0;
         uint32_t frgb[3] = {0, 0, 0};
         int avg[3] = {0, 0, 0};
-        if (P.src_variant == 1) {           // colour = int(mean) (dataset_generator.py:202-207)
+        if (y0 == 3) {                      // the line's colour, no similarity branch (datasets.py:369-388)
+            flat = 1;
+            for (int k = 0; k < 3; ++k) { frgb[k] = P.rnd_rgb[k]; psum[k] = 0; }
+        } else if (P.src_variant == 1) {    // colour = int(mean) (dataset_generator.py:202-207)
             flat = 1;
             for (int k = 0; k < 3; ++k) { frgb[k] = psum[k] / np; avg[k] = (int)frgb[k]; psum[k] = frgb[k] * np; }
         } else if (P.src_variant == 2) {    // random colour (dataset_generator.py:194-199)
             flat = 1;
             for (int k = 0; k < 3; ++k) { frgb[k] = P.rnd_rgb[k]; psum[k] = frgb[k] * np; }
         }
-        double cs;
-        const bool sim = similarity_branch(xs, (double)npix, psum, (double)np, cs);     // datasets.py:295 / 335
+        double cs = 0.0;
+        const bool sim = (y0 != 3) && similarity_branch(xs, (double)npix, psum, (double)np, cs);     // datasets.py:295 / 335
         if (flat && sim)                    // brightness of a flat patch is a flat patch
             for (int k = 0; k < 3; ++k) frgb[k] = brightness_u8(brightness_u8(frgb[k], D.bf1), D.bf2);
         D.flat = flat; D.sim = sim ? 1 : 0; D.cosine = cs;
@@ -742,8 +763,8 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
         const int per_w = ((total + NWARP - 1) / NWARP + 31) & ~31;
         w_lo = min(total, warp * per_w); w_hi = min(total, w_lo + per_w);
     };
-    if (y == 1) {
-        // polygon: one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
+    if (y == 1 || y == 3) {
+        // polygon (or the poly-line of label 3: a flat colour): one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
         // thread and round, their loads issued together: the chain coverage word -> cut pixel -> old pixel is three
         // memory latencies long, and nothing else hides it.
         constexpr int NB = SSAD_V7_NB_POLY;
@@ -1060,8 +1081,9 @@ static bool make_geo7(const SsadBatchDesc& d, Geo7& g) {
     g.cov_pitch = (uint32_t)(d.max_patch_w + 31) / 32u;
     g.cov_rows = (uint32_t)d.max_patch_h;
     g.cov_stride = (size_t)g.cov_pitch * g.cov_rows;
-    g.canvas_pitch = (uint32_t)d.max_patch_w;
-    g.canvas_stride = (size_t)d.max_patch_w * (size_t)d.max_patch_h;
+    const int cw = d.max_scar_w > 0 ? d.max_scar_w : d.max_patch_w, ch = d.max_scar_h > 0 ? d.max_scar_h : d.max_patch_h;
+    g.canvas_pitch = (uint32_t)cw;                          // the colour canvas holds rotated scars only
+    g.canvas_stride = (size_t)cw * (size_t)ch;
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
     g.o_canvas = up((size_t)d.batch * d.height * d.width * 3);
     g.o_state = g.o_canvas + up((size_t)d.batch * g.canvas_stride * 4);

@@ -154,6 +154,31 @@ paste_kernel(uint8_t* __restrict__ img, int W, int H, const uint8_t* __restrict_
     }
 }
 
+// ---- ImageDraw.line(points, fill, width) (datasets.py:383-388): the pixels set, one CTA per poly-line
+__global__ void __launch_bounds__(256)
+line_mask_kernel(const int16_t* __restrict__ xy, const uint8_t* __restrict__ npts, int max_pts, int width, uint8_t* __restrict__ out,
+                 int W, int H) {
+    extern __shared__ uint32_t cov[];            // H rows of ceil(W / 32) words (box coordinates: row stride = box pitch)
+    __shared__ Polygon quads[31];
+    __shared__ LineBox B;
+    const int i = blockIdx.x, tid = threadIdx.x;
+    const int16_t* p = xy + (size_t)i * max_pts * 2;
+    const int n = min((int)npts[i], min(max_pts, 32));
+    if (tid == 0) B = line_box(p, n, width, W, H);
+    for (int k = tid; k < H * ((W + 31) / 32); k += 256) cov[k] = 0u;
+    __syncthreads();
+    const int pitch = (B.w + 31) / 32;
+    line_rasterize(p, n, width, B, cov, max(pitch, 1), quads, tid, 256);
+    __syncthreads();
+    uint8_t* o = out + (size_t)i * W * H;
+    for (int k = tid; k < W * H; k += 256) {
+        const int y = k / W, x = k - y * W;
+        const int u = x - B.x0, v = y - B.y0;
+        const bool on = B.w > 0 && (unsigned)u < (unsigned)B.w && (unsigned)v < (unsigned)B.h && ((cov[v * pitch + (u >> 5)] >> (u & 31)) & 1u);
+        o[k] = on ? 255 : 0;
+    }
+}
+
 // ---- check_color_similarity (dataset_generator.py:147-159): cosine of the mean colours of two images
 __global__ void __launch_bounds__(256)
 color_similarity_kernel(const uint8_t* __restrict__ a, int na, const uint8_t* __restrict__ b, int nb, double* __restrict__ out) {
@@ -252,6 +277,17 @@ extern "C" int ssad_color_similarity(const uint8_t* image, int32_t n_image, cons
                                      void* stream) {
     if (!image || !patch || !out || n_image <= 0 || n_patch <= 0) return SSAD_EINVAL;
     ssad::color_similarity_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(image, n_image, patch, n_patch, out);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_line_mask(int32_t n, const int16_t* xy, const uint8_t* npts, int32_t max_pts, int32_t line_width, uint8_t* out,
+                              int32_t width, int32_t height, void* stream) {
+    if (n < 0 || !xy || !npts || !out || max_pts < 2 || width <= 0 || height <= 0 || line_width < 0) return SSAD_EINVAL;
+    if (n == 0) return SSAD_OK;
+    const size_t smem = (size_t)height * ((width + 31) / 32) * 4;
+    if (smem > 40 * 1024 || width > 1024) return SSAD_EUNSUPPORTED;
+    ssad::line_mask_kernel<<<n, 256, smem, static_cast<cudaStream_t>(stream)>>>(xy, npts, max_pts, line_width, out, width, height);
     SSAD_CHECK_LAUNCH();
     return SSAD_OK;
 }

@@ -255,6 +255,7 @@ def _script_config(imsize, patch_loc: bool) -> GeneratorConfig:
     """The exerciser script's call shape (test_artificial_transformations.py:20-24, 72-76): image-sized working image,
     no pre-warp, no jitter; container factor and area ratios switch on ``patch_loc``."""
     return GeneratorConfig(subject="bottle", imsize=imsize, jitter=False, patch_localization=False, force_warp=False,
+                           num_labels=4, force_line_patch_mode=bool(patch_loc),
                            force_container_factor=1 if patch_loc else None,
                            patch_area_ratio=CPP.rectangle_area_ratio_patch if patch_loc else None,
                            scar_area_ratio=CPP.scar_area_ratio_patch if patch_loc else None)
@@ -299,3 +300,10 @@ def do_scar(img, image_for_cutting=None, segmentation=None, patch_loc: bool = Fa
             rng: Optional[np.random.Generator] = None, device=None):
     """test_artificial_transformations.py:72-122: small rectangle rotated in [-45, 45] degrees, pasted 2-5 times (label 2)."""
     return _do_defect(2, img, image_for_cutting, segmentation, patch_loc, params, rng, device)
+
+
+def do_swirl(img, image_for_cutting=None, segmentation=None, patch_loc: bool = False, subject=None,
+             params: Optional[ParamBatch] = None, rng: Optional[np.random.Generator] = None, device=None):
+    """test_artificial_transformations.py:125-164 (the dataset's label 3, datasets.py:357-388): a smoothed poly-line
+    through picks of the mask, drawn black / white / silver, width 3 (1 and all 30 points with ``patch_loc``)."""
+    return _do_defect(3, img, image_for_cutting, segmentation, patch_loc, params, rng, device)

@@ -258,3 +258,119 @@ class PretextTaskDatamodule:
 
     def predict_dataloader(self) -> BatchLoader:
         return BatchLoader(self.test_dataset, self.batch_size, shuffle=False, drop_last=False)
+
+
+# ---------------------------------------------------------------------- MVTec evaluation data (datasets.py:50-163)
+def get_subdirectories(main_path: str) -> np.ndarray:
+    """functional.py:38-41."""
+    return np.array(sorted(n for n in os.listdir(main_path) if os.path.isdir(main_path + "/" + n)), dtype=str)
+
+
+def get_test_data_filenames(main_path: str) -> np.ndarray:
+    """functional.py:54-61: the ``*.png`` of every defect class under ``<root>/test/``, class by class."""
+    out = np.empty(0)
+    for defection in get_subdirectories(main_path):
+        out = np.concatenate([out, get_filenames(main_path + defection + "/")])
+    return out
+
+
+def get_ground_truth_filename(test_filename: str, ground_truth_dir: str) -> Optional[str]:
+    """functional.py:44-51: ``.../test/<defect>/<name>.png`` -> ``<gt dir><defect>/<name>_mask.png``; None for 'good'."""
+    parts = test_filename.rsplit("/", 2)
+    defection, image_name = parts[1], parts[2]
+    if defection == "good":
+        return None
+    stem = image_name.split(".")
+    return ground_truth_dir + defection + "/" + stem[0] + "_mask" + "." + stem[1]
+
+
+def get_ground_truth(filename: Optional[str] = None, imsize=(256, 256)) -> np.ndarray:
+    """functional.py:20-24: ``Image.open(f).resize(imsize).convert('1')`` (all-zero when there is no mask) -> bool [H, W]."""
+    from PIL import Image
+    if filename:
+        return np.asarray(Image.open(filename).resize(tuple(imsize)).convert("1"))
+    return np.zeros((imsize[1], imsize[0]), dtype=bool)
+
+
+class MVTecDataset:
+    """datasets.py:50-84: real test images with their ground-truth masks, no augmentation.  Every file is decoded once
+    on the host; images (uint8) and masks live on the device.  ``get_batch(indices)`` / iteration yield the reference's
+    item tuple batch-wise: ``(x, gt f32 [B,1,H,W], original f32 [B,3,H,W])`` with ``x`` = ``Normalize(ToTensor(...))``
+    when ``transform`` is set (the datamodule's transform, datasets.py:100-103), else the uint8 images."""
+
+    def __init__(self, dataset_dir: str, images_filenames, imsize: tuple = (256, 256), transform=True,
+                 patch_level: bool = False, *, device="cuda") -> None:
+        self.dataset_dir, self.imsize, self.transform, self.patch_level = dataset_dir, tuple(imsize), transform, patch_level
+        self.images_filenames = np.asarray(images_filenames)
+        self.device = torch.device(device)
+        W, H = self.imsize
+        n = len(self.images_filenames)
+        imgs = np.zeros((n, H, W, 3), dtype=np.uint8)
+        gts = np.zeros((n, H, W), dtype=bool)
+        for i, f in enumerate(self.images_filenames):
+            imgs[i] = load_image(str(f), self.imsize)
+            gts[i] = get_ground_truth(get_ground_truth_filename(str(f), dataset_dir + "ground_truth/"), self.imsize)
+        self.images = torch.from_numpy(imgs).to(self.device)
+        self.gt = torch.from_numpy(gts).to(self.device)
+        mean = torch.as_tensor(CPP.normalize_mean, dtype=torch.float32, device=self.device)[None, :, None, None]
+        std = torch.as_tensor(CPP.normalize_std, dtype=torch.float32, device=self.device)[None, :, None, None]
+        self._mean, self._std = mean, std
+
+    def __len__(self) -> int:
+        return int(self.images_filenames.shape[0])
+
+    def get_batch(self, indices: Sequence[int]):
+        idx = torch.as_tensor(np.asarray(indices), device=self.device)
+        src = self.images.index_select(0, idx)
+        original = to_tensor(src)                                    # ToTensor(original), datasets.py:81
+        x = (original - self._mean) / self._std if self.transform else src   # Normalize: the same float32 sub / div
+        gt = self.gt.index_select(0, idx)[:, None].to(torch.float32)         # ToTensor(gt) of a mode '1' image: 0.0 / 1.0
+        return x, gt, original
+
+    def __getitem__(self, index: int):
+        x, gt, original = self.get_batch([int(index)])
+        return x[0], gt[0], original[0]
+
+
+class _EvalLoader:
+    def __init__(self, dataset: MVTecDataset, batch_size: int, shuffle: bool, seed: int):
+        self.dataset, self.batch_size, self.shuffle = dataset, int(batch_size), shuffle
+        self.rng = np.random.default_rng(seed)
+
+    def __len__(self) -> int:
+        return (len(self.dataset) + self.batch_size - 1) // self.batch_size
+
+    def __iter__(self) -> Iterator:
+        n = len(self.dataset)
+        order = self.rng.permutation(n) if self.shuffle else np.arange(n)
+        for b in range(len(self)):
+            yield self.dataset.get_batch(order[b * self.batch_size:(b + 1) * self.batch_size])
+
+
+class MVTecDatamodule:
+    """datasets.py:87-163 with the same arguments (``tools.inference`` builds it at tools.py:331-339)."""
+
+    def __init__(self, root_dir: str, imsize: tuple = (256, 256), batch_size: int = 32, seed: int = 0, patch_level=None,
+                 *, device="cuda"):
+        self.root_dir, self.imsize, self.batch_size, self.seed, self.patch_level = root_dir, tuple(imsize), batch_size, seed, patch_level
+        self.device = device
+        self.train_images_filenames = get_filenames(self.root_dir + "/train/good/")
+        self.test_images_filenames = get_test_data_filenames(self.root_dir + "/test/")
+
+    def setup(self, stage=None) -> None:
+        from sklearn.model_selection import train_test_split
+        train, val = train_test_split(self.train_images_filenames, test_size=0.2, random_state=self.seed)
+        mk = lambda names: MVTecDataset(self.root_dir, names, imsize=self.imsize, transform=True, device=self.device)   # noqa: E731
+        self.train_dataset, self.val_dataset, self.test_dataset = mk(train), mk(val), mk(self.test_images_filenames)
+
+    def train_dataloader(self):
+        return _EvalLoader(self.train_dataset, self.batch_size, True, self.seed)
+
+    def val_dataloader(self):
+        return _EvalLoader(self.val_dataset, self.batch_size, False, self.seed)
+
+    def test_dataloader(self):
+        return _EvalLoader(self.test_dataset, self.batch_size, False, self.seed)
+
+    def predict_dataloader(self):
+        return _EvalLoader(self.test_dataset, self.batch_size, False, self.seed)

@@ -69,8 +69,10 @@ class BatchGenerator:
         self.lib = N.load()
         W, H = cfg.imsize
         self.mask_bits = None
+        self.mask_host = None
         if mask is not None:
             mask = np.asarray(mask, dtype=bool)
+            self.mask_host = mask
             if mask.shape != (H, W):
                 raise ValueError(f"mask must be [H={H}, W={W}]")
             self.mask_bits = torch.from_numpy(pack_mask_bits(mask).view(np.int32)).to(self.device)
@@ -170,8 +172,26 @@ class BatchGenerator:
         d.any_warp = int(cfg.warp)
         d.src_indexed = int(indexed)
         d.src_count = int(src.shape[0]) if indexed else 0
-        d.line_width = 1 if cfg.patch_localization else 3          # datasets.py:383-388
+        d.line_width = 1 if cfg.line_patch_mode else 3             # datasets.py:383-388
         return d
+
+    def _window_mask_fn(self, rec: np.ndarray, masks, src_index):
+        """i -> bool [h, w] mask window of item i as ``__getitem__`` sees it (datasets.py:242-264), None for textures."""
+        W, H = self.cfg.work_size
+        host_masks = None
+        if masks is not None:                        # per-image masks live on the device: label-3 items need theirs here
+            host_masks = unpack_mask_bits(masks.cpu().numpy(), self.cfg.imsize[0])
+
+        def fn(i: int):
+            if host_masks is not None:
+                m = host_masks[int(src_index[i]) if src_index is not None else i]
+            elif self.mask_host is not None:
+                m = self.mask_host
+            else:
+                return None
+            x0, y0 = int(rec["crop_off"][i][0]), int(rec["crop_off"][i][1])
+            return m[y0:y0 + H, x0:x0 + W]
+        return fn
 
     @staticmethod
     def batch_hints(rec: np.ndarray):
@@ -181,7 +201,9 @@ class BatchGenerator:
         max_w = max(int(rec["rect"][:, 2].max(initial=1)), int(rec["scar_size"][:, 0].max(initial=1)))
         max_h = max(int(rec["rect"][:, 3].max(initial=1)), int(rec["scar_size"][:, 1].max(initial=1)))
         sat_on = (rec["jit_en"] & 4) != 0
-        return crop_aligned, max_w, max_h, float(rec["jit_f"][:, 2][sat_on].max(initial=0.0))
+        scar = (max(int(rec["scar_size"][:, 0].max(initial=1)), 1), max(int(rec["scar_size"][:, 1].max(initial=1)), 1))
+        return (crop_aligned, max_w, max_h, float(rec["jit_f"][:, 2][sat_on].max(initial=0.0)), scar,
+                bool(np.any(rec["label"] == 3)))
 
     def plan(self, src: torch.Tensor, params: ParamBatch, *, masks=None, want_u8=True, norm_dtype=None, debug=False,
              params_dev=None, out_u8=None, out_norm=None, y_out=None, workspace=None, src_index=None,
@@ -203,18 +225,28 @@ class BatchGenerator:
             self.validate_records(rec, src.shape[1:3])
         if indexed and (int(np.min(src_index)) < 0 or int(np.max(src_index)) >= int(src.shape[0])):
             raise ValueError("src_index outside the resident set")
+        params_dev_given = params_dev is not None
         if params_dev is None:
             params_dev = self.upload_params(params, src_index)
         if hints is None:
             hints = self.batch_hints(rec)
-        crop_aligned, max_w, max_h, sat_max = hints
-        d = self.describe(B, src, max_w, max_h, masks, norm_dtype, crop_aligned, indexed)
-        line_xy = getattr(params, "line_xy", None)
+        crop_aligned, max_w, max_h, sat_max, scar_dims, any_line = hints
         line_dev = None
-        if line_xy is not None and int(rec["line_n"].max(initial=0)) > 0:
-            line_dev = torch.from_numpy(np.ascontiguousarray(line_xy, dtype=np.int16)).to(self.device)
-            d.line_max = int(line_xy.shape[1])
+        if any_line:
+            # label 3 "long line": the vertices depend on the mask (datasets.py:357-377) -- resolved on the host once
+            if params.line_xy is None:
+                if params_dev_given:
+                    raise ValueError("label-3 records: call params.resolve_lines(...) before uploading the records")
+                params.resolve_lines(self._window_mask_fn(rec, masks, src_index))
+            max_w, max_h = max(max_w, W), max(max_h, H)      # the coverage rows span the poly-line's bounding box
+        d = self.describe(B, src, max_w, max_h, masks, norm_dtype, crop_aligned, indexed)
+        d.max_scar_w, d.max_scar_h = scar_dims
+        if any_line:
+            line_dev = torch.from_numpy(np.ascontiguousarray(params.line_xy, dtype=np.int16)).to(self.device)
+            d.line_max = int(params.line_xy.shape[1])
             d.line_xy = line_dev.data_ptr()
+            if params_dev_given is False:
+                params_dev = self.upload_params(params, src_index)   # (line_n was written by resolve_lines)
         d.sat_factor_max = sat_max
         if want_u8 and out_u8 is None:
             out_u8 = torch.empty((B, H, W, 3), dtype=torch.uint8, device=self.device)
@@ -340,6 +372,11 @@ class BatchGenerator:
             raise ValueError("params and h_src disagree on the batch size (or the records have the wrong dtype)")
         self.validate_records(rec, h_src.shape[1:3])
         hints = self.batch_hints(rec)            # one set of bounds for every piece of the batch
+        if hints[5] and params.line_xy is None:  # label 3: the poly-lines are resolved against the mask before the upload
+            if masks_fn is not None:
+                raise ValueError("label-3 records with per-image device masks: call params.resolve_lines(...) first")
+            params.resolve_lines(self._window_mask_fn(rec, None, None))
+            rec = np.ascontiguousarray(params.records)
         st["ev_rec"].synchronize()               # the previous call's upload has left the staging buffer
         st["h_rec"].numpy()[...] = rec.view(np.uint8).reshape(B, IMAGE_PARAMS_DTYPE.itemsize)
         with torch.cuda.stream(st["up"]):

@@ -64,7 +64,12 @@ _DRAW_SPECS = {
     "fallback_c": ("i8", (6, 2)), "poly_n_side": ("i8", (4,)), "poly_v": ("i8", (4, 2)),
     "scar_k": ("i8", ()), "scar_angle": ("i8", ()), "jit_order": ("i8", (4,)),
     "jit_b": ("f8", ()), "jit_c": ("f8", ()), "jit_s": ("f8", ()),
+    # label 3 "long line" (datasets.py:357-388): side, the 60 (30 in patch mode) index draws, colour, split pick
+    "line_side": ("i8", ()), "line_r": ("u8", (60,)), "line_rgb": ("i8", ()), "line_k": ("i8", ()),
 }
+
+LINE_COLOURS = ((0, 0, 0), (255, 255, 255), (192, 192, 192))      # PIL 'black', 'white', 'silver' (datasets.py:369)
+LINE_MAX_POINTS = 32                                               # 30 points in patch mode, 6 after the split image-level
 
 
 def empty_draws(batch: int) -> Dict[str, np.ndarray]:
@@ -264,6 +269,7 @@ class ParamBatch:
     cfg: GeneratorConfig
     draws: Dict[str, np.ndarray]
     records: np.ndarray
+    line_xy: Optional[np.ndarray] = None      # int16 [B, LINE_MAX_POINTS, 2]: label-3 poly-lines once resolved against the masks
 
     def __len__(self) -> int:
         return self.records.shape[0]
@@ -272,7 +278,29 @@ class ParamBatch:
         return {k: (v[i].copy() if v[i].ndim else v[i].item()) for k, v in self.draws.items()}
 
     def slice(self, lo: int, hi: int) -> "ParamBatch":
-        return ParamBatch(self.cfg, {k: v[lo:hi] for k, v in self.draws.items()}, self.records[lo:hi])
+        return ParamBatch(self.cfg, {k: v[lo:hi] for k, v in self.draws.items()}, self.records[lo:hi],
+                          None if self.line_xy is None else self.line_xy[lo:hi])
+
+    def resolve_lines(self, window_mask_of) -> None:
+        """Label 3: turn the index draws into poly-line vertices (``line_xy``, ``records['line_n']``).  The picks index
+        ``coords_map`` (datasets.py:261-264), so they need the mask window of every label-3 image:
+        ``window_mask_of(i)`` -> bool [h, w] (None: all-positive mask).  Host work: ~60 picks, a stable sort and SciPy's
+        ``savgol_filter`` per image, exactly the reference's calls."""
+        rec, d = self.records, self.draws
+        B = len(rec)
+        self.line_xy = np.zeros((B, LINE_MAX_POINTS, 2), dtype=np.int16)
+        rec["line_n"] = 0
+        W, H = self.cfg.work_size
+        for i in np.nonzero(rec["label"] == 3)[0]:
+            m = window_mask_of(int(i))
+            flat = None if m is None else np.flatnonzero(np.asarray(m, dtype=bool).reshape(-1))
+            n_coords = W * H if flat is None else int(flat.shape[0])
+            pts = line_points(n_coords, flat, W, d["line_r"][i], int(d["line_side"][i]), int(d["line_k"][i]),
+                              self.cfg.line_patch_mode)
+            n = 0 if pts is None else pts.shape[0]
+            if n:
+                self.line_xy[i, :n] = np.clip(np.trunc(pts), -32768, 32767).astype(np.int16)   # _draw_lines: (int)p[k]
+            rec["line_n"][i] = n
 
     def shard(self, rank: int, world: int) -> "ParamBatch":
         """This rank's contiguous block of the batch (one process per GPU; images are independent, so the shards
@@ -288,6 +316,32 @@ def shard_bounds(batch: int, rank: int, world: int) -> Tuple[int, int]:
     q, r = divmod(int(batch), int(world))
     lo = rank * q + min(rank, r)
     return lo, lo + q + (1 if rank < r else 0)
+
+
+def line_points(n_coords: int, flat: Optional[np.ndarray], width: int, r, side: int, k: int, patch_mode: bool):
+    """datasets.py:359-377: n = 60 (30) picks ``coords_map[randint(c, int(N * i / n))]`` with c the previous index,
+    (sort by x when side == 'left'), ``savgol_filter(points, 10, 2, axis=0)``, image-level: part k of
+    ``np.array_split(points, 10)``.  ``flat`` = row-major flat indices of the set mask pixels (None: every pixel),
+    ``r`` the 32-bit draws: randint(a, b) = a + ((r * (b - a + 1)) >> 32).  -> float64 [m, 2] (x, y), or None when the
+    mask is empty (the reference raises IndexError there)."""
+    from scipy.signal import savgol_filter
+    if n_coords <= 0:
+        return None
+    n = 30 if patch_mode else 60
+    c = 0
+    idx = np.empty(n, dtype=np.int64)
+    for i in range(n):
+        hi = int(n_coords * (i / n))
+        c = c + ((int(r[i]) * (hi - c + 1)) >> 32)
+        idx[i] = c
+    pix = idx if flat is None else flat[idx]
+    pts = np.stack([pix % width, pix // width], axis=1)          # coords_map rows are (x, y)
+    if side == 0:                                                # 'left': points.sort(key=lambda tup: tup[0]) -- stable
+        pts = pts[np.argsort(pts[:, 0], kind="stable")]
+    pts = savgol_filter([tuple(p) for p in pts], 10, 2, axis=0)
+    if not patch_mode:
+        pts = np.array_split(pts, 10)[k]
+    return np.asarray(pts, dtype=np.float64)
 
 
 def derive_records(cfg: GeneratorConfig, draws: Dict[str, np.ndarray]) -> np.ndarray:
@@ -349,6 +403,14 @@ def derive_records(cfg: GeneratorConfig, draws: Dict[str, np.ndarray]) -> np.nda
         fix, size = rotate_expand_fixed(pw[idx], ph[idx], draws["scar_angle"][idx])
         rec["scar_fix"][idx] = fix
         rec["scar_size"][idx] = size
+    is_line = label == 3
+    if np.any(is_line):
+        # a line is a flat colour behind a coverage mask: no patch rectangle, no cut, the colour in rnd_rgb; the
+        # vertices depend on the mask and are resolved later (ParamBatch.resolve_lines)
+        idx = np.nonzero(is_line)[0]
+        rec["rect"][idx] = 0
+        rec["src_variant"][idx] = 2
+        rec["rnd_rgb"][idx] = np.asarray(LINE_COLOURS, dtype=np.uint8)[draws["line_rgb"][idx]]
     return rec
 
 
@@ -365,8 +427,8 @@ def sample_params(cfg: GeneratorConfig, batch: int, rng: Optional[np.random.Gene
     # datasets.py:215  y = random.randint(0, 3)  (3-class contract: {0,1,2})
     d["label"] = rng.integers(0, cfg.num_labels, B) if labels is None else np.asarray(labels, dtype=np.int64).copy()
     label = d["label"]
-    if np.any(label > 2) or np.any(label < 0):
-        raise ValueError("labels must be in {0,1,2} (label 3 'long line' is not implemented)")
+    if np.any(label > 3) or np.any(label < 0):
+        raise ValueError("labels must be in {0,1,2,3}")
     # datasets.py:221  RandomAffine(3, scale=(1.05, 1.1)): torch draws float32
     ang = rng.uniform(-CPP.affine_degrees, CPP.affine_degrees, B).astype(np.float32)
     ang[ang == 0] = np.float32(1e-3)
@@ -434,6 +496,12 @@ def sample_params(cfg: GeneratorConfig, batch: int, rng: Optional[np.random.Gene
     lo, hi = 1 - CPP.jitter_offset, 1 + CPP.jitter_offset
     for k in ("jit_b", "jit_c", "jit_s"):
         d[k] = rng.uniform(lo, hi, B).astype(np.float32).astype(np.float64)
+    if cfg.num_labels > 3 or np.any(label == 3):
+        # label 3 (drawn last: batches of the 3-class contract keep the values they had before this label existed)
+        d["line_side"] = rng.integers(0, 2, B)                                  # datasets.py:359 random.choice(['left','top'])
+        d["line_r"] = rng.integers(0, 1 << 32, (B, 60), dtype=np.uint64)        # :364 random.randint(c, int(N * i / n))
+        d["line_rgb"] = rng.integers(0, 3, B)                                   # :369 random.choice(['black','white','silver'])
+        d["line_k"] = rng.integers(0, 10, B)                                    # :376 random.randint(0, 9)
     return ParamBatch(cfg, d, derive_records(cfg, d))
 
 

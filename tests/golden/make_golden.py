@@ -37,7 +37,8 @@ import scenarios as S  # noqa: E402
 from oracle import reference_replay as rr  # noqa: E402
 
 BATCH = {"image_level": 10, "image_level_256": 4, "patch_level": 10, "patch_level_32": 12, "texture": 10,
-         "non_fixed": 8, "empty_mask": 6, "single_pixel_mask": 6, "flat_grey": 8}
+         "non_fixed": 8, "empty_mask": 6, "single_pixel_mask": 6, "flat_grey": 8,
+         "lines_image": 9, "lines_patch": 12, "lines_texture": 8, "screw_patch": 12}
 
 
 def scenario_sha(sc: S.Scenario) -> str:
@@ -118,14 +119,16 @@ def script_fn_outputs(seed: int = 0):
 
 def main():
     assert rr.available(), "reference checkout not found"
-    for name in S.ALL:
+    only = sys.argv[1:]                      # python make_golden.py [scenario ...]: regenerate just these
+    for name in (only or S.ALL):
         sc = S.build(name, BATCH[name])
         x, y, xn = reference_outputs(sc)
         np.savez_compressed(os.path.join(HERE, f"{name}.npz"), x=x, y=y, xn=xn,
                             sha=np.frombuffer(bytes.fromhex(scenario_sha(sc)), dtype=np.uint8))
         print(name, x.shape, "labels", y.tolist())
-    np.savez_compressed(os.path.join(HERE, "script_fns.npz"), **script_fn_outputs())
-    print("script_fns done")
+    if not only:
+        np.savez_compressed(os.path.join(HERE, "script_fns.npz"), **script_fn_outputs())
+        print("script_fns done")
 
 
 if __name__ == "__main__":

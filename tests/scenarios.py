@@ -115,6 +115,36 @@ def build(name: str, batch: int = 12, seed: int = 0) -> Scenario:
         donors = np.concatenate([synth.texture_images(1, S, S, 300 + k, tint=rng.integers(40, 220, 3))
                                  for k in range(15)])
         mask = None
+    elif name == "lines_image":         # label 3 "long line" (datasets.py:357-388), image-level: width 3, split in 10
+        S = 128
+        cfg = GeneratorConfig(subject="bottle", imsize=(S, S), num_labels=4)
+        imgs = synth.object_images(batch, S, S, 22 + seed)
+        mask = synth.disc_mask(S, S)
+        donors = None
+        labels = np.where(np.arange(batch) % 3 != 1, 3, rng.integers(0, 4, batch))
+    elif name == "lines_patch":         # label 3 in patch mode: width 1, all 30 points; coverage rule may zero the label
+        S, ps = 160, 96
+        cfg = GeneratorConfig(subject="bottle", imsize=(S, S), patch_localization=True, patch_size=ps, num_labels=4,
+                              patch_area_ratio=(0.1, 0.2), scar_area_ratio=(0.01, 0.02))
+        imgs = synth.object_images(batch, S, S, 23 + seed)
+        mask = synth.disc_mask(S, S, 0.45)
+        donors = None
+        labels = np.where(np.arange(batch) % 4 != 2, 3, rng.integers(0, 4, batch))
+    elif name == "lines_texture":       # label 3 on a texture class: all-positive mask, warp on
+        S = 128
+        cfg = GeneratorConfig(subject="carpet", imsize=(S, S), n_donors=15, num_labels=4)
+        imgs = synth.texture_images(batch, S, S, 24 + seed, tint=(120, 110, 100))
+        donors = np.concatenate([synth.texture_images(1, S, S, 400 + k, tint=rng.integers(40, 220, 3))
+                                 for k in range(15)])
+        mask = None
+        labels = np.where(np.arange(batch) % 2 == 0, 3, rng.integers(0, 4, batch))
+    elif name == "screw_patch":         # non-fixed class in patch mode: per-image mask AND the class pre-crop
+        S, ps = 256, 64                 # (25, 25, 230, 230), datasets.py:246-248; all four labels
+        cfg = GeneratorConfig(subject="screw", imsize=(S, S), patch_localization=True, patch_size=ps, num_labels=4)
+        imgs = synth.screw_images(batch, S, S, 25 + seed)
+        mask = "per_image"
+        donors = None
+        labels = np.arange(batch) % 4
     else:
         raise KeyError(name)
     if isinstance(mask, str):
@@ -128,7 +158,8 @@ def build(name: str, batch: int = 12, seed: int = 0) -> Scenario:
 BIG = ["big_fixed_768", "big_non_fixed_1024", "mid_texture_512"]      # no golden vectors (size); oracle parity only
 
 ALL = ["image_level", "image_level_256", "patch_level", "patch_level_32", "texture", "non_fixed",
-       "empty_mask", "single_pixel_mask", "flat_grey"]
+       "empty_mask", "single_pixel_mask", "flat_grey",
+       "lines_image", "lines_patch", "lines_texture", "screw_patch"]
 
 
 # ------------------------------------------------------------------ oracle driver

@@ -151,3 +151,36 @@ def test_argument_validation_raises():
         gen.generate(torch.zeros((2, 32, 64, 3), dtype=torch.uint8, device="cuda"), p)
     with pytest.raises(ValueError):
         gen.generate(torch.zeros((2, 64, 64, 3), dtype=torch.float32, device="cuda"), p)
+
+
+def test_line_mask_matches_pillow():
+    """ImageDraw.line(points, fill, width) for widths 1 and 3 (label 3, datasets.py:383-388): random poly-lines incl.
+    points outside the canvas, repeated points, axis-parallel and diagonal segments -- the set pixels, bit-exact."""
+    import ctypes as C
+    from PIL import Image, ImageDraw
+    from ssad_b200 import _native as N
+    lib = N.load()
+    rng = np.random.default_rng(17)
+    W, H, n, MAXP = 96, 80, 300, 32
+    xy = np.zeros((n, MAXP, 2), dtype=np.int16)
+    npts = np.zeros(n, dtype=np.uint8)
+    for i in range(n):
+        k = int(rng.integers(2, 31))
+        pts = np.stack([rng.integers(-12, W + 12, k), rng.integers(-12, H + 12, k)], axis=1)
+        if i % 4 == 0:
+            pts[1] = pts[0]                               # zero-length segment
+        if i % 5 == 0:
+            pts[:, 1] = pts[0, 1]                         # horizontal poly-line
+        if i % 7 == 0 and k >= 4:
+            pts[2:4, 0] = pts[2, 0]                       # a vertical segment
+        xy[i, :k], npts[i] = pts, k
+    for width in (1, 3):
+        d_xy, d_n = torch.from_numpy(xy).cuda(), torch.from_numpy(npts).cuda()
+        out = torch.zeros((n, H, W), dtype=torch.uint8, device="cuda")
+        N.check(lib.ssad_line_mask(n, C.c_void_p(d_xy.data_ptr()), C.c_void_p(d_n.data_ptr()), MAXP, width,
+                                   C.c_void_p(out.data_ptr()), W, H, None), "ssad_line_mask")
+        got = out.cpu().numpy() > 0
+        for i in range(n):
+            im = Image.new("L", (W, H), 0)
+            ImageDraw.Draw(im).line([tuple(map(float, p)) for p in xy[i, :npts[i]]], fill=255, width=width)
+            assert np.array_equal(got[i], np.array(im) > 0), (width, i, xy[i, :npts[i]].tolist())

@@ -239,3 +239,76 @@ def test_datamodule_yields_training_batches(tmp_path):
     assert len(dm.test_dataloader()) == 5
     xt, yt, _ = next(iter(dm.test_dataloader()))
     assert xt.shape[0] == 8
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("patch_loc", [False, True])
+def test_do_swirl_matches_oracle(patch_loc):
+    """do_swirl (test_artificial_transformations.py:125-164) = label 3 on one image, against the oracle's restatement
+    (pinned by the label-3 goldens made from the reference's own __getitem__)."""
+    from PIL import Image
+    from oracle import generator as og
+    from ssad_b200 import dataset_generator as dg, sample_params
+    sc = S.build("image_level", 6, seed=3)
+    seg = S.mask_to_pil(sc.mask)
+    cfg = dg._script_config(sc.cfg.imsize, patch_loc)
+    for i in range(6):
+        pb = sample_params(cfg, 1, np.random.default_rng(70 + i), labels=np.full(1, 3))
+        img = Image.fromarray(sc.images[i])
+        got = dg.do_swirl(img, img, seg, patch_loc, params=pb)
+        want = og.do_swirl(img, img, seg, patch_loc, pb.image_draws(0))
+        assert np.array_equal(np.array(got), np.array(want)), (patch_loc, i)
+        assert not np.array_equal(np.array(got), sc.images[i])
+
+
+# ---------------------------------------------------------------------------------------------- MVTec evaluation loader
+def _write_mvtec_tree(root, n_train=6, n_test=3, size=(40, 32)):
+    """A tiny MVTec-shaped class directory with PNG files: train/good, test/{good,crack}, ground_truth/crack."""
+    from PIL import Image
+    rng = np.random.default_rng(2)
+    for sub, n in (("train/good", n_train), ("test/good", n_test), ("test/crack", n_test)):
+        os.makedirs(os.path.join(root, sub), exist_ok=True)
+        for i in range(n):
+            Image.fromarray(rng.integers(0, 256, (size[1], size[0], 3), dtype=np.uint8)).save(os.path.join(root, sub, f"{i:03d}.png"))
+    os.makedirs(os.path.join(root, "ground_truth/crack"), exist_ok=True)
+    for i in range(n_test):
+        m = (rng.random((size[1], size[0])) < 0.3).astype(np.uint8) * 255
+        Image.fromarray(m, mode="L").save(os.path.join(root, "ground_truth/crack", f"{i:03d}_mask.png"))
+
+
+def test_mvtec_filename_helpers_match_reference_rules(tmp_path):
+    from ssad_b200 import datasets as D
+    root = str(tmp_path / "bottle") + "/"
+    _write_mvtec_tree(root)
+    names = D.get_test_data_filenames(root + "test/")
+    assert [n.rsplit("/", 2)[1] for n in names] == ["crack"] * 3 + ["good"] * 3          # class by class, sorted
+    assert D.get_ground_truth_filename(names[0], root + "ground_truth/") == root + "ground_truth/crack/000_mask.png"
+    assert D.get_ground_truth_filename(names[-1], root + "ground_truth/") is None          # functional.py:48-49
+    assert not D.get_ground_truth(None, (8, 6)).any() and D.get_ground_truth(None, (8, 6)).shape == (6, 8)
+
+
+@pytest.mark.gpu
+def test_mvtec_datamodule_matches_torchvision_items(tmp_path):
+    """MVTecDataset.__getitem__ (datasets.py:67-81): x = Normalize(ToTensor(resized)), ToTensor(gt), ToTensor(original)."""
+    import torch
+    from PIL import Image
+    from torchvision import transforms
+    from ssad_b200 import datasets as D
+    root = str(tmp_path / "bottle") + "/"
+    _write_mvtec_tree(root)
+    dm = D.MVTecDatamodule(root, imsize=(24, 16), batch_size=4, seed=0)
+    dm.setup()
+    tf = transforms.Compose([transforms.ToTensor(), transforms.Normalize((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))])
+    seen = 0
+    for x, gt, original in dm.test_dataloader():
+        for k in range(x.shape[0]):
+            f = dm.test_images_filenames[seen]
+            img = Image.open(f).resize((24, 16)).convert("RGB")
+            g = D.get_ground_truth_filename(f, root + "ground_truth/")
+            gt_ref = Image.open(g).resize((24, 16)).convert("1") if g else Image.new(mode="1", size=(24, 16))
+            assert torch.equal(x[k].cpu(), tf(img))
+            assert torch.equal(original[k].cpu(), transforms.ToTensor()(img))
+            assert torch.equal(gt[k].cpu(), transforms.ToTensor()(gt_ref))
+            seen += 1
+    assert seen == len(dm.test_images_filenames) == 6
+    assert len(dm.train_dataset) + len(dm.val_dataset) == 6
