@@ -404,6 +404,13 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
     for i in range(warm):
         step(i)
     barrier()
+    if getattr(args, "profile_steps", 0) > 0:      # the steps a profiler looks at (plain order on one stream), nothing else
+        torch.cuda.profiler.start()
+        for i in range(args.profile_steps):
+            step(i)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return {"profiled_steps": args.profile_steps, "launches_per_step": launches_per_step}
     timed(warm, True)                        # warm the lanes too
     ms_serial = timed(steps, False)
     sampler = ClockSampler(_phys_gpu(rt["local_rank"]))
@@ -573,6 +580,8 @@ def main():
     ap.add_argument("--e2e-chunks", type=int, default=None, help="pieces of the batch in flight in the host-buffer call")
     ap.add_argument("--inflight", type=int, default=2, help="batches in flight: steps alternate between this many streams (1|2)")
     ap.add_argument("--graph", type=int, default=1, help="1: replay each step's ssad_generate call from a CUDA graph")
+    ap.add_argument("--profile-steps", type=int, default=0, help="run this many steps of --config between cudaProfilerStart/Stop "
+                    "and exit (for `ncu --profile-from-start off`: tools/traffic.py)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -603,6 +612,9 @@ def main():
     steps = args.steps or (30 if args.config == 4 else 300)
     e2e_steps = args.e2e_steps if args.e2e_steps is not None else (4 if args.config == 4 else 20)
     head = run_config(args.config, args, rt, steps, e2e_steps, args.verify, batch=args.batch)
+    if "profiled_steps" in head:
+        print(json.dumps(head))
+        return
     per_config = {}
     want_pc = args.per_config if args.per_config is not None else int(world == 1 and args.config == 4 and args.batch is None)
     if want_pc:

@@ -303,8 +303,9 @@ __device__ inline void line_segment(uint32_t* cov, int pitch, const LineBox& B, 
         }
     }
 }
-// ImagingDrawWideLine: the polygon of one wide segment, in box coordinates; false: zero-length segment (a single point)
-__device__ inline bool wide_line_polygon(Polygon& P, const LineBox& B, int x0, int y0, int x1, int y1, int width) {
+// ImagingDrawWideLine: the polygon of one wide segment, in IMAGE coordinates (the filler's float32 edge arithmetic is
+// not translation invariant: x0 + (y - y0) dx rounds differently after a shift); false: zero-length segment (a point)
+__device__ inline bool wide_line_polygon(Polygon& P, int H, int x0, int y0, int x1, int y1, int width) {
     const int dx = x1 - x0, dy = y1 - y0;
     if (dx == 0 && dy == 0) return false;
     // hypot(dx, dy): dx^2 + dy^2 is an exact integer, its correctly rounded root is what a correctly rounded hypot returns
@@ -313,16 +314,16 @@ __device__ inline bool wide_line_polygon(Polygon& P, const LineBox& B, int x0, i
     const double ratio_max = draw_round_up(small) / big, ratio_min = draw_round_down(small) / big;
     const int dxmin = draw_round_down(ratio_min * dy), dxmax = draw_round_down(ratio_max * dy);
     const int dymin = draw_round_up(ratio_min * dx), dymax = draw_round_up(ratio_max * dx);
-    int16_t v[4][2] = {{(int16_t)(x0 - dxmin - B.x0), (int16_t)(y0 + dymax - B.y0)}, {(int16_t)(x1 - dxmin - B.x0), (int16_t)(y1 + dymax - B.y0)},
-                       {(int16_t)(x1 + dxmax - B.x0), (int16_t)(y1 - dymin - B.y0)}, {(int16_t)(x0 + dxmax - B.x0), (int16_t)(y0 - dymin - B.y0)}};
-    polygon_setup(P, v, 4, B.h);
+    int16_t v[4][2] = {{(int16_t)(x0 - dxmin), (int16_t)(y0 + dymax)}, {(int16_t)(x1 - dxmin), (int16_t)(y1 + dymax)},
+                       {(int16_t)(x1 + dxmax), (int16_t)(y1 - dymin)}, {(int16_t)(x0 + dxmax), (int16_t)(y0 - dymin)}};
+    polygon_setup(P, v, 4, H);
     return true;
 }
 // The whole poly-line into `cov` (B.h rows of `pitch` words, zeroed by the caller, visible to every thread: a barrier
 // lies between the zeroing and this call); `quads`: shared scratch for n - 1 polygons (width > 1).  Every thread of the
 // CTA calls it; the caller synchronises before reading `cov`.
-__device__ inline void line_rasterize(const int16_t* __restrict__ xy, int n, int width, const LineBox& B, uint32_t* cov, int pitch,
-                                      Polygon* quads, int tid, int nt) {
+__device__ inline void line_rasterize(const int16_t* __restrict__ xy, int n, int width, int W, int H, const LineBox& B, uint32_t* cov,
+                                      int pitch, Polygon* quads, int tid, int nt) {
     if (B.w <= 0 || n < 2) return;
     const int nseg = n - 1;
     if (width <= 1) {
@@ -331,23 +332,30 @@ __device__ inline void line_rasterize(const int16_t* __restrict__ xy, int n, int
         return;
     }
     for (int s = tid; s < nseg; s += nt) {
-        if (!wide_line_polygon(quads[s], B, xy[2 * s], xy[2 * s + 1], xy[2 * s + 2], xy[2 * s + 3], width)) {
+        if (!wide_line_polygon(quads[s], H, xy[2 * s], xy[2 * s + 1], xy[2 * s + 2], xy[2 * s + 3], width)) {
             quads[s].n = -1;
             line_set(cov, pitch, B, xy[2 * s], xy[2 * s + 1]);
         }
     }
     __syncthreads();
+    const int iw = (W + 31) >> 5;                                                    // words of an image row (W <= 1024)
     for (int item = tid; item < nseg * B.h; item += nt) {
-        const int s = item / B.h, v = item - s * B.h;
+        const int s = item / B.h, v = item - s * B.h, y = B.y0 + v;
         const Polygon& P = quads[s];
         if (P.n < 0) continue;
-        bool touches = v >= P.ymin && v <= P.ymax;
-        for (int i = 0; i < P.n && !touches; ++i) touches = P.e[i].ymin == P.e[i].ymax && P.e[i].ymin == v;
+        bool touches = y >= P.ymin && y <= P.ymax;
+        for (int i = 0; i < P.n && !touches; ++i) touches = P.e[i].ymin == P.e[i].ymax && P.e[i].ymin == y;
         if (!touches) continue;
-        uint32_t row[32];                                                            // W <= 1024
-        for (int j = 0; j < pitch; ++j) row[j] = 0u;
-        polygon_fill_row(P, v, B.w, row);
-        for (int j = 0; j < pitch; ++j) if (row[j]) atomicOr(&cov[(size_t)v * pitch + j], row[j]);
+        uint32_t row[33];                                                            // the image row, then into the box
+        for (int j = 0; j <= iw; ++j) row[j] = 0u;
+        polygon_fill_row(P, y, W, row);
+        const int w0 = B.x0 >> 5, sh = B.x0 & 31;
+        for (int j = 0; j < pitch; ++j) {
+            uint32_t bits = __funnelshift_r(row[min(w0 + j, iw)], row[min(w0 + j + 1, iw)], sh);
+            const int left = B.w - 32 * j;                                           // columns of the box in this word
+            if (left < 32) bits &= (1u << left) - 1u;
+            if (bits) atomicOr(&cov[(size_t)v * pitch + j], bits);
+        }
     }
 }
 

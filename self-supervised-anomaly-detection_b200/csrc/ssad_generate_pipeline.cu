@@ -437,7 +437,7 @@ plan_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ 
     } else if (y == 3 && npaste) {
         for (int i = tid; i < bh * pitchw; i += NT) cov[i] = 0;
         __syncthreads();
-        line_rasterize(lxy, ln, d.line_width, LB, cov, pitchw, quads, tid, NT);
+        line_rasterize(lxy, ln, d.line_width, W, H, LB, cov, pitchw, quads, tid, NT);
     }
     if (tid == 0) {
         // work lists: pass 1 runs the ops ahead of Contrast (and may have nothing to do at all), pass 2 the rest

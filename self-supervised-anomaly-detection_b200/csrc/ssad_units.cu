@@ -168,7 +168,7 @@ line_mask_kernel(const int16_t* __restrict__ xy, const uint8_t* __restrict__ npt
     for (int k = tid; k < H * ((W + 31) / 32); k += 256) cov[k] = 0u;
     __syncthreads();
     const int pitch = (B.w + 31) / 32;
-    line_rasterize(p, n, width, B, cov, max(pitch, 1), quads, tid, 256);
+    line_rasterize(p, n, width, W, H, B, cov, max(pitch, 1), quads, tid, 256);
     __syncthreads();
     uint8_t* o = out + (size_t)i * W * H;
     for (int k = tid; k < W * H; k += 256) {
