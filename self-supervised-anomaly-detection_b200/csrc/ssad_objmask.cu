@@ -314,8 +314,9 @@ static_assert(SM_H * SM_W <= SV_H * SG_W, "|gradient|^2 reuses the axis-0 buffer
 
 struct C32K {
     float w[7];              // taps 0..6 (centre last) of the symmetric 13-tap kernel
-    float tl, th;            // thresholds in grey levels (255 low, 255 high)
     float ec[2], em[2];      // error bounds of a gradient component / of |gradient|: [interior, border]
+    float lo_no[2], lo_yes[2], hi_no[2], hi_yes[2];   // 255 low -+ em, 255 high -+ em (lower ones clamped at 0)
+    float lo_no2[2];         // lo_no^2, a hair below (the squares' own rounding)
     int sub_cap;             // <= SUB_CAP
     unsigned pix_cap;        // entries of the undecided-pixel list
 };
@@ -324,6 +325,8 @@ struct C32Smem {
     float V[SV_H * SG_W];    // axis-0 pass; reused for |gradient|^2
     float ra[SV_H], rb[SS_W];   // 1 / bleed-over along the rows / the columns (border tiles)
     uint32_t cand[SC_H * (SC_W / 32)];   // pixels whose |gradient| may reach the low threshold, one word per 32 pixels of a row
+    uint32_t nword;                      // words with a candidate ...
+    uint16_t words[SC_H * (SC_W / 32)];  // ... and which
     uint32_t sub_cnt[4];
     uint16_t sub_list[4][SUB_CAP];
 };
@@ -357,6 +360,7 @@ __device__ __forceinline__ om_f32x2 om_pack2(float lo, float hi) {
     asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
     return r;
 }
+__device__ __forceinline__ void om_unpack2(om_f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
 __device__ __forceinline__ om_f32x2 om_fma2(om_f32x2 a, om_f32x2 b, om_f32x2 c) {
     om_f32x2 r;
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
@@ -393,6 +397,7 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     const bool border = (x0 - 8 < 6) || (y0 - 8 < 6) || (x0 + SC_W + 8 > W - 6) || (y0 + SC_H + 8 > H - 6);
 
     if (tid < 4) sm.sub_cnt[tid] = 0u;
+    if (tid == 4) sm.nword = 0u;
     if (tid < SC_H * (SC_W / 32)) sm.cand[tid] = 0u;
     static_assert(SC_H * (SC_W / 32) <= SC_NT, "one thread per candidate word");
     if (border) {
@@ -459,12 +464,15 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     }
     __syncthreads();
 
-    // ---- Gaussian along axis 0: a thread slides down 12 rows of a column pair (the last segment has 8)
+    // ---- Gaussian along axis 0: a thread slides down 12 rows of a column pair (the last segment has 8).  The result is
+    // stored with the rows interleaved in pairs -- V2[r / 2][c] = (V[r][c], V[r + 1][c]) -- so that the axis-1 pass
+    // reads ready-made packed pairs (two rows per FFMA2)
+    om_f32x2 wp[7];
+    #pragma unroll
+    for (int j = 0; j < 7; ++j) wp[j] = om_pack2(K.w[j], K.w[j]);
     {
-        om_f32x2 wp[7];
-        #pragma unroll
-        for (int j = 0; j < 7; ++j) wp[j] = om_pack2(K.w[j], K.w[j]);
         constexpr int NP = SG_W / 2, SEG = 12, NSEG = (SV_H + SEG - 1) / SEG;
+        static_assert(SEG % 2 == 0 && SV_H % 2 == 0, "row pairs");
         for (int t = tid; t < NP * NSEG; t += SC_NT) {
             const int seg = t / NP, pr = t - seg * NP;
             const int r0 = seg * SEG, nrow = min(SEG, SV_H - r0);
@@ -473,41 +481,43 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
             #pragma unroll
             for (int k = 0; k < SEG + 12; ++k) v[k] = (k < nrow + 12) ? *reinterpret_cast<const om_f32x2*>(g + k * SG_W) : 0ull;
             #pragma unroll
-            for (int o = 0; o < SEG; ++o)
-                if (o < nrow) *reinterpret_cast<om_f32x2*>(&sm.V[(r0 + o) * SG_W + 2 * pr]) = om_sym13(v + o, wp);
+            for (int o = 0; o < SEG; o += 2) {
+                if (o < nrow) {
+                    float a0, a1, b0, b1;
+                    om_unpack2(om_sym13(v + o, wp), a0, a1);          // row r0 + o:     columns 2 pr, 2 pr + 1
+                    om_unpack2(om_sym13(v + o + 1, wp), b0, b1);      // row r0 + o + 1
+                    *reinterpret_cast<float4*>(&sm.V[(((r0 + o) >> 1) * SG_W + 2 * pr) * 2]) = make_float4(a0, b0, a1, b1);
+                }
+            }
         }
     }
     __syncthreads();
 
-    // ---- Gaussian along axis 1 (/ bleed-over in border tiles): a thread takes four columns of a row; lanes walk along
-    // the row, so every 128-bit shared-memory access of a warp is a run of consecutive chunks (no bank conflicts)
+    // ---- Gaussian along axis 1 (/ bleed-over in border tiles): a thread takes two columns of a row pair; lanes walk
+    // along the row, so every 128-bit shared-memory access of a warp is a run of consecutive chunks (no bank conflicts)
     float* const S = sm.G;
     {
-        constexpr int NG = SS_W / 4;                     // 33 groups: S columns 0 .. 131
-        for (int t = tid; t < SV_H * NG; t += SC_NT) {
-            const int r = t / NG, g = t - r * NG;
-            // S[r][c] = sum_k w[k] V[r][c + k]: the chunks 4g .. 4g+15 of V
-            const float4* vp = reinterpret_cast<const float4*>(&sm.V[r * SG_W + 4 * g]);
-            float v[16];
+        constexpr int NQ = SS_W / 2, NRP = SV_H / 2;     // 66 column pairs (S columns 0 .. 131), 34 row pairs
+        for (int t = tid; t < NRP * NQ; t += SC_NT) {
+            const int rp = t / NQ, q = t - rp * NQ;
+            // S[r][c] = sum_k w[k] V[r][c + k], c = 2q, 2q + 1: the pairs V2[rp][2q .. 2q + 13]
+            const float4* vp = reinterpret_cast<const float4*>(&sm.V[(rp * SG_W + 2 * q) * 2]);
+            om_f32x2 v[14];
             #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float4 q = vp[k];
-                v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
+            for (int k = 0; k < 7; ++k) {
+                const float4 f = vp[k];
+                v[2 * k] = om_pack2(f.x, f.y); v[2 * k + 1] = om_pack2(f.z, f.w);
             }
-            float o[4];
-            #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float a = v[6 + j] * K.w[6];
-                #pragma unroll
-                for (int i = 0; i < 6; ++i) a = fmaf(v[j + i] + v[12 + j - i], K.w[i], a);
-                o[j] = a;
-            }
+            float s00, s10, s01, s11;                    // s<row><column>
+            om_unpack2(om_sym13(v, wp), s00, s10);
+            om_unpack2(om_sym13(v + 1, wp), s01, s11);
+            const int r = 2 * rp, c = 2 * q;
             if (border) {
-                const float ra = sm.ra[r];
-                #pragma unroll
-                for (int j = 0; j < 4; ++j) o[j] *= ra * sm.rb[4 * g + j];
+                const float ra0 = sm.ra[r], ra1 = sm.ra[r + 1], cb0 = sm.rb[c], cb1 = sm.rb[c + 1];
+                s00 *= ra0 * cb0; s01 *= ra0 * cb1; s10 *= ra1 * cb0; s11 *= ra1 * cb1;
             }
-            *reinterpret_cast<float4*>(&S[r * SS_W + 4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<float2*>(&S[r * SS_W + c]) = make_float2(s00, s01);
+            *reinterpret_cast<float2*>(&S[(r + 1) * SS_W + c]) = make_float2(s10, s11);
         }
     }
     __syncthreads();
@@ -531,9 +541,9 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     // ---- Sobel, |gradient|^2 for the tile and a 1-pixel halo: a thread takes four pixels of a row; the pixels that may
     // reach the low threshold (a few per cent of an image) are marked in the candidate words
     float* const M2 = sm.V;          // M2[r][c] <-> pixel (y0 - 1 + r, x0 - 1 + c) from S rows r .. r+2, columns c .. c+2
-    const float Ec = K.ec[border ? 1 : 0], Em = K.em[border ? 1 : 0];
-    const float lo_no = fmaxf(K.tl - Em, 0.0f), lo_yes = K.tl + Em, hi_no = fmaxf(K.th - Em, 0.0f), hi_yes = K.th + Em;
-    const float lo_no2 = lo_no * lo_no * 0.999999f;            // (the squares' own rounding)
+    const int bc = border ? 1 : 0;
+    const float Ec = K.ec[bc], Em = K.em[bc];
+    const float lo_no = K.lo_no[bc], lo_yes = K.lo_yes[bc], hi_no = K.hi_no[bc], hi_yes = K.hi_yes[bc], lo_no2 = K.lo_no2[bc];
     {
         constexpr int NG = SM_W / 4;
         for (int t = tid; t < SM_H * NG; t += SC_NT) {
@@ -574,21 +584,27 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     }
     __syncthreads();
 
-    // ---- words without a candidate: both planes are zero there (one thread per word)
-    if (tid < SC_H * (SC_W / 32) && sm.cand[tid] == 0u) {
-        const int i = tid >> 2, xw = (x0 >> 5) + (tid & 3), y = y0 + i;
-        if (y < H && xw < nw) {
-            low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
-            high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
+    // ---- words without a candidate: both planes are zero there (one thread per word); the others are listed
+    if (tid < SC_H * (SC_W / 32)) {
+        if (sm.cand[tid] == 0u) {
+            const int i = tid >> 2, xw = (x0 >> 5) + (tid & 3), y = y0 + i;
+            if (y < H && xw < nw) {
+                low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
+                high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
+            }
+        } else {
+            sm.words[atomicAdd(&sm.nword, 1u)] = (uint16_t)tid;
         }
     }
+    __syncthreads();
     // ---- thresholds and non-maximum suppression of the candidates, decided in float32 where the error bounds allow; a
     // warp owns 32 pixels of a row and writes their word of the two planes
     {
         const int lane = tid & 31, warp = tid >> 5;
-        for (int task = warp; task < SC_H * (SC_W / 32); task += SC_NT / 32) {
+        const int nword = (int)sm.nword;
+        for (int k = warp; k < nword; k += SC_NT / 32) {
+            const int task = sm.words[k];
             const uint32_t cw = sm.cand[task];
-            if (cw == 0u) continue;                          // (uniform over the warp)
             const int i = task >> 2, q = task & 3;
             const int j = q * 32 + lane;
             const int y = y0 + i;
@@ -1133,9 +1149,16 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
     K.low = consts->low; K.high = consts->high; K.eps = consts->eps;
     ssad::C32K FK;
     for (int i = 0; i < 7; ++i) FK.w[i] = (float)consts->gauss_w[i];
-    FK.tl = (float)(consts->low * 255.0); FK.th = (float)(consts->high * 255.0);
     FK.ec[0] = 0.003f * g_margin_scale; FK.em[0] = 0.0045f * g_margin_scale;
     FK.ec[1] = 0.0125f * g_margin_scale; FK.em[1] = 0.018f * g_margin_scale;
+    for (int c = 0; c < 2; ++c) {
+        const float tl = (float)(consts->low * 255.0), th = (float)(consts->high * 255.0);
+        FK.lo_no[c] = tl - FK.em[c] > 0.0f ? tl - FK.em[c] : 0.0f;
+        FK.lo_yes[c] = tl + FK.em[c];
+        FK.hi_no[c] = th - FK.em[c] > 0.0f ? th - FK.em[c] : 0.0f;
+        FK.hi_yes[c] = th + FK.em[c];
+        FK.lo_no2[c] = FK.lo_no[c] * FK.lo_no[c] * 0.999999f;
+    }
     FK.sub_cap = g_sub_cap;
     {
         const unsigned long long cap = (unsigned long long)batch * (unsigned)g_pix_per_image;
