@@ -59,7 +59,7 @@ struct alignas(16) Hdr {
     int32_t cx0, cy0;            // crop window
     float fs;                    // Saturation factor of the pass's program
     int32_t si;                  // source image (the record's src_index, or the image itself)
-    int32_t pad;
+    uint32_t rows;               // rows [lo, hi) of the working image the pastes touch: lo | hi << 16 (0: none)
 };
 enum { HF_WARP = 1, HF_PRE = 2, HF_DEFECT = 4, HF_LUMA = 8 };
 
@@ -502,7 +502,11 @@ lists_v7_kernel(const __grid_constant__ Geo7 g, const SsadImageParams* __restric
         float fs = 1.0f;                 // factor of the Saturation inside the pass's program, if any
         const int i0 = (ps == 0) ? 0 : (D.s_in_pre ? D.cpos : 0), i1 = (ps == 0) ? max(D.cpos, 0) : D.nops;
         for (int i = i0; i < i1; ++i) if (D.ops[i] == 2) fs = D.fac[i];
-        h.fs = fs; h.si = g.src_indexed ? (int32_t)p->src_index : b; h.pad = 0;
+        h.fs = fs; h.si = g.src_indexed ? (int32_t)p->src_index : b;
+        // rows any paste touches: only those slabs of an un-warped defect image go through the x buffer
+        int lo = g.H, hi = 0;
+        for (int k = 0; k < D.npaste; ++k) { lo = min(lo, max(D.paste[k][1], 0)); hi = max(hi, min(D.paste[k][1] + D.bh, g.H)); }
+        h.rows = (lo < hi) ? ((uint32_t)lo | ((uint32_t)hi << 16)) : 0u;
         hdr[(size_t)ps * g.batch + rank] = h;
     }
 }
@@ -528,8 +532,9 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     ImgState* const S = state + b;
     const bool warped = (flags & HF_WARP) != 0, defect = (flags & HF_DEFECT) != 0, need_luma = (flags & HF_LUMA) != 0;
     const bool store_pre = (flags & HF_PRE) != 0;                    // pass 2 starts from pre(x)
-    const bool store_raw = defect && !store_pre && !warped;          // the pastes are written into x
     const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
+    const bool pasted = r0 < (int)((uint32_t)h1.w >> 16) && r1 > (int)((uint32_t)h1.w & 0xFFFFu);     // a paste touches this slab
+    const bool store_raw = defect && !store_pre && !warped && pasted;      // the pastes are written into x
     const int nunits = (r1 - r0) * g.upr;
     const uint8_t* const sbase = src + (size_t)h1.z * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;
     const int spitch = (int)d.src_pitch;
@@ -994,8 +999,10 @@ pass2_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     const int b = h0.x, kind = h0.y;
     if (b < 0) return;
     const int H = g.H, W = g.W, npix = H * W;
-    const bool stored = (h0.z & (HF_WARP | HF_PRE | HF_DEFECT)) != 0;              // pass 2 starts from the x buffer
     const int r0 = slab * g.rows_slab, r1 = min(H, r0 + g.rows_slab);
+    const bool pasted = r0 < (int)((uint32_t)h1.w >> 16) && r1 > (int)((uint32_t)h1.w & 0xFFFFu);
+    // pass 2 starts from the x buffer where pass 1 left something there: warped x, pre(x), or a slab with pastes
+    const bool stored = (h0.z & (HF_WARP | HF_PRE)) != 0 || ((h0.z & HF_DEFECT) != 0 && pasted);
     const int nunits = (r1 - r0) * g.upr;
     const uint8_t* const in2 = stored ? xbuf + (size_t)b * npix * 3
                                       : src + (size_t)h1.z * d.src_stride + (size_t)h1.x * d.src_pitch + (size_t)h0.w * 3;

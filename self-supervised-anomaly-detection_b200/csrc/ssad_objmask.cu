@@ -301,9 +301,16 @@ canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* 
 // difference is within  2 Em den + Ec (n12 + 2 n11 + m)  (+ 1e-3 second order + 1e-6 (lhs + rhs) evaluation rounding)
 // of the true one, so it is certain when it exceeds  T = 2 Em den + 2 Ec (n11 + n12 + m) + 1e-3 + 1e-6 (lhs + rhs).
 #ifndef SSAD_C32_NT
-#define SSAD_C32_NT 512
+#define SSAD_C32_NT 256
 #endif
-constexpr int SC_W = 128, SC_H = 64, SC_NT = SSAD_C32_NT;
+#ifndef SSAD_C32_H
+#define SSAD_C32_H 32
+#endif
+#ifndef SSAD_C32_MINB
+#define SSAD_C32_MINB 4
+#endif
+constexpr int SC_W = 128, SC_H = SSAD_C32_H, SC_NT = SSAD_C32_NT;     // SC_H: a multiple of the 32-row dense tiles
+static_assert(SC_H % 32 == 0, "whole 64x32 tiles");
 constexpr int SG_W = SC_W + 16, SG_H = SC_H + 16;       // L: rows y0-8 .. y0+SC_H+7, columns x0-8 .. x0+SC_W+7
 constexpr int SV_H = SC_H + 4;                           // V (axis-0 pass): rows y0-2 .. y0+SC_H+1, the columns of L
 constexpr int SS_W = SC_W + 4;                           // S (smoothed): rows of V, columns x0-2 .. x0+SC_W+1
@@ -327,8 +334,8 @@ struct C32Smem {
     uint32_t cand[SC_H * (SC_W / 32)];   // pixels whose |gradient| may reach the low threshold, one word per 32 pixels of a row
     uint32_t nword;                      // words with a candidate ...
     uint16_t words[SC_H * (SC_W / 32)];  // ... and which
-    uint32_t sub_cnt[4];
-    uint16_t sub_list[4][SUB_CAP];
+    uint32_t sub_cnt[SC_H / 16];
+    uint16_t sub_list[SC_H / 16][SUB_CAP];
 };
 static_assert(SV_H * SS_W <= SG_H * SG_W, "S reuses the L buffer");
 
@@ -384,7 +391,7 @@ __device__ __forceinline__ om_f32x2 om_sym13(const om_f32x2* v, const om_f32x2 (
     return t;
 }
 
-__global__ void __launch_bounds__(SC_NT, 2)
+__global__ void __launch_bounds__(SC_NT, SSAD_C32_MINB)
 canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __restrict__ src, long long src_pitch,
                long long src_stride, uint32_t* __restrict__ low_plane, uint32_t* __restrict__ high_plane, int nw,
                long long plane_stride, uint2* __restrict__ pix_list, uint32_t* __restrict__ pix_count,
@@ -396,8 +403,8 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     const uint8_t* img = src + (size_t)b * src_stride;
     const bool border = (x0 - 8 < 6) || (y0 - 8 < 6) || (x0 + SC_W + 8 > W - 6) || (y0 + SC_H + 8 > H - 6);
 
-    if (tid < 4) sm.sub_cnt[tid] = 0u;
-    if (tid == 4) sm.nword = 0u;
+    if (tid < SC_H / 16) sm.sub_cnt[tid] = 0u;
+    if (tid == 32) sm.nword = 0u;
     if (tid < SC_H * (SC_W / 32)) sm.cand[tid] = 0u;
     static_assert(SC_H * (SC_W / 32) <= SC_NT, "one thread per candidate word");
     if (border) {
@@ -557,27 +564,48 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
                 const float2 c = *reinterpret_cast<const float2*>(&S[(r + k) * SS_W + 4 * g + 4]);
                 s[k][0] = a.x; s[k][1] = a.y; s[k][2] = a.z; s[k][3] = a.w; s[k][4] = c.x; s[k][5] = c.y;
             }
-            float dc[6], e[3][4], o[4];
-            #pragma unroll
-            for (int c = 0; c < 6; ++c) dc[c] = s[2][c] - s[0][c];
+            // packed pairs where the operands are natural register pairs (columns 2p, 2p + 1)
+            om_f32x2 sp[3][3];
             #pragma unroll
             for (int k = 0; k < 3; ++k)
                 #pragma unroll
-                for (int j = 0; j < 4; ++j) e[k][j] = s[k][j + 2] - s[k][j];
+                for (int p2 = 0; p2 < 3; ++p2) sp[k][p2] = om_pack2(s[k][2 * p2], s[k][2 * p2 + 1]);
+            const om_f32x2 NEG1 = om_pack2(-1.0f, -1.0f), TWO = om_pack2(2.0f, 2.0f);
+            float dc[6], o[4];
             #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float is = fmaf(2.0f, dc[j + 1], dc[j]) + dc[j + 2];
-                const float js = fmaf(2.0f, e[1][j], e[0][j]) + e[2][j];
-                o[j] = fmaf(is, is, js * js);
+            for (int p2 = 0; p2 < 3; ++p2) om_unpack2(om_fma2(sp[0][p2], NEG1, sp[2][p2]), dc[2 * p2], dc[2 * p2 + 1]);   // down - up
+            om_f32x2 js2[2];
+            #pragma unroll
+            for (int p2 = 0; p2 < 2; ++p2) {                   // e[k] = right - left for the pixel pairs (0,1), (2,3)
+                const om_f32x2 e0 = om_fma2(sp[0][p2], NEG1, sp[0][p2 + 1]), e1 = om_fma2(sp[1][p2], NEG1, sp[1][p2 + 1]);
+                const om_f32x2 e2 = om_fma2(sp[2][p2], NEG1, sp[2][p2 + 1]);
+                js2[p2] = om_add2(om_fma2(TWO, e1, e0), e2);
+            }
+            #pragma unroll
+            for (int p2 = 0; p2 < 2; ++p2) {
+                const float is0 = fmaf(2.0f, dc[2 * p2 + 1], dc[2 * p2]) + dc[2 * p2 + 2];
+                const float is1 = fmaf(2.0f, dc[2 * p2 + 2], dc[2 * p2 + 1]) + dc[2 * p2 + 3];
+                const om_f32x2 is2 = om_pack2(is0, is1);
+                om_unpack2(om_fma2(is2, is2, om_mul2(js2[p2], js2[p2])), o[2 * p2], o[2 * p2 + 1]);
             }
             *reinterpret_cast<float4*>(&M2[r * SM_W + 4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
             if (fmaxf(fmaxf(o[0], o[1]), fmaxf(o[2], o[3])) >= lo_no2 && r >= 1 && r <= SC_H) {
-                const int i = r - 1, y = y0 + i;
-                #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int j = 4 * g + k - 1, x = x0 + j;       // eroded_mask: the 1-pixel border of the image never qualifies
-                    if (o[k] >= lo_no2 && j >= 0 && j < SC_W && y >= 1 && y <= H - 2 && x >= 1 && x <= W - 2)
-                        atomicOr(&sm.cand[i * (SC_W / 32) + (j >> 5)], 1u << (j & 31));
+                // the four pixels j = 4g - 1 .. 4g + 2 of tile row i as bits of one 64-bit window (they may straddle a word)
+                const int i = r - 1, y = y0 + i, j0 = 4 * g - 1;
+                uint32_t nib = (o[0] >= lo_no2 ? 1u : 0u) | (o[1] >= lo_no2 ? 2u : 0u) | (o[2] >= lo_no2 ? 4u : 0u) | (o[3] >= lo_no2 ? 8u : 0u);
+                if (j0 < 0) nib &= ~1u;                         // column -1 is halo
+                if (j0 + 3 >= SC_W) nib &= (1u << (SC_W - j0)) - 1u;     // columns >= SC_W are halo
+                if (border) {                                   // eroded_mask: the 1-pixel border of the image never qualifies
+                    if (y < 1 || y > H - 2) nib = 0u;
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) { const int x = x0 + j0 + k; if (x < 1 || x > W - 2) nib &= ~(1u << k); }
+                }
+                if (nib) {
+                    const int jb = max(j0, 0);                   // first valid column of the window
+                    const uint32_t bits = (j0 < 0) ? (nib >> 1) : nib;
+                    const int w0 = jb >> 5, sh = jb & 31;
+                    atomicOr(&sm.cand[i * (SC_W / 32) + w0], bits << sh);
+                    if (sh > 28 && (bits >> (32 - sh))) atomicOr(&sm.cand[i * (SC_W / 32) + w0 + 1], bits >> (32 - sh));
                 }
             }
         }
@@ -610,7 +638,7 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
             const int y = y0 + i;
             bool lo = false, hi = false, undecided = false;
             if ((cw >> lane) & 1u) {
-                const float m = __fsqrt_rn(M2[(i + 1) * SM_W + (j + 1)]);
+                const float m = __fsqrt_rn(M2[(i + 1) * SM_W + (j + 1)]);       // (the thresholds want the correctly rounded root)
                 if (m >= lo_no) {
                     undecided = m < lo_yes;
                     // the gradient again (S rows i+1 .. i+3 around row i+2 <-> y, columns j+1 .. j+3 around j+2 <-> x)
@@ -668,10 +696,9 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     // float64 kernel when there are too many (or the list is full)
     {
         const int warp = tid >> 5, lane = tid & 31;
-        if (warp < 4) {
-            const int sub = warp;
+        for (int sub = warp; sub < SC_H / 16; sub += SC_NT / 32) {
             const uint32_t n = sm.sub_cnt[sub];
-            const int tx = 2 * blockIdx.x + (sub & 1), ty = 2 * blockIdx.y + (sub >> 1);
+            const int tx = 2 * blockIdx.x + (sub & 1), ty = (SC_H / 32) * blockIdx.y + (sub >> 1);
             if (n > 0 && tx < ntx && ty < nty) {
                 bool dense = n > (uint32_t)K.sub_cap;
                 uint32_t base = 0;
