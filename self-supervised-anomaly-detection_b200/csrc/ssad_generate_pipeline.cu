@@ -120,7 +120,11 @@ constexpr int UPT = SSAD_V7_UPT_FAST;
 #define SSAD_V7_P2_MINB 4
 #endif
 
+#ifdef SSAD_V7_PREFETCH_L1
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+#else
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#endif
 
 // sum of Convert.c's L over the 8 pixels of a unit: two 16x8-bit dot products per pixel, straight from the words
 __device__ __forceinline__ uint32_t luma_sum_fast(const uint32_t (&w)[6]) {
@@ -625,6 +629,113 @@ pass1_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__
     if (tid < 7 && tot != 0) atomicAdd(&S->acc[tid], tot);
 }
 
+// ---- 8-pixel units in the canvas kernel (polygon / poly-line paste)
+// Convert.c L of the 8 pixels of a unit
+__device__ __forceinline__ void luma8(const uint32_t (&w)[6], uint32_t (&L)[8]) {
+    constexpr uint32_t kRG = (38470u << 16) | 19595u, kB0 = 7471u;          // pixel at bytes 0,1,2 of a word
+    constexpr uint32_t k0R = (19595u << 16), kGB = (7471u << 16) | 38470u;  // pixel at bytes 1,2,3 of a word
+    #pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const uint32_t w0 = w[3 * q], w1 = w[3 * q + 1], w2 = w[3 * q + 2];
+        const uint32_t p1 = __byte_perm(w0, w1, 0x0543), p2 = __byte_perm(w1, w2, 0x0432);
+        L[4 * q + 0] = dp2a_hi(kB0, w0, dp2a_lo(kRG, w0, 0x8000u)) >> 16;
+        L[4 * q + 1] = dp2a_hi(kB0, p1, dp2a_lo(kRG, p1, 0x8000u)) >> 16;
+        L[4 * q + 2] = dp2a_hi(kB0, p2, dp2a_lo(kRG, p2, 0x8000u)) >> 16;
+        L[4 * q + 3] = dp2a_hi(kGB, w2, dp2a_lo(k0R, w2, 0x8000u)) >> 16;
+    }
+}
+// 8 coverage bits of canvas row `crow` for canvas x = u0 .. u0 + 7 (u0 may be negative; bits beyond the row are zero)
+__device__ __forceinline__ uint32_t cov_bits8(const uint32_t* __restrict__ crow, int u0, int pitch_words) {
+    const int lo = max(u0, 0);
+    const int wi = lo >> 5;
+    const uint32_t a = wi < pitch_words ? crow[wi] : 0u;
+    const uint32_t b = (wi + 1 < pitch_words) ? crow[wi + 1] : 0u;
+    const uint32_t bits = __funnelshift_r(a, b, lo & 31) & 0xFFu;      // canvas x = lo .. lo + 7
+    return (u0 < 0) ? ((u0 > -8) ? (bits << (-u0)) & 0xFFu : 0u) : bits;   // pixel p of the unit <-> canvas x = u0 + p
+}
+
+// One paste of a polygon patch (or the flat colour of a poly-line) into the x buffer, an 8-pixel unit at a time:
+// coverage bits -> byte masks, the cut / flat colour as 24 bytes, the old pixels as 24 bytes, a byte-wise select, and
+// the change of the sum of L that Contrast will see (through the `pre` program of the image, kind LK).
+template <int LK>
+__device__ __forceinline__ uint32_t polygon_units(int total, const uint16_t* row_cu0, const uint32_t* row_pre, int nrows, int my_lo,
+                                                  const uint32_t* __restrict__ cov, int pitchw, int pl, int pt, int W,
+                                                  uint8_t* xb, const Donor& dn, bool flat, const uint32_t (&fw)[3], bool cut_sim,
+                                                  uint32_t simtab_addr, const uint32_t (*bmask)[3], bool want_l, const ProgRegs& R, int tid) {
+    constexpr bool SP = LK >= LK_SAT_UC;          // Saturation precedes Contrast: the x buffer holds pre(x)
+    uint32_t dl = 0;
+    for (int t = tid; t < total; t += NT) {
+        int lo = 0, hi = max(nrows - 1, 0);       // the row of item t
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if ((int)row_pre[mid] <= t) lo = mid; else hi = mid - 1;
+        }
+        const int v = my_lo + lo, cu = (int)row_cu0[lo] + t - (int)row_pre[lo];
+        const int X0 = cu * 8, u0 = X0 - pl;
+        const uint32_t m8 = cov_bits8(cov + (size_t)v * pitchw, u0, pitchw);
+        if (!m8) continue;
+        uint8_t* const q = xb + ((size_t)(pt + v) * W + X0) * 3;
+        uint32_t O[6], N[6];
+        {
+            const uint2* qo = reinterpret_cast<const uint2*>(q);
+            const uint2 a = qo[0], b = qo[1], c = qo[2];
+            O[0] = a.x; O[1] = a.y; O[2] = b.x; O[3] = b.y; O[4] = c.x; O[5] = c.y;
+        }
+        if (flat) {
+            N[0] = fw[0]; N[1] = fw[1]; N[2] = fw[2]; N[3] = fw[0]; N[4] = fw[1]; N[5] = fw[2];
+        } else {
+            if (u0 >= 0 && u0 + 8 <= dn.u_hi && v + 1 < dn.v_hi) {  // the whole unit lies inside the cut (and a row follows:
+                                                                    // the aligned 32-byte read may run 8 bytes past the unit)
+                const uint8_t* c = dn.base + (size_t)v * dn.pitch + 3 * u0;
+                const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(c) & 7u);
+                Raw r;
+                ld_raw(c - mis, mis != 0, true, r);
+                raw_to_words(r, mis, N);
+            } else {                                               // patch edge: PIL's crop pads with 0 outside the donor
+                #pragma unroll
+                for (int i = 0; i < 6; ++i) N[i] = 0u;
+                for (int p = 0; p < 8; ++p) {
+                    const int u = u0 + p;
+                    if (!((m8 >> p) & 1u) || u < 0 || u >= dn.u_hi || v >= dn.v_hi) continue;
+                    const uint8_t* c = dn.base + (size_t)v * dn.pitch + 3 * u;
+                    #pragma unroll
+                    for (int ch = 0; ch < 3; ++ch) {
+                        const int k = 3 * p + ch;
+                        N[k >> 2] |= (uint32_t)__ldg(c + ch) << (8 * (k & 3));
+                    }
+                }
+            }
+            if (cut_sim) unit_bytelut(N, simtab_addr);
+        }
+        uint32_t M[6];
+        {
+            const uint32_t n0 = m8 & 15u, n1 = m8 >> 4;
+            M[0] = bmask[n0][0]; M[1] = bmask[n0][1]; M[2] = bmask[n0][2];
+            M[3] = bmask[n1][0]; M[4] = bmask[n1][1]; M[5] = bmask[n1][2];
+        }
+        if (want_l) {
+            uint32_t Np[6], Op[6], Ln[8], Lo[8];
+            #pragma unroll
+            for (int i = 0; i < 6; ++i) { Np[i] = N[i]; Op[i] = O[i]; }
+            apply_prog<LK>(Np, R);                               // pre(new)
+            if (!SP) apply_prog<LK>(Op, R);                      // the x buffer holds x itself: pre(old)
+            luma8(Np, Ln);
+            luma8(Op, Lo);
+            #pragma unroll
+            for (int p = 0; p < 8; ++p) if ((m8 >> p) & 1u) dl += Ln[p] - Lo[p];
+            if (SP) {
+                #pragma unroll
+                for (int i = 0; i < 6; ++i) N[i] = Np[i];
+            }
+        }
+        uint2* qs = reinterpret_cast<uint2*>(q);
+        qs[0] = make_uint2((O[0] & ~M[0]) | (N[0] & M[0]), (O[1] & ~M[1]) | (N[1] & M[1]));
+        qs[1] = make_uint2((O[2] & ~M[2]) | (N[2] & M[2]), (O[3] & ~M[3]) | (N[3] & M[3]));
+        qs[2] = make_uint2((O[4] & ~M[4]) | (N[4] & M[4]), (O[5] & ~M[5]) | (N[5] & M[5]));
+    }
+    return dl;
+}
+
 // ================================================================ canvas
 __global__ void __launch_bounds__(NT)
 canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant__ Geo7 g,
@@ -636,8 +747,9 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
     __shared__ Tables TP;
     __shared__ uint8_t simtab[256];
     __shared__ uint32_t red[NWARP * 8 + 8];
-    __shared__ uint16_t row_lo[kCanvasRows];     // first covered column of this CTA's canvas rows
-    __shared__ uint32_t row_pre[kCanvasRows + 1];   // covered-span pixels in the rows before
+    __shared__ uint16_t row_lo[kCanvasRows];     // first covered column of this CTA's canvas rows (polygon: first unit column)
+    __shared__ uint32_t row_pre[kCanvasRows + 1];   // covered-span pixels (polygon: 8-pixel units) in the rows before
+    __shared__ uint32_t bmask[16][3];            // byte masks of the four pixels of half a unit, by their coverage bits
     const int tid = threadIdx.x;
     const int b = (int)(blockIdx.x / (unsigned)g.ncanvas), part = (int)(blockIdx.x - (unsigned)b * g.ncanvas);
     const int H = g.H, W = g.W, npix = H * W;
@@ -727,8 +839,22 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
             if (wv) { if (lo < 0) lo = 32 * j + __ffs(wv) - 1; hi = 32 * j + 31 - __clz(wv); }
         }
         lo = min(max(lo, 0), max(bw - 1, 0)); hi = min(hi, bw - 1);
-        row_lo[r] = (uint16_t)lo;
-        row_pre[r + 1] = (hi >= lo && hi >= 0) ? (uint32_t)(hi - lo + 1) : 0u;
+        if (y != 2) {
+            // polygon / poly-line: the 8-pixel units of the image row the covered span touches
+            const int Xlo = max(D.paste[0][0] + lo, 0), Xhi = min(D.paste[0][0] + hi, W - 1);
+            const bool any = hi >= lo && hi >= 0 && Xlo <= Xhi;
+            row_lo[r] = (uint16_t)(Xlo >> 3);
+            row_pre[r + 1] = any ? (uint32_t)((Xhi >> 3) - (Xlo >> 3) + 1) : 0u;
+        } else {
+            row_lo[r] = (uint16_t)lo;
+            row_pre[r + 1] = (hi >= lo && hi >= 0) ? (uint32_t)(hi - lo + 1) : 0u;
+        }
+    }
+    if (tid < 48) {
+        const int n = tid / 3, j = tid - 3 * n;
+        uint32_t m = 0;
+        for (int qb = 0; qb < 4; ++qb) if ((n >> ((4 * j + qb) / 3)) & 1) m |= 0xFFu << (8 * qb);
+        bmask[n][j] = m;
     }
     __syncthreads();
     if (tid < 32) {
@@ -769,64 +895,22 @@ canvas_v7_kernel(const __grid_constant__ SsadBatchDesc d, const __grid_constant_
         w_lo = min(total, warp * per_w); w_hi = min(total, w_lo + per_w);
     };
     if (y == 1 || y == 3) {
-        // polygon (or the poly-line of label 3: a flat colour): one paste, straight into the x buffer (paste_patch, dataset_generator.py:268-275).  NB pixels per
-        // thread and round, their loads issued together: the chain coverage word -> cut pixel -> old pixel is three
-        // memory latencies long, and nothing else hides it.
-        constexpr int NB = SSAD_V7_NB_POLY;
-        const int total = span_total;
-        const int pl = D.paste[0][0], pt = D.paste[0][1];
-        const bool read_cut = !K.flat;
-        int w_lo, w_hi;
-        warp_range(total, w_lo, w_hi);
-        if (w_lo < w_hi) seek(w_lo);
-        for (int idx0 = w_lo + lane; idx0 < w_hi; idx0 += 32 * NB) {
-            int uu[NB], vv[NB];
-            uint32_t cw[NB];
-            #pragma unroll
-            for (int j = 0; j < NB; ++j) {
-                locate(min(idx0 + j * 32, w_hi - 1), uu[j], vv[j]);
-                cw[j] = cov[(size_t)vv[j] * pitchw + (uu[j] >> 5)];
-            }
-            bool on[NB];
-            const uint8_t* qc[NB];
-            uint8_t* qx[NB];
-            #pragma unroll
-            for (int j = 0; j < NB; ++j) {
-                const int X = pl + uu[j];
-                on[j] = (idx0 + j * 32 < w_hi) && ((cw[j] >> (uu[j] & 31)) & 1u) && X >= 0 && X < W;
-                const bool in_cut = on[j] && read_cut && uu[j] < dn.u_hi && vv[j] < dn.v_hi;
-                qc[j] = in_cut ? dn.base + (size_t)vv[j] * dn.pitch + 3 * uu[j] : nullptr;
-                qx[j] = on[j] ? xb + ((size_t)(pt + vv[j]) * W + X) * 3 : nullptr;
-            }
-            uint32_t cr[NB], cg[NB], cb[NB], xr[NB], xg[NB], xbl[NB];
-            #pragma unroll
-            for (int j = 0; j < NB; ++j) {
-                cr[j] = cg[j] = cb[j] = 0;
-                if (qc[j]) { cr[j] = __ldg(qc[j]); cg[j] = __ldg(qc[j] + 1); cb[j] = __ldg(qc[j] + 2); }
-            }
-            #pragma unroll
-            for (int j = 0; j < NB; ++j) {
-                xr[j] = xg[j] = xbl[j] = 0;
-                if (qx[j] && want_l) { xr[j] = qx[j][0]; xg[j] = qx[j][1]; xbl[j] = qx[j][2]; }
-            }
-            #pragma unroll
-            for (int j = 0; j < NB; ++j) {
-                if (!on[j]) continue;
-                uint32_t r = cr[j], gg = cg[j], bl = cb[j];
-                if (K.flat) { r = K.frgb[0]; gg = K.frgb[1]; bl = K.frgb[2]; }
-                else if (cut_sim) { r = simtab[r]; gg = simtab[gg]; bl = simtab[bl]; }
-                if (want_l) {
-                    uint32_t pr = r, pg = gg, pb = bl;
-                    pixel_prog(D.pre, TP, pr, pg, pb);
-                    const uint32_t L = luma_u8(pr, pg, pb);
-                    if (s_in_pre) { r = pr; gg = pg; bl = pb; }
-                    uint32_t orr = xr[j], og = xg[j], ob = xbl[j];
-                    if (!s_in_pre) pixel_prog(D.pre, TP, orr, og, ob);     // the x buffer holds x itself
-                    dl += L - luma_u8(orr, og, ob);
-                }
-                qx[j][0] = (uint8_t)r; qx[j][1] = (uint8_t)gg; qx[j][2] = (uint8_t)bl;
-            }
+        // polygon (or the poly-line of label 3: a flat colour): one paste, straight into the x buffer (paste_patch,
+        // dataset_generator.py:268-275), 8 pixels = 24 bytes at a time (see polygon_units)
+        uint32_t fw[3];                          // the flat colour as three words of repeating R, G, B bytes
+        {
+            const uint32_t r = K.frgb[0], gg = K.frgb[1], bl = K.frgb[2];
+            fw[0] = r | (gg << 8) | (bl << 16) | (r << 24);
+            fw[1] = gg | (bl << 8) | (r << 16) | (gg << 24);
+            fw[2] = bl | (r << 8) | (gg << 16) | (bl << 24);
         }
+        ProgRegs R;
+        R.fs = D.pre.fs; R.ta = smem_u32(TP.a); R.tab = smem_u32(TP.ab); R.tbc = smem_u32(TP.b) + (uint32_t)TB_OFF - kMagicBits;
+        const int kind = want_l ? loop_kind(D.pre) : LK_COPY;
+        #define SSAD_CALL(LK) dl = polygon_units<LK>(span_total, row_lo, row_pre, nrows, my_lo, cov, pitchw, D.paste[0][0], D.paste[0][1], \
+                                                     W, xb, dn, K.flat != 0, fw, cut_sim, smem_u32(simtab), bmask, want_l, R, tid)
+        SSAD_V7_BY_KIND(kind, SSAD_CALL)
+        #undef SSAD_CALL
     } else {
         int w_lo, w_hi;
         warp_range(span_total, w_lo, w_hi);
