@@ -103,6 +103,10 @@ __device__ __forceinline__ void sobel_at(const double* S, int y, int x, int y0, 
 #ifndef SSAD_PLANES_WARPS
 #define SSAD_PLANES_WARPS 16
 #endif
+// ... and the fewest rows a band should have
+#ifndef SSAD_PLANES_ROWS
+#define SSAD_PLANES_ROWS 64
+#endif
 
 __global__ void __launch_bounds__(CT_NT, SSAD_CANNY_MINB)
 canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* __restrict__ src, long long src_pitch,
@@ -986,7 +990,7 @@ __device__ void reach_component(const Plane& Mp, const Plane& Rp, int H, int ylo
 }
 
 // One CTA per image, one band of rows per warp, one lane per 32-pixel word of a row.
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(32 * SSAD_PLANES_WARPS)
 mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, long long plane_words,
                    uint32_t* __restrict__ mask_bits, int mask_pitch_words, long long mask_stride_words) {
     __shared__ int s_first, s_cnt;
@@ -1005,45 +1009,38 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
     // 1. hysteresis: edges = pixels of the low plane 8-connected to a pixel of the high plane (P0 = low, P1 = high -> edges)
     reach<false>(P0, P1, H, ylo, yhi, rowmask, lane);
 
-    // 2. binary_dilation(3x3): P2 = dilate(P1)   (rows above / below the band belong to other warps: barrier between steps)
-    auto dilate = [&](const Plane& A, const Plane& D) {
-        if (ylo <= yhi) {
-            uint32_t up = ylo > 0 ? A.ld(ylo - 1) : 0u, cur = A.ld(ylo);
-            for (int y = ylo; y <= yhi; ++y) {
-                const uint32_t dn = (y + 1 < H) ? A.ld(y + 1) : 0u;
-                D.st(y, spread3(up | cur | dn, lane) & rowmask);
-                up = cur; cur = dn;
-            }
-        }
-        __syncthreads();
-    };
-    dilate(P1, P2);
-    // 3. binary_closing(3x3) = erosion(dilation): P0 = dilate(P2); P1 = erode3(P0), outside the image counts as 0
-    dilate(P2, P0);
+    // 2-4a. binary_dilation(3x3), then binary_closing(3x3) = erosion(dilation), then the seeds of the hole fill, in ONE
+    //    sweep: row y of the closing needs rows y-3..y+3 of the edges, so the warp streams its band plus three rows
+    //    either side and keeps the two previous rows of each stage in registers (D1 = dilate(E), D2 = dilate(D1),
+    //    C = erode3(D2); rows outside the image are 0 at every stage, as scipy's border_value=0).  P0 = C,
+    //    P2 = seeds = background pixels of C on the image border.
     if (ylo <= yhi) {
-        uint32_t up = ylo > 0 ? P0.ld(ylo - 1) : 0u, cur = P0.ld(ylo);
-        for (int y = ylo; y <= yhi; ++y) {
-            const uint32_t dn = (y + 1 < H) ? P0.ld(y + 1) : 0u;
-            const uint32_t t = up & cur & dn;
-            P1.st(y, t & shl1(t, lane) & shr1(t, lane));
-            up = cur; cur = dn;
+        uint32_t e2 = 0, e1 = 0, d1b = 0, d1a = 0, d2b = 0, d2a = 0;       // E[yy-2], E[yy-1], D1[yy-3], D1[yy-2], D2[yy-4], D2[yy-3]
+        #pragma unroll 1
+        for (int yy = ylo - 3; yy <= yhi + 3; ++yy) {
+            const uint32_t e0 = (yy >= 0 && yy < H) ? P1.ld(yy) : 0u;
+            const uint32_t d1 = (yy - 1 >= 0 && yy - 1 < H) ? (spread3(e2 | e1 | e0, lane) & rowmask) : 0u;      // D1[yy-1]
+            const uint32_t d2 = (yy - 2 >= 0 && yy - 2 < H) ? (spread3(d1b | d1a | d1, lane) & rowmask) : 0u;    // D2[yy-2]
+            const uint32_t t = d2b & d2a & d2;
+            const uint32_t c = t & shl1(t, lane) & shr1(t, lane);                                                  // C[yy-3]
+            const int y = yy - 3;
+            if (y >= ylo) {
+                P0.st(y, c);
+                uint32_t seed = ~c & rowmask;
+                if (y != 0 && y != H - 1) {
+                    uint32_t e = 0;
+                    if (lane == 0) e |= 1u;
+                    if (lane == nw - 1) e |= 1u << ((W - 1) & 31);
+                    seed &= e;
+                }
+                P2.st(y, seed);
+            }
+            e2 = e1; e1 = e0; d1b = d1a; d1a = d1; d2b = d2a; d2a = d2;
         }
     }
     __syncthreads();
-    // 4. binary_fill_holes: background reachable from outside the image through ~P1 (8-connected); filled = the rest
-    for (int y = ylo; y <= yhi; ++y) {
-        const uint32_t bg = ~P1.ld(y) & rowmask;
-        uint32_t seed = bg;
-        if (y != 0 && y != H - 1) {
-            uint32_t e = 0;
-            if (lane == 0) e |= 1u;
-            if (lane == nw - 1) e |= 1u << ((W - 1) & 31);
-            seed &= e;
-        }
-        P2.st(y, seed);
-    }
-    __syncthreads();
-    reach<true>(P1, P2, H, ylo, yhi, rowmask, lane);
+    // 4b. binary_fill_holes: background reachable from outside the image through ~C (8-connected); filled = the rest
+    reach<true>(P0, P2, H, ylo, yhi, rowmask, lane);
     // 5. binary_erosion(4x4), origin 0: offsets -2..+1 in both axes; P0 = erode4(~P2)
     if (ylo <= yhi) {
         auto fg = [&](int y) { return (y >= 0 && y < H) ? (~P2.ld(y) & rowmask) : 0u; };
@@ -1053,16 +1050,15 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
             const uint32_t t = f2 & f1 & f0 & fn;
             const uint32_t l1 = shl1(t, lane), l2 = shl1(l1, lane);
             P0.st(y, l2 & l1 & t & shr1(t, lane));
+            P1.st(y, 0u); OUT.st(y, 0u);                                    // (step 6's scratch and result planes)
             f2 = f1; f1 = f0; f0 = fn;
         }
     }
-    __syncthreads();
-    // 6. largest 8-connected component (skimage label + argmax(bincount)): peel components in raster order of their
-    //    first pixel; strictly-greater keeps the first of equal sizes (= the lowest label).  P0 = remaining, P1 = scratch.
-    //    (P2 is still being read by slower warps' erosion above until the barrier; P1 is free.)
-    for (int y = ylo; y <= yhi; ++y) { P1.st(y, 0u); OUT.st(y, 0u); }
     if (threadIdx.x == 0) { s_first = 0x7FFFFFFF; s_cnt = 0; }
     __syncthreads();
+    // 6. largest 8-connected component (skimage label + argmax(bincount)): peel components in raster order of their
+    //    first pixel; strictly-greater keeps the first of equal sizes (= the lowest label).  P0 = remaining, P1 = scratch
+    //    (zeroed by the erosion sweep above: the edges it held were last read before the hole fill).
     int best = 0, blo = 1, bhi = 0;          // rows of the band the best component so far occupies in OUT
     int ys = ylo;                            // first row of the band that may still hold a pixel
     for (;;) {
@@ -1228,7 +1224,7 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
     e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     // 4. hysteresis, morphology, hole filling, largest component on the bit planes: a CTA per image, a band of rows per warp
-    int nwarp = height / 64;
+    int nwarp = height / SSAD_PLANES_ROWS;
     nwarp = nwarp < 1 ? 1 : (nwarp > SSAD_PLANES_WARPS ? SSAD_PLANES_WARPS : nwarp);
     ssad::mask_planes_kernel<<<batch, 32 * nwarp, 0, st>>>(batch, height, width, nw, ws, plane_words, mask_bits, mask_pitch_words,
                                                          mask_stride_words);
