@@ -199,6 +199,10 @@ int ssad_obj_mask_launches(void);
  * (margin_scale > 1), cap the pixels a tile may list (sub_cap, 0..96) and the list entries per image (0..4096) so that
  * the tests can drive every path; the masks must not depend on them.  Arguments out of range restore the defaults. */
 void ssad_obj_mask_test_knobs(float margin_scale, int32_t sub_cap, int32_t pix_per_image);
+/* Test hook: the largest component is found by a union-find over the runs of set pixels when the plane holds at most
+ * `max_runs` of them (default and maximum 4096), by peeling flooded components otherwise; 0 always takes the second
+ * path, out of range restores the default.  The masks must not depend on it. */
+void ssad_obj_mask_test_runs(int32_t max_runs);
 
 /* Unit entry points (parity tests of the individual reference routines). */
 

@@ -20,6 +20,7 @@
 //                      the carry trick  reach = (M & ~(M + S)) | S  inside a word and a ballot + add carry chain
 //                      across the 32 words, until a sweep pair changes nothing.
 #include <cuda_runtime.h>
+#include <cstdio>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -989,11 +990,180 @@ __device__ void reach_component(const Plane& Mp, const Plane& Rp, int H, int ylo
     }
 }
 
+// ---- largest component by runs (the usual case: a few runs per row after the hole fill and the 4x4 erosion) ----------
+// A run = a maximal stretch of set pixels of one row; runs are numbered in raster order, so the smallest number of a
+// component is the run that holds its first pixel (skimage's label order).  Rows are independent here: every warp takes
+// rows round-robin, there is no sweep that has to walk the image top to bottom.
+constexpr int CCL_MAXH = 2048;     // rows the row-offset table holds
+constexpr int CCL_CAP = 4096;      // runs the union-find tables hold; more -> the caller falls back to the flood peel
+
+struct CclSmem {
+    int off[CCL_MAXH + 1];         // off[r] = number of runs in rows < r
+    uint32_t parent[CCL_CAP];
+    uint32_t size[CCL_CAP];
+    int wsum[32];
+    unsigned long long wbest[32];
+};
+
+__device__ __forceinline__ uint32_t le_mask(int q) { return FULL >> (31 - q); }
+
+// exclusive prefix over the lanes of a warp
+__device__ __forceinline__ int lane_prefix(int v, int lane) {
+    int x = v;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(FULL, x, o);
+        if (lane >= o) x += y;
+    }
+    return x - v;
+}
+
+__device__ __forceinline__ uint32_t ccl_find(volatile uint32_t* parent, uint32_t a) {
+    uint32_t pa;
+    while ((pa = parent[a]) != a) a = pa;
+    return a;
+}
+// roots only ever get a smaller parent: no cycles, and the root of a component ends as its smallest run number
+__device__ __forceinline__ void ccl_unite(uint32_t* parent, uint32_t a, uint32_t b) {
+    for (;;) {
+        a = ccl_find(parent, a);
+        b = ccl_find(parent, b);
+        if (a == b) return;
+        if (a < b) { const uint32_t t = a; a = b; b = t; }
+        if (atomicCAS(parent + a, a, b) == a) return;
+    }
+}
+
+// OUT = the largest 8-connected component of P0 (ties: the first in raster order), all ones when P0 is empty.
+// false (nothing written) when P0 holds more than `cap` runs.  Every thread of the CTA must call this.
+__device__ bool largest_component_runs(const Plane& P0, const Plane& OUT, int H, uint32_t rowmask, int cap, CclSmem& S) {
+    const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = NT >> 5;
+    // 1. runs per row.  (The three row passes of this routine take the same 8-row groups per warp and issue the eight row
+    //    loads together: a row is a 128-byte line that the first pass brings into this SM's L1.)
+    for (int r0 = warp * 8; r0 < H; r0 += nwarp * 8) {
+        uint32_t Bv[8];
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) Bv[k] = (r0 + k < H) ? P0.ld(r0 + k) : 0u;
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int c = __reduce_add_sync(FULL, (unsigned)__popc(Bv[k] & ~shl1(Bv[k], lane)));
+            if (lane == 0 && r0 + k < H) S.off[r0 + k + 1] = c;
+        }
+    }
+    if (tid == 0) S.off[0] = 0;
+    __syncthreads();
+    // 2. off[] <- inclusive prefix (each thread a stretch of rows, a warp scan of the stretch sums, then the warps' sums)
+    {
+        const int per = (H + NT - 1) / NT, r0 = 1 + tid * per, r1 = min(H + 1, r0 + per);
+        int sum = 0;
+        for (int r = r0; r < r1; ++r) sum += S.off[r];
+        const int before = lane_prefix(sum, lane);
+        if (lane == 31) S.wsum[warp] = before + sum;
+        __syncthreads();
+        int base = before;
+        for (int w = 0; w < warp; ++w) base += S.wsum[w];
+        for (int r = r0; r < r1; ++r) { base += S.off[r]; S.off[r] = base; }
+        __syncthreads();
+    }
+    const int n = S.off[H];
+    if (n > cap) return false;
+    if (n == 0) {
+        for (int r = warp; r < H; r += nwarp) OUT.st(r, rowmask);
+        return true;
+    }
+    for (int i = tid; i < n; i += NT) { S.parent[i] = i; S.size[i] = 0; }
+    __syncthreads();
+    // 3. unions with the row above and pixel counts, eight rows at a time per warp (the row above is carried in registers).
+    //    Run i of this row and run j of the row above touch (8-connected) iff i meets j widened by one pixel either
+    //    side; each such pair has exactly one first common column, which is either the start of i (then the row above has
+    //    a pixel there or one column to the left) or the start of j minus one (then this row has a pixel there).  With
+    //    SB(x) / SA(x) = run starts at columns <= x, the runs at such a column q are SB(q) - 1 and SA(q) - 1 in both cases.
+    for (int r0 = warp * 8; r0 < H; r0 += nwarp * 8) {
+        uint32_t A = 0, A1 = 0, sA = 0;
+        int PA = 0;
+        if (r0 > 0) {
+            A = P0.ld(r0 - 1); A1 = shl1(A, lane); sA = A & ~A1;
+            PA = S.off[r0 - 1] + lane_prefix(__popc(sA), lane);
+        }
+        uint32_t Bv[8];
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) Bv[k] = (r0 + k < H) ? P0.ld(r0 + k) : 0u;
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int r = r0 + k;
+            const uint32_t B = Bv[k];
+            if (!__any_sync(FULL, B != 0u)) { A = A1 = sA = 0; PA = 0; continue; }
+            const uint32_t B1 = shl1(B, lane), sB = B & ~B1;
+            const int PB = S.off[r] + lane_prefix(__popc(sB), lane);
+            uint32_t m = (sB & (A | A1)) | (sA & B1);
+            while (m) {
+                const int q = __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t le = le_mask(q);
+                ccl_unite(S.parent, PB + __popc(sB & le) - 1, PA + __popc(sA & le) - 1);
+            }
+            m = B;
+            while (m) {                                   // the pieces of runs inside this word
+                const uint32_t low = m & (0u - m), t = m + low, piece = m & ~t;
+                atomicAdd(&S.size[PB + __popc(sB & le_mask(__ffs(low) - 1)) - 1], (uint32_t)__popc(piece));
+                m &= t;
+            }
+            A = B; A1 = B1; sA = sB; PA = PB;
+        }
+    }
+    __syncthreads();
+    // 4. every run learns its root; the roots collect the pixel counts
+    for (int i = tid; i < n; i += NT) {
+        const uint32_t r = ccl_find(S.parent, i);
+        if (r != (uint32_t)i) { S.parent[i] = r; atomicAdd(&S.size[r], S.size[i]); }
+    }
+    __syncthreads();
+    // 5. the largest root, the smallest number among equals: key = size << 32 | ~number
+    unsigned long long best = 0;
+    for (int i = tid; i < n; i += NT)
+        if (S.parent[i] == (uint32_t)i) {
+            const unsigned long long k = ((unsigned long long)S.size[i] << 32) | (uint32_t)~i;
+            best = k > best ? k : best;
+        }
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long k = __shfl_xor_sync(FULL, best, o);
+        best = k > best ? k : best;
+    }
+    if (lane == 0) S.wbest[warp] = best;
+    __syncthreads();
+    for (int w = 0; w < nwarp; ++w) best = S.wbest[w] > best ? S.wbest[w] : best;
+    const uint32_t keep = ~(uint32_t)best;
+    // 6. the rows of the result: the runs whose root is the winner
+    for (int r0 = warp * 8; r0 < H; r0 += nwarp * 8) {
+        uint32_t Bv[8];
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) Bv[k] = (r0 + k < H) ? P0.ld(r0 + k) : 0u;
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int r = r0 + k;
+            const uint32_t B = Bv[k];
+            uint32_t out = 0;
+            if (__any_sync(FULL, B != 0u)) {
+                const uint32_t sB = B & ~shl1(B, lane);
+                int id = S.off[r] + lane_prefix(__popc(sB), lane);
+                uint32_t ks = 0;
+                for (uint32_t m = sB; m; m &= m - 1, ++id)
+                    if (S.parent[id] == keep) ks |= m & (0u - m);
+                if (__any_sync(FULL, ks != 0u)) out = flood_row(B, ks, lane);
+            }
+            if (r < H) OUT.st(r, out);
+        }
+    }
+    return true;
+}
+
 // One CTA per image, one band of rows per warp, one lane per 32-pixel word of a row.
 __global__ void __launch_bounds__(32 * SSAD_PLANES_WARPS)
 mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, long long plane_words,
-                   uint32_t* __restrict__ mask_bits, int mask_pitch_words, long long mask_stride_words) {
+                   uint32_t* __restrict__ mask_bits, int mask_pitch_words, long long mask_stride_words, int ccl_cap) {
     __shared__ int s_first, s_cnt;
+    __shared__ CclSmem s_ccl;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
     const int b = blockIdx.x;
     const int per = (H + nwarp - 1) / nwarp;
@@ -1006,8 +1176,15 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
     Plane P2{P1.p + plane_words, nw, lane, on};
     Plane OUT{mask_bits + (size_t)b * mask_stride_words + lo_, mask_pitch_words, lane, on};
 
+#ifdef SSAD_PLANES_TIMING
+    long long tk[8]; int ncomp = 0; tk[0] = clock64();
+#define SSAD_TICK(i) tk[i] = clock64()
+#else
+#define SSAD_TICK(i)
+#endif
     // 1. hysteresis: edges = pixels of the low plane 8-connected to a pixel of the high plane (P0 = low, P1 = high -> edges)
     reach<false>(P0, P1, H, ylo, yhi, rowmask, lane);
+    SSAD_TICK(1);
 
     // 2-4a. binary_dilation(3x3), then binary_closing(3x3) = erosion(dilation), then the seeds of the hole fill, in ONE
     //    sweep: row y of the closing needs rows y-3..y+3 of the edges, so the warp streams its band plus three rows
@@ -1017,14 +1194,20 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
     if (ylo <= yhi) {
         uint32_t e2 = 0, e1 = 0, d1b = 0, d1a = 0, d2b = 0, d2a = 0;       // E[yy-2], E[yy-1], D1[yy-3], D1[yy-2], D2[yy-4], D2[yy-3]
         #pragma unroll 1
-        for (int yy = ylo - 3; yy <= yhi + 3; ++yy) {
-            const uint32_t e0 = (yy >= 0 && yy < H) ? P1.ld(yy) : 0u;
+        for (int yb = ylo - 3; yb <= yhi + 3; yb += 4) {                    // four row loads in flight
+        uint32_t ev[4];
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) ev[k] = (yb + k >= 0 && yb + k < H && yb + k <= yhi + 3) ? P1.ld(yb + k) : 0u;
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int yy = yb + k;
+            const uint32_t e0 = ev[k];
             const uint32_t d1 = (yy - 1 >= 0 && yy - 1 < H) ? (spread3(e2 | e1 | e0, lane) & rowmask) : 0u;      // D1[yy-1]
             const uint32_t d2 = (yy - 2 >= 0 && yy - 2 < H) ? (spread3(d1b | d1a | d1, lane) & rowmask) : 0u;    // D2[yy-2]
             const uint32_t t = d2b & d2a & d2;
             const uint32_t c = t & shl1(t, lane) & shr1(t, lane);                                                  // C[yy-3]
             const int y = yy - 3;
-            if (y >= ylo) {
+            if (y >= ylo && y <= yhi) {
                 P0.st(y, c);
                 uint32_t seed = ~c & rowmask;
                 if (y != 0 && y != H - 1) {
@@ -1037,28 +1220,52 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
             }
             e2 = e1; e1 = e0; d1b = d1a; d1a = d1; d2b = d2a; d2a = d2;
         }
+        }
     }
     __syncthreads();
+    SSAD_TICK(2);
     // 4b. binary_fill_holes: background reachable from outside the image through ~C (8-connected); filled = the rest
     reach<true>(P0, P2, H, ylo, yhi, rowmask, lane);
+    SSAD_TICK(3);
     // 5. binary_erosion(4x4), origin 0: offsets -2..+1 in both axes; P0 = erode4(~P2)
     if (ylo <= yhi) {
         auto fg = [&](int y) { return (y >= 0 && y < H) ? (~P2.ld(y) & rowmask) : 0u; };
         uint32_t f2 = fg(ylo - 2), f1 = fg(ylo - 1), f0 = fg(ylo);        // rows y-2, y-1, y
-        for (int y = ylo; y <= yhi; ++y) {
-            const uint32_t fn = fg(y + 1);
-            const uint32_t t = f2 & f1 & f0 & fn;
-            const uint32_t l1 = shl1(t, lane), l2 = shl1(l1, lane);
-            P0.st(y, l2 & l1 & t & shr1(t, lane));
-            P1.st(y, 0u); OUT.st(y, 0u);                                    // (step 6's scratch and result planes)
-            f2 = f1; f1 = f0; f0 = fn;
+        #pragma unroll 1
+        for (int yb = ylo; yb <= yhi; yb += 4) {                            // four row loads in flight
+            uint32_t fv[4];
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) fv[k] = (yb + k <= yhi) ? fg(yb + k + 1) : 0u;
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int y = yb + k;
+                const uint32_t fn = fv[k];
+                const uint32_t t = f2 & f1 & f0 & fn;
+                const uint32_t l1 = shl1(t, lane), l2 = shl1(l1, lane);
+                if (y <= yhi) {
+                    P0.st(y, l2 & l1 & t & shr1(t, lane));
+                    P1.st(y, 0u); OUT.st(y, 0u);                            // (step 6's scratch and result planes)
+                }
+                f2 = f1; f1 = f0; f0 = fn;
+            }
         }
     }
     if (threadIdx.x == 0) { s_first = 0x7FFFFFFF; s_cnt = 0; }
     __syncthreads();
+    SSAD_TICK(4);
     // 6. largest 8-connected component (skimage label + argmax(bincount)): peel components in raster order of their
     //    first pixel; strictly-greater keeps the first of equal sizes (= the lowest label).  P0 = remaining, P1 = scratch
     //    (zeroed by the erosion sweep above: the edges it held were last read before the hole fill).
+    //    Usual case: few runs -> union-find over the runs; the flood peel below is the path for planes with more runs.
+    if (H <= CCL_MAXH && ccl_cap > 0 && largest_component_runs(P0, OUT, H, rowmask, min(ccl_cap, CCL_CAP), s_ccl)) {
+#ifdef SSAD_PLANES_TIMING
+        SSAD_TICK(5);
+        if (threadIdx.x == 0 && (b % 128) == 0)
+            printf("planes b=%d hyst %lld closing %lld fill %lld erode %lld runs %lld total %lld\n", b, tk[1] - tk[0],
+                   tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[5] - tk[0]);
+#endif
+        return;
+    }
     int best = 0, blo = 1, bhi = 0;          // rows of the band the best component so far occupies in OUT
     int ys = ylo;                            // first row of the band that may still hold a pixel
     for (;;) {
@@ -1068,6 +1275,9 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
         __syncthreads();
         const int y0 = s_first;
         if (y0 == 0x7FFFFFFF) break;
+#ifdef SSAD_PLANES_TIMING
+        ++ncomp;
+#endif
         int alo = 0x7FFFFFFF, ahi = -1;
         if (y0 >= ylo && y0 <= yhi) {        // the band that owns the row plants the seed: the row's first pixel, flooded
             const uint32_t w = P0.ld(y0);
@@ -1100,6 +1310,12 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
     }
     if (best == 0)                                             // no foreground: label 0 wins the argmax -> all True
         for (int y = ylo; y <= yhi; ++y) OUT.st(y, rowmask);
+#ifdef SSAD_PLANES_TIMING
+    SSAD_TICK(5);
+    if (threadIdx.x == 0 && (b % 128) == 0)
+        printf("planes b=%d hyst %lld closing %lld fill %lld erode %lld peel %lld (components %d) total %lld\n", b, tk[1] - tk[0],
+               tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], ncomp, tk[5] - tk[0]);
+#endif
 }
 
 }  // namespace ssad
@@ -1117,6 +1333,7 @@ struct ObjMaskLayout {
 float g_margin_scale = 1.0f;
 int g_sub_cap = ssad::SUB_CAP;
 int g_pix_per_image = 4096;
+int g_ccl_cap = ssad::CCL_CAP;          // runs the union-find of the largest component takes (0: always the flood peel)
 
 ObjMaskLayout obj_mask_layout(int batch, int height, int width) {
     ObjMaskLayout L;
@@ -1152,6 +1369,10 @@ extern "C" void ssad_obj_mask_test_knobs(float margin_scale, int32_t sub_cap, in
     g_margin_scale = margin_scale > 0.0f ? margin_scale : 1.0f;
     g_sub_cap = (sub_cap >= 0 && sub_cap <= ssad::SUB_CAP) ? sub_cap : ssad::SUB_CAP;
     g_pix_per_image = (pix_per_image >= 0 && pix_per_image <= 4096) ? pix_per_image : 4096;
+}
+
+extern "C" void ssad_obj_mask_test_runs(int32_t max_runs) {
+    g_ccl_cap = (max_runs >= 0 && max_runs <= ssad::CCL_CAP) ? max_runs : ssad::CCL_CAP;
 }
 
 extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
@@ -1227,7 +1448,7 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
     int nwarp = height / SSAD_PLANES_ROWS;
     nwarp = nwarp < 1 ? 1 : (nwarp > SSAD_PLANES_WARPS ? SSAD_PLANES_WARPS : nwarp);
     ssad::mask_planes_kernel<<<batch, 32 * nwarp, 0, st>>>(batch, height, width, nw, ws, plane_words, mask_bits, mask_pitch_words,
-                                                         mask_stride_words);
+                                                         mask_stride_words, g_ccl_cap);
     e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     return SSAD_OK;

@@ -89,5 +89,44 @@ def test_float64_fallback_paths_give_the_same_masks(knobs):
         lib.ssad_obj_mask_test_knobs(-1.0, -1, -1)
 
 
+def _blob_images():
+    """Bright blobs on a flat ground: several components of EQUAL size (the first in raster order must win), nested
+    shapes, a comb whose teeth are one component, blobs one and two pixels apart, a blob on the image border."""
+    H, W = 200, 288
+    img = np.full((4, H, W, 3), 30, dtype=np.uint8)
+    for (y, x) in [(20, 200), (20, 40), (120, 40), (120, 200)]:       # four equal squares
+        img[0, y:y + 40, x:x + 40] = 220
+    img[1, 30:170, 30:250] = 220                                       # ring with an island inside
+    img[1, 60:140, 60:220] = 30
+    img[1, 90:110, 100:180] = 220
+    for k in range(12):                                                # comb: teeth joined at the bottom
+        img[2, 20:150, 20 + 20 * k:30 + 20 * k] = 220
+    img[2, 150:170, 20:250] = 220
+    img[3, 0:50, 0:60] = 220                                           # on the border
+    img[3, 80:130, 100:150] = 220                                      # two blobs a few pixels apart (closing may join them)
+    img[3, 80:130, 153:203] = 220
+    img[3, 150:190, 100:150] = 220
+    return img
+
+
+@pytest.mark.parametrize("max_runs", [-1, 0, 16])
+def test_largest_component_paths_give_the_same_masks(max_runs):
+    """The largest component is a union-find over the runs of the eroded plane when it holds at most `max_runs` runs, a
+    peel of flooded components otherwise (include/ssad.h: ssad_obj_mask_test_runs): same masks on either path."""
+    from ssad_b200 import _native
+    lib = _native.load()
+    try:
+        lib.ssad_obj_mask_test_runs(max_runs)
+        _check(_blob_images(), f"blobs max_runs={max_runs}")
+        _check(synth.screw_images(3, 192, 256, 91), f"screw 192x256 max_runs={max_runs}")
+        _check(synth.texture_images(2, 160, 224, 7), f"texture max_runs={max_runs}")
+        rng = np.random.default_rng(5)
+        blocks = np.kron(rng.integers(0, 2, (2, 12, 15, 1), dtype=np.uint8), np.ones((1, 10, 10, 3), np.uint8)) * 200 + 20
+        _check(blocks.astype(np.uint8), f"checker blocks max_runs={max_runs}")
+        _check(synth.screw_images(1, 1024, 1024, 77), f"screw 1024 max_runs={max_runs}")
+    finally:
+        lib.ssad_obj_mask_test_runs(-1)
+
+
 def test_1024_batch_of_three():
     _check(synth.screw_images(3, 1024, 1024, 78), "screw 1024 x3")
