@@ -322,7 +322,9 @@ constexpr int SS_W = SC_W + 4;                           // S (smoothed): rows o
 constexpr int SM_H = SC_H + 2, SM_W = SS_W;              // |gradient|^2: rows y0-1 .. y0+SC_H, columns x0-1 .. (130 used)
 constexpr int SUB_CAP = 96;                              // undecided pixels a 64x32 tile may list (else: dense float64 tile)
 static_assert(SG_W % 4 == 0 && SS_W % 4 == 0, "vector rows");
-static_assert(SM_H * SM_W <= SV_H * SG_W, "|gradient|^2 reuses the axis-0 buffer");
+constexpr int SV_P = 2 * SG_W + 4;                       // floats per row PAIR of the axis-0 result: an odd number of 16-byte
+                                                         // chunks, so lanes on consecutive row pairs hit different banks
+static_assert(SM_H * SM_W <= (SV_H / 2) * SV_P, "|gradient|^2 reuses the axis-0 buffer");
 
 struct C32K {
     float w[7];              // taps 0..6 (centre last) of the symmetric 13-tap kernel
@@ -334,7 +336,7 @@ struct C32K {
 };
 struct C32Smem {
     float G[SG_H * SG_W];    // L (grey levels); reused for S once the axis-0 pass is done
-    float V[SV_H * SG_W];    // axis-0 pass; reused for |gradient|^2
+    float V[(SV_H / 2) * SV_P];   // axis-0 pass, rows interleaved in pairs; reused for |gradient|^2
     float ra[SV_H], rb[SS_W];   // 1 / bleed-over along the rows / the columns (border tiles)
     uint32_t cand[SC_H * (SC_W / 32)];   // pixels whose |gradient| may reach the low threshold, one word per 32 pixels of a row
     uint32_t nword;                      // words with a candidate ...
@@ -498,38 +500,44 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
                     float a0, a1, b0, b1;
                     om_unpack2(om_sym13(v + o, wp), a0, a1);          // row r0 + o:     columns 2 pr, 2 pr + 1
                     om_unpack2(om_sym13(v + o + 1, wp), b0, b1);      // row r0 + o + 1
-                    *reinterpret_cast<float4*>(&sm.V[(((r0 + o) >> 1) * SG_W + 2 * pr) * 2]) = make_float4(a0, b0, a1, b1);
+                    *reinterpret_cast<float4*>(&sm.V[((r0 + o) >> 1) * SV_P + 4 * pr]) = make_float4(a0, b0, a1, b1);
                 }
             }
         }
     }
     __syncthreads();
 
-    // ---- Gaussian along axis 1 (/ bleed-over in border tiles): a thread takes two columns of a row pair; lanes walk
-    // along the row, so every 128-bit shared-memory access of a warp is a run of consecutive chunks (no bank conflicts)
+    // ---- Gaussian along axis 1 (/ bleed-over in border tiles): a thread takes twelve columns of a row pair -- 24 packed
+    // pairs = 12 LDS.128 for 12 packed results (two columns per thread cost 7 loads for 2).  Lanes walk down the row
+    // pairs: SV_P makes the eight 16-byte accesses of a quarter warp fall on different banks.
     float* const S = sm.G;
     {
-        constexpr int NQ = SS_W / 2, NRP = SV_H / 2;     // 66 column pairs (S columns 0 .. 131), 34 row pairs
-        for (int t = tid; t < NRP * NQ; t += SC_NT) {
-            const int rp = t / NQ, q = t - rp * NQ;
-            // S[r][c] = sum_k w[k] V[r][c + k], c = 2q, 2q + 1: the pairs V2[rp][2q .. 2q + 13]
-            const float4* vp = reinterpret_cast<const float4*>(&sm.V[(rp * SG_W + 2 * q) * 2]);
-            om_f32x2 v[14];
+        constexpr int SEG1 = 12, NS1 = SS_W / SEG1, NRP = SV_H / 2;     // 11 column segments x 18 row pairs = 198 tasks
+        static_assert(SS_W % SEG1 == 0 && SEG1 % 4 == 0 && (NS1 - 1) * SEG1 + SEG1 + 12 <= SG_W, "whole segments inside a row of V");
+        for (int t = tid; t < NRP * NS1; t += SC_NT) {
+            const int sg = t / NRP, rp = t - sg * NRP, c0 = sg * SEG1;
+            // S[r][c] = sum_k w[k] V[r][c + k], c = c0 .. c0 + 11: the pairs V2[rp][c0 .. c0 + 23]
+            const float4* vp = reinterpret_cast<const float4*>(&sm.V[rp * SV_P + 2 * c0]);
+            om_f32x2 v[SEG1 + 12];
             #pragma unroll
-            for (int k = 0; k < 7; ++k) {
+            for (int k = 0; k < (SEG1 + 12) / 2; ++k) {
                 const float4 f = vp[k];
                 v[2 * k] = om_pack2(f.x, f.y); v[2 * k + 1] = om_pack2(f.z, f.w);
             }
-            float s00, s10, s01, s11;                    // s<row><column>
-            om_unpack2(om_sym13(v, wp), s00, s10);
-            om_unpack2(om_sym13(v + 1, wp), s01, s11);
-            const int r = 2 * rp, c = 2 * q;
+            float s0[SEG1], s1[SEG1];                     // rows 2 rp, 2 rp + 1
+            #pragma unroll
+            for (int j = 0; j < SEG1; ++j) om_unpack2(om_sym13(v + j, wp), s0[j], s1[j]);
+            const int r = 2 * rp;
             if (border) {
-                const float ra0 = sm.ra[r], ra1 = sm.ra[r + 1], cb0 = sm.rb[c], cb1 = sm.rb[c + 1];
-                s00 *= ra0 * cb0; s01 *= ra0 * cb1; s10 *= ra1 * cb0; s11 *= ra1 * cb1;
+                const float ra0 = sm.ra[r], ra1 = sm.ra[r + 1];
+                #pragma unroll
+                for (int j = 0; j < SEG1; ++j) { const float cb = sm.rb[c0 + j]; s0[j] *= ra0 * cb; s1[j] *= ra1 * cb; }
             }
-            *reinterpret_cast<float2*>(&S[r * SS_W + c]) = make_float2(s00, s01);
-            *reinterpret_cast<float2*>(&S[(r + 1) * SS_W + c]) = make_float2(s10, s11);
+            #pragma unroll
+            for (int j = 0; j < SEG1; j += 4) {
+                *reinterpret_cast<float4*>(&S[r * SS_W + c0 + j]) = make_float4(s0[j], s0[j + 1], s0[j + 2], s0[j + 3]);
+                *reinterpret_cast<float4*>(&S[(r + 1) * SS_W + c0 + j]) = make_float4(s1[j], s1[j + 1], s1[j + 2], s1[j + 3]);
+            }
         }
     }
     __syncthreads();
@@ -557,60 +565,63 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     const float Ec = K.ec[bc], Em = K.em[bc];
     const float lo_no = K.lo_no[bc], lo_yes = K.lo_yes[bc], hi_no = K.hi_no[bc], hi_yes = K.hi_yes[bc], lo_no2 = K.lo_no2[bc];
     {
-        constexpr int NG = SM_W / 4;
-        for (int t = tid; t < SM_H * NG; t += SC_NT) {
-            const int r = t / NG, g = t - r * NG;
-            float s[3][6];
+        // a thread slides down five rows of a group of four columns: every row of S is loaded once (6 floats) and its
+        // horizontal differences computed once for the three result rows that use it
+        constexpr int NG = SM_W / 4, SEG5 = 5, NS5 = (SM_H + SEG5 - 1) / SEG5;       // 33 x 7 = 231 tasks
+        static_assert(NG * NS5 <= SC_NT, "one round");
+        const om_f32x2 NEG1 = om_pack2(-1.0f, -1.0f), TWO = om_pack2(2.0f, 2.0f);
+        for (int t = tid; t < NG * NS5; t += SC_NT) {
+            const int sg = t / NG, g = t - sg * NG;
+            const int r0 = sg * SEG5, nr = min(SEG5, SM_H - r0);
+            om_f32x2 spa[3], spb[3], ea[2], eb[2];          // rows r, r + 1 of S: column pairs, right - left of the pixel pairs
             #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float4 a = *reinterpret_cast<const float4*>(&S[(r + k) * SS_W + 4 * g]);
-                // (the last group reads two floats past the row: finite values of the next row / the V buffer, for the
-                //  unused columns 130, 131)
-                const float2 c = *reinterpret_cast<const float2*>(&S[(r + k) * SS_W + 4 * g + 4]);
-                s[k][0] = a.x; s[k][1] = a.y; s[k][2] = a.z; s[k][3] = a.w; s[k][4] = c.x; s[k][5] = c.y;
-            }
-            // packed pairs where the operands are natural register pairs (columns 2p, 2p + 1)
-            om_f32x2 sp[3][3];
-            #pragma unroll
-            for (int k = 0; k < 3; ++k)
-                #pragma unroll
-                for (int p2 = 0; p2 < 3; ++p2) sp[k][p2] = om_pack2(s[k][2 * p2], s[k][2 * p2 + 1]);
-            const om_f32x2 NEG1 = om_pack2(-1.0f, -1.0f), TWO = om_pack2(2.0f, 2.0f);
-            float dc[6], o[4];
-            #pragma unroll
-            for (int p2 = 0; p2 < 3; ++p2) om_unpack2(om_fma2(sp[0][p2], NEG1, sp[2][p2]), dc[2 * p2], dc[2 * p2 + 1]);   // down - up
-            om_f32x2 js2[2];
-            #pragma unroll
-            for (int p2 = 0; p2 < 2; ++p2) {                   // e[k] = right - left for the pixel pairs (0,1), (2,3)
-                const om_f32x2 e0 = om_fma2(sp[0][p2], NEG1, sp[0][p2 + 1]), e1 = om_fma2(sp[1][p2], NEG1, sp[1][p2 + 1]);
-                const om_f32x2 e2 = om_fma2(sp[2][p2], NEG1, sp[2][p2 + 1]);
-                js2[p2] = om_add2(om_fma2(TWO, e1, e0), e2);
-            }
-            #pragma unroll
-            for (int p2 = 0; p2 < 2; ++p2) {
-                const float is0 = fmaf(2.0f, dc[2 * p2 + 1], dc[2 * p2]) + dc[2 * p2 + 2];
-                const float is1 = fmaf(2.0f, dc[2 * p2 + 2], dc[2 * p2 + 1]) + dc[2 * p2 + 3];
-                const om_f32x2 is2 = om_pack2(is0, is1);
-                om_unpack2(om_fma2(is2, is2, om_mul2(js2[p2], js2[p2])), o[2 * p2], o[2 * p2 + 1]);
-            }
-            *reinterpret_cast<float4*>(&M2[r * SM_W + 4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
-            if (fmaxf(fmaxf(o[0], o[1]), fmaxf(o[2], o[3])) >= lo_no2 && r >= 1 && r <= SC_H) {
-                // the four pixels j = 4g - 1 .. 4g + 2 of tile row i as bits of one 64-bit window (they may straddle a word)
-                const int i = r - 1, y = y0 + i, j0 = 4 * g - 1;
-                uint32_t nib = (o[0] >= lo_no2 ? 1u : 0u) | (o[1] >= lo_no2 ? 2u : 0u) | (o[2] >= lo_no2 ? 4u : 0u) | (o[3] >= lo_no2 ? 8u : 0u);
-                if (j0 < 0) nib &= ~1u;                         // column -1 is halo
-                if (j0 + 3 >= SC_W) nib &= (1u << (SC_W - j0)) - 1u;     // columns >= SC_W are halo
-                if (border) {                                   // eroded_mask: the 1-pixel border of the image never qualifies
-                    if (y < 1 || y > H - 2) nib = 0u;
+            for (int k = 0; k < SEG5 + 2; ++k) {
+                if (k < nr + 2) {
+                    // (the last group reads two floats past the row: finite values of the next row / the V buffer, for
+                    //  the unused columns 130, 131)
+                    const float4 a = *reinterpret_cast<const float4*>(&S[(r0 + k) * SS_W + 4 * g]);
+                    const float2 c = *reinterpret_cast<const float2*>(&S[(r0 + k) * SS_W + 4 * g + 4]);
+                    om_f32x2 sp[3], e[2];
+                    sp[0] = om_pack2(a.x, a.y); sp[1] = om_pack2(a.z, a.w); sp[2] = om_pack2(c.x, c.y);
+                    e[0] = om_fma2(sp[0], NEG1, sp[1]); e[1] = om_fma2(sp[1], NEG1, sp[2]);
+                    if (k >= 2) {
+                        const int r = r0 + k - 2;           // result row: S rows r (a), r + 1 (b), r + 2 (this one)
+                        float dc[6], o[4];
+                        #pragma unroll
+                        for (int p2 = 0; p2 < 3; ++p2) om_unpack2(om_fma2(spa[p2], NEG1, sp[p2]), dc[2 * p2], dc[2 * p2 + 1]);   // down - up
+                        #pragma unroll
+                        for (int p2 = 0; p2 < 2; ++p2) {
+                            const om_f32x2 js2 = om_add2(om_fma2(TWO, eb[p2], ea[p2]), e[p2]);
+                            const float is0 = fmaf(2.0f, dc[2 * p2 + 1], dc[2 * p2]) + dc[2 * p2 + 2];
+                            const float is1 = fmaf(2.0f, dc[2 * p2 + 2], dc[2 * p2 + 1]) + dc[2 * p2 + 3];
+                            const om_f32x2 is2 = om_pack2(is0, is1);
+                            om_unpack2(om_fma2(is2, is2, om_mul2(js2, js2)), o[2 * p2], o[2 * p2 + 1]);
+                        }
+                        *reinterpret_cast<float4*>(&M2[r * SM_W + 4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
+                        if (fmaxf(fmaxf(o[0], o[1]), fmaxf(o[2], o[3])) >= lo_no2 && r >= 1 && r <= SC_H) {
+                            // the four pixels j = 4g - 1 .. 4g + 2 of tile row i as bits of one 64-bit window (they may straddle a word)
+                            const int i = r - 1, y = y0 + i, j0 = 4 * g - 1;
+                            uint32_t nib = (o[0] >= lo_no2 ? 1u : 0u) | (o[1] >= lo_no2 ? 2u : 0u) | (o[2] >= lo_no2 ? 4u : 0u) | (o[3] >= lo_no2 ? 8u : 0u);
+                            if (j0 < 0) nib &= ~1u;                         // column -1 is halo
+                            if (j0 + 3 >= SC_W) nib &= (1u << (SC_W - j0)) - 1u;     // columns >= SC_W are halo
+                            if (border) {                                   // eroded_mask: the 1-pixel border of the image never qualifies
+                                if (y < 1 || y > H - 2) nib = 0u;
+                                #pragma unroll
+                                for (int q = 0; q < 4; ++q) { const int x = x0 + j0 + q; if (x < 1 || x > W - 2) nib &= ~(1u << q); }
+                            }
+                            if (nib) {
+                                const int jb = max(j0, 0);                   // first valid column of the window
+                                const uint32_t bits = (j0 < 0) ? (nib >> 1) : nib;
+                                const int w0 = jb >> 5, sh = jb & 31;
+                                atomicOr(&sm.cand[i * (SC_W / 32) + w0], bits << sh);
+                                if (sh > 28 && (bits >> (32 - sh))) atomicOr(&sm.cand[i * (SC_W / 32) + w0 + 1], bits >> (32 - sh));
+                            }
+                        }
+                    }
                     #pragma unroll
-                    for (int k = 0; k < 4; ++k) { const int x = x0 + j0 + k; if (x < 1 || x > W - 2) nib &= ~(1u << k); }
-                }
-                if (nib) {
-                    const int jb = max(j0, 0);                   // first valid column of the window
-                    const uint32_t bits = (j0 < 0) ? (nib >> 1) : nib;
-                    const int w0 = jb >> 5, sh = jb & 31;
-                    atomicOr(&sm.cand[i * (SC_W / 32) + w0], bits << sh);
-                    if (sh > 28 && (bits >> (32 - sh))) atomicOr(&sm.cand[i * (SC_W / 32) + w0 + 1], bits >> (32 - sh));
+                    for (int p2 = 0; p2 < 3; ++p2) { spa[p2] = spb[p2]; spb[p2] = sp[p2]; }
+                    #pragma unroll
+                    for (int p2 = 0; p2 < 2; ++p2) { ea[p2] = eb[p2]; eb[p2] = e[p2]; }
                 }
             }
         }
