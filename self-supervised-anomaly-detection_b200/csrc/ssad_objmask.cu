@@ -339,12 +339,12 @@ struct C32Smem {
     float V[(SV_H / 2) * SV_P];   // axis-0 pass, rows interleaved in pairs; reused for |gradient|^2
     float ra[SV_H], rb[SS_W];   // 1 / bleed-over along the rows / the columns (border tiles)
     uint32_t cand[SC_H * (SC_W / 32)];   // pixels whose |gradient| may reach the low threshold, one word per 32 pixels of a row
-    uint32_t nword;                      // words with a candidate ...
-    uint16_t words[SC_H * (SC_W / 32)];  // ... and which
+    uint32_t ncand;                      // ... how many: they are listed (i << 8 | j) behind S in the G buffer
+    uint32_t lo_w[SC_H * (SC_W / 32)], hi_w[SC_H * (SC_W / 32)];   // the tile's words of the two planes
     uint32_t sub_cnt[SC_H / 16];
     uint16_t sub_list[SC_H / 16][SUB_CAP];
 };
-static_assert(SV_H * SS_W <= SG_H * SG_W, "S reuses the L buffer");
+static_assert((SV_H * SS_W + 2) * 4 + SC_H * SC_W * 2 <= SG_H * SG_W * 4, "S and the candidate list reuse the L buffer");
 
 __device__ __forceinline__ uint32_t om_dp2a_lo(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t d;
@@ -411,8 +411,8 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     const bool border = (x0 - 8 < 6) || (y0 - 8 < 6) || (x0 + SC_W + 8 > W - 6) || (y0 + SC_H + 8 > H - 6);
 
     if (tid < SC_H / 16) sm.sub_cnt[tid] = 0u;
-    if (tid == 32) sm.nword = 0u;
-    if (tid < SC_H * (SC_W / 32)) sm.cand[tid] = 0u;
+    if (tid == 32) sm.ncand = 0u;
+    if (tid < SC_H * (SC_W / 32)) { sm.cand[tid] = 0u; sm.lo_w[tid] = 0u; sm.hi_w[tid] = 0u; }
     static_assert(SC_H * (SC_W / 32) <= SC_NT, "one thread per candidate word");
     if (border) {
         // gaussian_filter(ones): the taps that fall inside the image, per row and per column of the tile
@@ -430,28 +430,32 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     // ---- L (Convert.c), four pixels = three words per task; 0 outside the image (mode='constant')
     {
         const bool vec_ok = ((src_pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
-        constexpr int NG = SG_W / 4, NTASK = SG_H * NG, NR = (NTASK + SC_NT - 1) / SC_NT;
-        uint32_t w[NR][3];
+        // a thread keeps one group of four columns and takes every RS-th row: one division per thread, pointers and
+        // shared-memory offsets advance by constants
+        constexpr int NG = SG_W / 4, RS = SC_NT / NG, NK = (SG_H + RS - 1) / RS;
+        static_assert(RS >= 1, "a row of groups per pass");
+        const int rr = tid / NG, g = tid - rr * NG;
+        const bool active = rr < RS;                       // (the last SC_NT - RS * NG threads repeat rows of others, unstored)
+        uint32_t w[NK][3];
         const bool inside = vec_ok && x0 >= 8 && y0 >= 8 && x0 + SC_W + 8 <= W && y0 + SC_H + 8 <= H;   // (uniform)
         if (inside) {
-            // every pixel of the tile and its halo is in the image: no bounds, one pointer per task
-            const uint8_t* const base = img + (size_t)(y0 - 8) * src_pitch + (size_t)(x0 - 8) * 3;
+            // every pixel of the tile and its halo is in the image: no bounds
+            const uint8_t* const base = img + (size_t)(y0 - 8) * src_pitch + (size_t)(x0 - 8) * 3 + g * 12;
             #pragma unroll
-            for (int k = 0; k < NR; ++k) {
-                const int t = min(tid + k * SC_NT, NTASK - 1);
-                const int r = t / NG, g = t - r * NG;
-                const uint32_t* q = reinterpret_cast<const uint32_t*>(base + (size_t)r * src_pitch + g * 12);
+            for (int k = 0; k < NK; ++k) {
+                const int r = min(rr + k * RS, SG_H - 1);
+                const uint32_t* q = reinterpret_cast<const uint32_t*>(base + (size_t)r * src_pitch);
                 w[k][0] = __ldg(q); w[k][1] = __ldg(q + 1); w[k][2] = __ldg(q + 2);
             }
         } else {
+            const int x = x0 - 8 + 4 * g;
+            const bool xany = x + 3 >= 0 && x < W, xfull = vec_ok && x >= 0 && x + 3 < W;
             #pragma unroll
-            for (int k = 0; k < NR; ++k) {
-                const int t = tid + k * SC_NT;
-                const int r = t / NG, g = t - r * NG;
-                const int y = y0 - 8 + r, x = x0 - 8 + 4 * g;
+            for (int k = 0; k < NK; ++k) {
+                const int r = rr + k * RS, y = y0 - 8 + r;
                 w[k][0] = w[k][1] = w[k][2] = 0u;
-                if (t < NTASK && y >= 0 && y < H && x + 3 >= 0 && x < W) {
-                    if (vec_ok && x >= 0 && x + 3 < W) {
+                if (active && r < SG_H && y >= 0 && y < H && xany) {
+                    if (xfull) {
                         const uint32_t* q = reinterpret_cast<const uint32_t*>(img + (size_t)y * src_pitch + (size_t)x * 3);
                         w[k][0] = __ldg(q); w[k][1] = __ldg(q + 1); w[k][2] = __ldg(q + 2);
                     } else {
@@ -471,9 +475,9 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
             }
         }
         #pragma unroll
-        for (int k = 0; k < NR; ++k) {
-            const int t = tid + k * SC_NT;
-            if (t < NTASK) *reinterpret_cast<float4*>(&sm.G[4 * t]) = luma4(w[k][0], w[k][1], w[k][2]);     // (an all-zero group gives L = 0)
+        for (int k = 0; k < NK; ++k) {
+            const int r = rr + k * RS;
+            if (active && r < SG_H) *reinterpret_cast<float4*>(&sm.G[(r * NG + g) * 4]) = luma4(w[k][0], w[k][1], w[k][2]);     // (an all-zero group gives L = 0)
         }
     }
     __syncthreads();
@@ -628,32 +632,25 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
     }
     __syncthreads();
 
-    // ---- words without a candidate: both planes are zero there (one thread per word); the others are listed
+    // ---- the candidates, listed (any order): one thread per pixel below instead of one warp per 32-pixel word, of which
+    // only the few candidate lanes would work
+    uint16_t* const clist = reinterpret_cast<uint16_t*>(sm.G + SV_H * SS_W + 2);     // (S's last row is read 2 floats past its end)
     if (tid < SC_H * (SC_W / 32)) {
-        if (sm.cand[tid] == 0u) {
-            const int i = tid >> 2, xw = (x0 >> 5) + (tid & 3), y = y0 + i;
-            if (y < H && xw < nw) {
-                low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
-                high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = 0u;
-            }
-        } else {
-            sm.words[atomicAdd(&sm.nword, 1u)] = (uint16_t)tid;
+        uint32_t cw = sm.cand[tid];
+        if (cw) {
+            uint32_t pos = atomicAdd(&sm.ncand, (uint32_t)__popc(cw));
+            const uint32_t ij = (uint32_t)((tid >> 2) << 8) | (uint32_t)((tid & 3) * 32);
+            for (; cw; cw &= cw - 1) clist[pos++] = (uint16_t)(ij + (__ffs(cw) - 1));
         }
     }
     __syncthreads();
-    // ---- thresholds and non-maximum suppression of the candidates, decided in float32 where the error bounds allow; a
-    // warp owns 32 pixels of a row and writes their word of the two planes
+    // ---- thresholds and non-maximum suppression of the candidates, decided in float32 where the error bounds allow
     {
-        const int lane = tid & 31, warp = tid >> 5;
-        const int nword = (int)sm.nword;
-        for (int k = warp; k < nword; k += SC_NT / 32) {
-            const int task = sm.words[k];
-            const uint32_t cw = sm.cand[task];
-            const int i = task >> 2, q = task & 3;
-            const int j = q * 32 + lane;
-            const int y = y0 + i;
+        const int ncand = (int)sm.ncand;
+        for (int k = tid; k < ncand; k += SC_NT) {
+            const int i = clist[k] >> 8, j = clist[k] & 255;
             bool lo = false, hi = false, undecided = false;
-            if ((cw >> lane) & 1u) {
+            {
                 const float m = __fsqrt_rn(M2[(i + 1) * SM_W + (j + 1)]);       // (the thresholds want the correctly rounded root)
                 if (m >= lo_no) {
                     undecided = m < lo_yes;
@@ -699,15 +696,18 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
                 const uint32_t pos = atomicAdd(&sm.sub_cnt[sub], 1u);
                 if (pos < (uint32_t)K.sub_cap) sm.sub_list[sub][pos] = (uint16_t)((i << 8) | j);
             }
-            const uint32_t wl = __ballot_sync(0xFFFFFFFFu, lo), wh = __ballot_sync(0xFFFFFFFFu, hi);
-            const int xw = (x0 >> 5) + q;
-            if (lane == 0 && y < H && xw < nw) {
-                low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = wl;
-                high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = wh;
-            }
+            if (lo) atomicOr(&sm.lo_w[i * (SC_W / 32) + (j >> 5)], 1u << (j & 31));
+            if (hi) atomicOr(&sm.hi_w[i * (SC_W / 32) + (j >> 5)], 1u << (j & 31));
         }
     }
     __syncthreads();
+    if (tid < SC_H * (SC_W / 32)) {                  // the tile's words of both planes, zero where nothing qualified
+        const int xw = (x0 >> 5) + (tid & 3), y = y0 + (tid >> 2);
+        if (y < H && xw < nw) {
+            low_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = sm.lo_w[tid];
+            high_plane[(size_t)b * plane_stride + (size_t)y * nw + xw] = sm.hi_w[tid];
+        }
+    }
     // ---- the undecided pixels of every 64x32 tile: listed for canny_resolve_kernel, or the whole tile to the dense
     // float64 kernel when there are too many (or the list is full)
     {
