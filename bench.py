@@ -37,7 +37,7 @@ METRIC, UNIT = "synthetic_anomaly_images_per_sec", "images/s"
 DEFAULT_BATCH = {1: 96, 2: 512, 3: 1024, 4: 1024, 5: 512}
 KERNELS = {
     "generate": "ssad_generate: plan, lists, pass1, canvas, finish, pass2 (_v7_kernel), timed as one step",
-    "obj_mask": "ssad_obj_mask (canny_screen, canny_tiles, canny_nms, mask_planes) + ssad_generate (6 _v7_kernel), timed as one step",
+    "obj_mask": "ssad_obj_mask (canny32, canny_nms, canny_resolve, mask_planes) + ssad_generate (6 _v7_kernel), timed as one step",
 }
 
 

@@ -917,40 +917,67 @@ struct Plane {
 };
 
 // Grow R (subset of M) to everything 8-connected to it through M.  COMPLEMENT: M = ~plane & rowmask.
-// The rows of the image are cut into one band per warp of the CTA; a round = every warp sweeps its band down and up
-// (one row step floods a whole row, see flood_row), entering with the neighbouring bands' boundary rows as they are;
-// rounds repeat until no warp changed anything.  R only grows, so reading a neighbour's row while it is being
-// rewritten costs at most another round.  Every thread of the CTA must call this.
+// The rows of the image are cut into one band per warp of the CTA.  A warp brings its band to a fixed point on its own --
+// sweeps down and up (one row step floods a whole row, see flood_row) until a sweep changes nothing -- with the
+// neighbouring bands' boundary rows as it read them; a round ends at a CTA barrier.  In the following rounds a band that
+// is at its fixed point only looks at the two boundary rows again: unchanged -> nothing to do; changed -> changes can
+// only run inwards from that edge, so the sweep stops at the first row it leaves as it was, and the band iterates again
+// only if something did change.  Rounds repeat until no warp changed anything (then every boundary row read in that
+// round was final).  R only grows, so reading a neighbour's row while it is being rewritten costs at most another round.
+// Every thread of the CTA must call this.  Returns the number of rounds.
 template <bool COMPLEMENT>
-__device__ void reach(const Plane& Mp, const Plane& Rp, int H, int ylo, int yhi, uint32_t rowmask, int lane) {
-    bool first = true;
-    for (;;) {
+__device__ int reach(const Plane& Mp, const Plane& Rp, int H, int ylo, int yhi, uint32_t rowmask, int lane) {
+    bool first = true, settled = false;
+    uint32_t seen_top = 0u, seen_bot = 0u;            // the neighbours' boundary rows as last read
+    // one sweep over the band from its first (dir 0) or last (dir 1) row, `prev` = the row before it.  EDGE: the band is
+    // at its fixed point, stop at the first row that does not change.
+    auto sweep = [&](int dir, uint32_t prev, bool edge) -> bool {
+        const int step = dir == 0 ? 1 : -1, n = yhi - ylo + 1;
+        int y = dir == 0 ? ylo : yhi;
+        bool ch = false;
+        uint32_t Mn = Mp.ld(y), Rn = Rp.ld(y);
+        #pragma unroll 1
+        for (int i = 0; i < n; ++i, y += step) {
+            const uint32_t M = COMPLEMENT ? (~Mn & rowmask) : Mn;
+            const uint32_t R = Rn;
+            if (i + 1 < n) { Mn = Mp.ld(y + step); Rn = Rp.ld(y + step); }      // next row is in flight during the step
+            const uint32_t S = R | (M & spread3(prev, lane));
+            uint32_t Rnew = R;
+            // (the very first sweep floods every row that holds a seed at all: R has not been spread inside its rows yet)
+            if (__any_sync(FULL, first ? S != 0u : S != R)) {
+                Rnew = flood_row(M, S, lane);
+                if (Rnew != R) { Rp.st(y, Rnew); ch = true; }
+            } else if (edge) {
+                break;
+            }
+            prev = Rnew;
+        }
+        return __any_sync(FULL, ch);
+    };
+    for (int rounds = 1;; ++rounds) {
         bool changed = false;
         if (ylo <= yhi) {
-            #pragma unroll 1
-            for (int dir = 0; dir < 2; ++dir) {
-                const int step = dir == 0 ? 1 : -1, n = yhi - ylo + 1;
-                int y = dir == 0 ? ylo : yhi;
-                uint32_t prev = 0;
-                if (dir == 0 ? (ylo > 0) : (yhi + 1 < H)) prev = Rp.ldcg(y - step);
-                uint32_t Mn = Mp.ld(y), Rn = Rp.ld(y);
-                #pragma unroll 1
-                for (int i = 0; i < n; ++i, y += step) {
-                    const uint32_t M = COMPLEMENT ? (~Mn & rowmask) : Mn;
-                    const uint32_t R = Rn;
-                    if (i + 1 < n) { Mn = Mp.ld(y + step); Rn = Rp.ld(y + step); }      // next row is in flight during the step
-                    const uint32_t S = R | (M & spread3(prev, lane));
-                    uint32_t Rnew = R;
-                    if (first || __any_sync(FULL, S != R)) {
-                        Rnew = flood_row(M, S, lane);
-                        if (Rnew != R) { Rp.st(y, Rnew); changed = true; }
-                    }
-                    prev = Rnew;
+            const uint32_t top = ylo > 0 ? Rp.ldcg(ylo - 1) : 0u, bot = yhi + 1 < H ? Rp.ldcg(yhi + 1) : 0u;
+            const bool same = __all_sync(FULL, top == seen_top && bot == seen_bot);
+            seen_top = top; seen_bot = bot;
+            bool work = !settled;
+            if (settled && !same) {
+                const bool c0 = sweep(0, top, true), c1 = sweep(1, bot, true);
+                work = c0 || c1;
+                changed = work;
+            }
+            if (work) {
+                // to the band's own fixed point: a sweep that changes nothing right after one in the other direction
+                for (int k = 0;; ++k) {
+                    const bool ch = sweep(k & 1, (k & 1) ? bot : top, false);
+                    first = false;
+                    changed = changed || ch;
+                    if (!ch && k >= 1) break;
                 }
-                first = false;
+                settled = true;
             }
         }
-        if (!__syncthreads_or(changed ? 1 : 0)) break;
+        if (!__syncthreads_or(changed ? 1 : 0)) return rounds;
     }
 }
 
@@ -1170,7 +1197,7 @@ __device__ bool largest_component_runs(const Plane& P0, const Plane& OUT, int H,
 }
 
 // One CTA per image, one band of rows per warp, one lane per 32-pixel word of a row.
-__global__ void __launch_bounds__(32 * SSAD_PLANES_WARPS)
+__global__ void __launch_bounds__(32 * SSAD_PLANES_WARPS, 3)
 mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, long long plane_words,
                    uint32_t* __restrict__ mask_bits, int mask_pitch_words, long long mask_stride_words, int ccl_cap) {
     __shared__ int s_first, s_cnt;
@@ -1194,6 +1221,9 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
 #define SSAD_TICK(i)
 #endif
     // 1. hysteresis: edges = pixels of the low plane 8-connected to a pixel of the high plane (P0 = low, P1 = high -> edges)
+#ifdef SSAD_PLANES_TIMING
+    const int rounds_h =
+#endif
     reach<false>(P0, P1, H, ylo, yhi, rowmask, lane);
     SSAD_TICK(1);
 
@@ -1236,6 +1266,9 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
     __syncthreads();
     SSAD_TICK(2);
     // 4b. binary_fill_holes: background reachable from outside the image through ~C (8-connected); filled = the rest
+#ifdef SSAD_PLANES_TIMING
+    const int rounds_f =
+#endif
     reach<true>(P0, P2, H, ylo, yhi, rowmask, lane);
     SSAD_TICK(3);
     // 5. binary_erosion(4x4), origin 0: offsets -2..+1 in both axes; P0 = erode4(~P2)
@@ -1272,8 +1305,8 @@ mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, l
 #ifdef SSAD_PLANES_TIMING
         SSAD_TICK(5);
         if (threadIdx.x == 0 && (b % 128) == 0)
-            printf("planes b=%d hyst %lld closing %lld fill %lld erode %lld runs %lld total %lld\n", b, tk[1] - tk[0],
-                   tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[5] - tk[0]);
+            printf("planes b=%d hyst %lld (%d rounds) closing %lld fill %lld (%d rounds) erode %lld runs %lld total %lld\n", b, tk[1] - tk[0],
+                   rounds_h, tk[2] - tk[1], tk[3] - tk[2], rounds_f, tk[4] - tk[3], tk[5] - tk[4], tk[5] - tk[0]);
 #endif
         return;
     }
