@@ -36,7 +36,9 @@ enum {
     SSAD_EALIGN = -2,       /* pointer / pitch not aligned as required */
     SSAD_EUNSUPPORTED = -3, /* valid request this build cannot serve (e.g. image too large for the fused path) */
     SSAD_ELAUNCH = -4,      /* CUDA launch / attribute error (cudaGetLastError text via ssad_last_cuda_error) */
-    SSAD_EWORKSPACE = -5    /* workspace too small */
+    SSAD_EWORKSPACE = -5,   /* workspace too small */
+    SSAD_ESTATIC = -6       /* request needs more scratch than the library's static device array holds
+                               (ssad_obj_mask_static: SSAD_OBJ_MASK_STATIC_BYTES) */
 };
 
 /* mask_mode */
@@ -203,6 +205,23 @@ void ssad_obj_mask_test_knobs(float margin_scale, int32_t sub_cap, int32_t pix_p
  * `max_runs` of them (default and maximum 4096), by peeling flooded components otherwise; 0 always takes the second
  * path, out of range restores the default.  The masks must not depend on it. */
 void ssad_obj_mask_test_runs(int32_t max_runs);
+
+/* ssad_obj_mask without a caller workspace and without any allocation.  (No counterpart in the reference: added
+ * for callers that cannot allocate device memory -- code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc.)  Same arguments, same kernels and bit-identical masks as
+ * ssad_obj_mask; the scratch (bit planes, undecided-pixel / tile lists, counters) lives in ONE file-scope
+ * `static __device__` array of SSAD_OBJ_MASK_STATIC_BYTES inside the library, which every GPU that loads the library
+ * holds until the process exits.  The call makes no cudaMalloc / cudaFree and calls no allocating library routine.
+ *  - Limit: ssad_obj_mask_workspace(batch, height, width) <= SSAD_OBJ_MASK_STATIC_BYTES (16 MiB: e.g. 36 images of
+ *    1024x1024, 290 of 256x256); a larger request returns SSAD_ESTATIC and launches nothing.
+ *  - All calls on a device share the array.  It keeps the previous call's contents; the call clears the two counters
+ *    it needs at zero itself, every other word is written before it is read.  Calls that overlap on the GPU (two
+ *    streams, two host threads, or graphs replayed concurrently) race on it: serialise them, or use ssad_obj_mask
+ *    with one workspace per stream. */
+#define SSAD_OBJ_MASK_STATIC_BYTES (16u << 20)
+int ssad_obj_mask_static(int32_t batch, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
+                         int64_t src_stride, const SsadCannyConsts* consts /* host */, uint32_t* mask_bits,
+                         int32_t mask_pitch_words, int64_t mask_stride_words, void* stream);
 
 /* Unit entry points (parity tests of the individual reference routines). */
 

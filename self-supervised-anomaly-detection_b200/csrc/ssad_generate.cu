@@ -40,6 +40,8 @@ extern "C" const char* ssad_strerror(int code) {
         case SSAD_EUNSUPPORTED: return "unsupported configuration for this build";
         case SSAD_ELAUNCH: return "CUDA launch failed";
         case SSAD_EWORKSPACE: return "workspace too small";
+        case SSAD_ESTATIC: return "request needs more scratch than the static device array holds (SSAD_OBJ_MASK_STATIC_BYTES = 16 MiB): "
+                                  "use ssad_obj_mask with a caller workspace, or a smaller batch";
         default: return "unknown error";
     }
 }

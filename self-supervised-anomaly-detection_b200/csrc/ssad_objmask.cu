@@ -20,6 +20,7 @@
 //                      the carry trick  reach = (M & ~(M + S)) | S  inside a word and a ballot + add carry chain
 //                      across the 32 words, until a sweep pair changes nothing.
 #include <cuda_runtime.h>
+#include <mutex>
 #include <cstdio>
 #include <stdint.h>
 #include <stdlib.h>
@@ -1496,4 +1497,40 @@ extern "C" int ssad_obj_mask(int32_t batch, int32_t height, int32_t width, const
     e = cudaGetLastError();
     if (e != cudaSuccess) return ssad_set_cuda_error(e);
     return SSAD_OK;
+}
+
+// ------------------------------------------------------------------ ssad_obj_mask_static: no caller workspace, no allocation
+// The scratch of ssad_obj_mask in a file-scope device array (include/ssad.h: why, the limit, and the sharing rules).
+// In host code the NAME of the array is a host-side stand-in, not a device address: the address the kernels get comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) unsigned char g_obj_mask_static_scratch[SSAD_OBJ_MASK_STATIC_BYTES];
+
+extern "C" int ssad_obj_mask_static(int32_t batch, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
+                                    int64_t src_stride, const SsadCannyConsts* consts, uint32_t* mask_bits,
+                                    int32_t mask_pitch_words, int64_t mask_stride_words, void* stream) {
+    if (batch < 0 || height <= 0 || width <= 0 || !src || !mask_bits || !consts) return SSAD_EINVAL;
+    if (batch == 0) return SSAD_OK;
+    if (width > 1024 || batch > 65535 || height > 65535) return SSAD_EUNSUPPORTED;      // (keeps the layout arithmetic in range)
+    if (obj_mask_layout(batch, height, width).total > (size_t)SSAD_OBJ_MASK_STATIC_BYTES) return SSAD_ESTATIC;
+    static void* scratch_of[64];                   // device address of the array on every device, asked once
+    static std::mutex mu;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return ssad_set_cuda_error(e);
+    if (dev < 0 || dev >= 64) return SSAD_EUNSUPPORTED;
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!scratch_of[dev]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_obj_mask_static_scratch);       // the current device's copy
+            if (e != cudaSuccess || !p) return ssad_set_cuda_error(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+            scratch_of[dev] = p;
+        }
+        scratch = scratch_of[dev];
+    }
+    // the planes, lists and counters are laid out exactly as in a caller workspace; ssad_obj_mask zeroes the two
+    // counters on the stream (cudaMemsetAsync) and writes every other word before reading it
+    return ssad_obj_mask(batch, height, width, src, src_pitch, src_stride, consts, mask_bits, mask_pitch_words, mask_stride_words,
+                         scratch, (size_t)SSAD_OBJ_MASK_STATIC_BYTES, stream);
 }
