@@ -770,15 +770,28 @@ canny_resolve_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8
         const int b = (int)e.x, y = (int)(e.y >> 16), x = (int)(e.y & 0xFFFFu);
         const uint8_t* img = src + (size_t)b * src_stride;
         __syncwarp();
-        for (int i = lane; i < 17 * 17; i += 32) {
-            const int r = i / 17, c = i - r * 17;
-            const int yy = y - 8 + r, xx = x - 8 + c;
-            double v = 0.0;
-            if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-                const uint8_t* q = img + (size_t)yy * src_pitch + (size_t)xx * 3;
-                v = lut[(19595u * q[0] + 38470u * q[1] + 7471u * q[2] + 0x8000u) >> 16];
+        {
+            // the 17 x 17 window: all byte loads of the lane issued before the first is used (their latency is the
+            // kernel's top stall)
+            constexpr int NR = (17 * 17 + 31) / 32;
+            uint32_t px[NR];
+            #pragma unroll
+            for (int k = 0; k < NR; ++k) {
+                const int i = lane + 32 * k, r = i / 17, c = i - r * 17;
+                const int yy = y - 8 + r, xx = x - 8 + c;
+                px[k] = 0xFFFFFFFFu;
+                if (i < 17 * 17 && yy >= 0 && yy < H && xx >= 0 && xx < W) {
+                    const uint8_t* q = img + (size_t)yy * src_pitch + (size_t)xx * 3;
+                    px[k] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + 1) << 8) | ((uint32_t)__ldg(q + 2) << 16);
+                }
             }
-            R.L[i] = v;
+            #pragma unroll
+            for (int k = 0; k < NR; ++k) {
+                const int i = lane + 32 * k;
+                if (i < 17 * 17)
+                    R.L[i] = px[k] == 0xFFFFFFFFu ? 0.0
+                           : lut[(19595u * (px[k] & 255u) + 38470u * ((px[k] >> 8) & 255u) + 7471u * (px[k] >> 16) + 0x8000u) >> 16];
+            }
         }
         __syncwarp();
         for (int i = lane; i < 5 * 17; i += 32) {
