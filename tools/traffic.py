@@ -55,6 +55,7 @@ def main():
     allt[f"config{config}_{out}"] = res["bytes_per_step"]
     allt.setdefault("detail", {})[f"config{config}_{out}"] = res
     json.dump(allt, open(path, "w"), indent=1)
+    json.dump(allt, open(os.path.join(ROOT, "gpurun_out", "traffic.json"), "w"), indent=1)      # (gpurun merges gpurun_out/ back)
     print(json.dumps({k: v for k, v in res.items() if k != "per_kernel_mb_per_step"}))
     for k, v in res["per_kernel_mb_per_step"].items():
         print(f"  {k:28s} read {v['read']:9.2f} MB  write {v['write']:9.2f} MB  {v['us']:9.1f} us")
