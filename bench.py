@@ -513,6 +513,37 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
     return res
 
 
+def datamodule_rate(rt, items: int = 1000, batch: int = 96, epochs: int = 3) -> dict:
+    """VERDICT item 4 / datasets.py:501-508: what replaces ``DataLoader(PretextTaskDataset, batch_size=96, shuffle=True,
+    num_workers=8)`` -- one epoch of ``BatchLoader`` over a device-resident ``PretextTaskDataset`` of 1000 items (40
+    distinct synthetic images, duplicated as ``duplicate_filenames`` does), records drawn by the host sampler on the
+    loader's background thread, float32 NCHW tensors + labels (+ the originals, as the reference returns them)."""
+    import torch
+    from ssad_b200 import synth
+    from ssad_b200.datasets import BatchLoader, PretextTaskDataset
+    dev = rt["dev"]
+    S = 256
+    base = synth.object_images(40, S, S, 4242)
+    ds = PretextTaskDataset("bottle", imsize=(S, S), images=base, fixed_segmentation=synth.disc_mask(S, S, 0.4), device=dev,
+                            seed=7 + rt["rank"], dataset_dir="/nonexistent/")
+    ds.images_filenames = np.arange(items)                 # 1000 items over the 40 resident images
+    ds.index = np.arange(items) % len(base)
+    loader = BatchLoader(ds, batch, shuffle=True, drop_last=True)
+    n = 0
+    for b in loader:                                       # warm-up epoch (workspace, contexts)
+        n += 1
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    seen = 0
+    for _ in range(epochs):
+        for b in loader:
+            seen += int(b[1].shape[0])
+    torch.cuda.synchronize(dev)
+    dt = time.perf_counter() - t0
+    return {"value": seen / dt, "unit": UNIT, "items": items, "batch": batch, "batches_per_epoch": n, "epochs": epochs,
+            "what": "PretextTaskDataset (device-resident) + BatchLoader, shuffle, drop_last, host sampler included, float32 NCHW + labels"}
+
+
 def roofline_of(res: dict, peaks: dict, traffic: dict) -> dict:
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = res["batch"] * res["ab"] / (res["ms_per_step"] * 1e-3) / 1e9      # per GPU: one step = one batch
@@ -624,6 +655,10 @@ def main():
             r = run_config(c, args, rt, max(steps, 200), 10, args.verify)
             per_config[str(c)] = r
         try:
+            per_config["datamodule"] = datamodule_rate(rt)
+        except Exception as e:
+            per_config["datamodule"] = {"error": f"{type(e).__name__}: {e}"}
+        try:
             from ssad_b200 import trainer_feed
             per_config["5"] = trainer_feed.measure(args, rt, make_workload, steps=20, warmup=5)
         except Exception as e:                    # the trainer feed needs torchvision's ResNet-18; report, do not hide
@@ -660,6 +695,9 @@ def main():
     if per_config:
         pc = {}
         for k, r in per_config.items():
+            if k == "datamodule":
+                line["datamodule"] = r
+                continue
             if "ms_per_step" not in r or k == "5":
                 pc[k] = r
                 continue
