@@ -109,6 +109,10 @@ __device__ __forceinline__ void sobel_at(const double* S, int y, int x, int y0, 
 #ifndef SSAD_PLANES_ROWS
 #define SSAD_PLANES_ROWS 64
 #endif
+// resident CTAs per SM the plane kernel is compiled for (3 x 512 threads = 40 registers per thread)
+#ifndef SSAD_PLANES_MINB
+#define SSAD_PLANES_MINB 3
+#endif
 
 __global__ void __launch_bounds__(CT_NT, SSAD_CANNY_MINB)
 canny_nms_kernel(const __grid_constant__ CannyK K, int H, int W, const uint8_t* __restrict__ src, long long src_pitch,
@@ -1211,7 +1215,7 @@ __device__ bool largest_component_runs(const Plane& P0, const Plane& OUT, int H,
 }
 
 // One CTA per image, one band of rows per warp, one lane per 32-pixel word of a row.
-__global__ void __launch_bounds__(32 * SSAD_PLANES_WARPS, 3)
+__global__ void __launch_bounds__(32 * SSAD_PLANES_WARPS, SSAD_PLANES_MINB)
 mask_planes_kernel(int batch, int H, int W, int nw, uint32_t* __restrict__ ws, long long plane_words,
                    uint32_t* __restrict__ mask_bits, int mask_pitch_words, long long mask_stride_words, int ccl_cap) {
     __shared__ int s_first, s_cnt;
