@@ -295,30 +295,37 @@ def _restore_affinity():
 
 
 class ParamPrefetcher:
-    """Draws the next batch of parameter records on a background thread while the current batch runs (the host
-    sampler is part of the end-to-end path: SURVEY.md section 8d/8e)."""
+    """Draws the parameter records on a background thread while the current batch runs (the host sampler is part of the
+    end-to-end path: SURVEY.md section 8d/8e).  Small batches are drawn several at a time (one call of the sampler costs
+    ~60 NumPy calls whatever the batch) and handed out as slices; every step still gets records nobody has used."""
+    POOL = 2048
 
     def __init__(self, cfg, batch, seed):
         from ssad_b200 import sample_params
         self.cfg, self.batch, self.rng, self.sample = cfg, batch, np.random.default_rng(seed), sample_params
+        self.per_pool = max(1, self.POOL // batch)
         self.busy_s, self.n = 0.0, 0
         self._next, self._thread = None, None
+        self._cur, self._used = None, 0
         self._start()
 
     def _work(self):
         t0 = time.perf_counter()
-        self._next = self.sample(self.cfg, self.batch, self.rng)
+        self._next = self.sample(self.cfg, self.batch * self.per_pool, self.rng)
         self.busy_s += time.perf_counter() - t0
-        self.n += self.batch
+        self.n += self.batch * self.per_pool
 
     def _start(self):
         self._thread = threading.Thread(target=self._work, daemon=True)
         self._thread.start()
 
     def get(self):
-        self._thread.join()
-        p = self._next
-        self._start()
+        if self._cur is None or self._used == self.per_pool:
+            self._thread.join()
+            self._cur, self._used = self._next, 0
+            self._start()
+        p = self._cur if self.per_pool == 1 else self._cur.slice(self._used * self.batch, (self._used + 1) * self.batch)
+        self._used += 1
         return p
 
     def close(self):
@@ -482,7 +489,7 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
             p = pre.get()                        # this step's records: drawn while the previous step was being issued
             t_in = time.perf_counter()
             pending[j] = gen.generate_from_host(h_src[j], p, h_outs[j], h_ys[j], chunks=args.e2e_chunks,
-                                                masks_fn=masks_fn, wait=not deep)
+                                                masks_fn=masks_fn, wait=not deep, upload=args.e2e_upload)
             host_s[0] += time.perf_counter() - t_in
 
         for i in range(3):
@@ -608,6 +615,8 @@ def main():
                     "(default: on for a 1-GPU run of the default headline)")
     ap.add_argument("--verify", type=int, default=32, help="images of the timed buffers compared with the CPU oracle (0: off)")
     ap.add_argument("--e2e-steps", type=int, default=None)
+    ap.add_argument("--e2e-upload", default="auto", choices=["auto", "full", "windows"],
+                    help="host-buffer call: whole images up (auto = full), or only the windows a patch-mode call reads")
     ap.add_argument("--e2e-chunks", type=int, default=None, help="pieces of the batch in flight in the host-buffer call")
     ap.add_argument("--inflight", type=int, default=2, help="batches in flight: steps alternate between this many streams (1|2)")
     ap.add_argument("--graph", type=int, default=1, help="1: replay each step's ssad_generate call from a CUDA graph")

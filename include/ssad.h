@@ -270,6 +270,18 @@ int ssad_color_similarity(const uint8_t* image, int32_t n_image, const uint8_t* 
 int ssad_to_tensor(int32_t n, int32_t height, int32_t width, const uint8_t* src, int64_t src_pitch,
                    int64_t src_stride, float* out, void* stream);
 
+/* Patch mode reads only a window of every source image (datasets.py:246-252) and, for labels 1 / 2 on non-texture classes,
+ * the cut rectangle of image_for_cutting (datasets.py:253, dataset_generator.py:172-191).  When the images live in PINNED
+ * host memory the device can address (cudaHostAlloc / torch pin_memory), this kernel fetches exactly those bytes over
+ * PCIe into the device copy `dev_src` (same layout: pitch, stride), instead of a copy of the whole batch.  `params` are
+ * the DEVICE records of the n images (image b of both buffers belongs to record b; crop_off, donor_off, rect, label,
+ * donor_idx are read); max_patch_h bounds rect[3].  host_src, dev_src 16-byte aligned, src_stride a multiple of 16.
+ * Not for records with warp_en (the pre-warp gathers from the whole image) or per-image obj_mask (it needs the whole
+ * image on the device). */
+int ssad_upload_windows(int32_t n, const SsadImageParams* params, const uint8_t* host_src, uint8_t* dev_src, int64_t src_pitch,
+                        int64_t src_stride, int32_t src_height, int32_t src_width, int32_t win_height, int32_t win_width,
+                        int32_t max_patch_h, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

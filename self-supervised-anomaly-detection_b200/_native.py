@@ -59,6 +59,8 @@ EXPORTS = {
     "ssad_obj_mask_launches": (C.c_int, []),
     "ssad_obj_mask_test_knobs": (None, [C.c_float, C.c_int32, C.c_int32]),
     "ssad_obj_mask_test_runs": (None, [C.c_int32]),
+    "ssad_upload_windows": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
+                                      C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "ssad_obj_mask_static": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                        C.c_int32, C.c_int64, C.c_void_p]),
     "ssad_polygon_mask": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),

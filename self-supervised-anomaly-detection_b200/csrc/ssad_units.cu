@@ -123,6 +123,42 @@ __global__ void to_tensor_kernel(int height, int width, const uint8_t* __restric
     o[2 * npix + p] = __fdiv_rn((float)q[2], 255.0f);
 }
 
+// ---- upload of only what a patch-mode call reads of a host image (ssad_upload_windows) -------------------------------
+// src is pinned host memory the device can address; dst the device copy with the same layout.  Per image: the working
+// window (crop_off, win_w x win_h) and, for labels 1 / 2 whose patch comes from the image itself, the cut rectangle
+// (donor_off + rect).  One warp per row segment, 16-byte blocks that cover it (source and destination share their
+// alignment; the few extra bytes either side are the image's own pixels).
+__global__ void __launch_bounds__(256)
+upload_windows_kernel(int n, const SsadImageParams* __restrict__ params, const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                      long long pitch, long long stride, int src_h, int src_w, int win_h, int win_w, int rows) {
+    // a small persistent grid (the launch sizes it): the kernel waits on PCIe, not on SMs, and must leave them to the
+    // generation kernels of the previous piece of the batch that run beside it
+    const int lane = threadIdx.x & 31;
+    const long long nwarp = (long long)gridDim.x * 8, ntask = (long long)n * rows;
+    for (long long t = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); t < ntask; t += nwarp) {
+        const int b = (int)(t / rows), r = (int)(t - (long long)b * rows);
+        const SsadImageParams* const p = params + b;
+        const bool a = r < win_h;
+        int x, y, w;
+        if (a) {
+            x = p->crop_off[0]; y = p->crop_off[1] + r; w = win_w;
+        } else {
+            const bool cut = (p->label == 1 || p->label == 2) && p->donor_idx < 0;
+            if (!cut || r - win_h >= p->rect[3]) continue;
+            x = p->donor_off[0] + p->rect[0]; y = p->donor_off[1] + p->rect[1] + (r - win_h); w = p->rect[2];
+        }
+        if (y < 0 || y >= src_h) continue;
+        const int x0 = max(x, 0), x1 = min(x + w, src_w);
+        if (x1 <= x0) continue;
+        const long long img = (long long)b * stride;
+        const long long lo = ((long long)y * pitch + 3ll * x0) & ~15ll, hi = min(((long long)y * pitch + 3ll * x1 + 15) & ~15ll, stride);
+        const int4* s4 = reinterpret_cast<const int4*>(src + img + lo);
+        int4* d4 = reinterpret_cast<int4*>(dst + img + lo);
+        const int nb = (int)((hi - lo) >> 4);
+        for (int k = lane; k < nb; k += 32) d4[k] = s4[k];
+    }
+}
+
 }  // namespace ssad
 
 #define SSAD_CHECK_LAUNCH()                                   \
@@ -288,6 +324,35 @@ extern "C" int ssad_line_mask(int32_t n, const int16_t* xy, const uint8_t* npts,
     const size_t smem = (size_t)height * ((width + 31) / 32) * 4;
     if (smem > 40 * 1024 || width > 1024) return SSAD_EUNSUPPORTED;
     ssad::line_mask_kernel<<<n, 256, smem, static_cast<cudaStream_t>(stream)>>>(xy, npts, max_pts, line_width, out, width, height);
+    SSAD_CHECK_LAUNCH();
+    return SSAD_OK;
+}
+
+extern "C" int ssad_upload_windows(int32_t n, const SsadImageParams* params, const uint8_t* host_src, uint8_t* dev_src, int64_t src_pitch,
+                                   int64_t src_stride, int32_t src_height, int32_t src_width, int32_t win_height, int32_t win_width,
+                                   int32_t max_patch_h, void* stream) {
+    if (n < 0 || !params || !host_src || !dev_src || src_height <= 0 || src_width <= 0 || win_height <= 0 || win_width <= 0 ||
+        max_patch_h < 0 || src_pitch < 3ll * src_width || src_stride < src_pitch * src_height) return SSAD_EINVAL;
+    if (n == 0) return SSAD_OK;
+    if ((reinterpret_cast<uintptr_t>(host_src) & 15) || (reinterpret_cast<uintptr_t>(dev_src) & 15) || (src_stride & 15)) return SSAD_EALIGN;
+    const int rows = win_height + max_patch_h;
+    static int sm_count[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return ssad_set_cuda_error(e);
+    if (dev < 0 || dev >= 64) return SSAD_EUNSUPPORTED;
+    if (sm_count[dev] == 0) {
+        int k = 0;
+        e = cudaDeviceGetAttribute(&k, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return ssad_set_cuda_error(e);
+        sm_count[dev] = k > 0 ? k : 1;
+    }
+    const long long ntask = (long long)n * rows;
+    long long grid = (ntask + 7) / 8;
+    if (grid > 2ll * sm_count[dev]) grid = 2ll * sm_count[dev];        // two CTAs per SM keep ~2 MB of reads in flight
+    ssad::upload_windows_kernel<<<(unsigned)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(n, params, host_src, dev_src, src_pitch,
+                                                                                             src_stride, src_height, src_width,
+                                                                                             win_height, win_width, rows);
     SSAD_CHECK_LAUNCH();
     return SSAD_OK;
 }

@@ -344,14 +344,20 @@ class BatchGenerator:
 
     # ------------------------------------------------------------------ host buffers in, host buffers out
     def generate_from_host(self, h_src: torch.Tensor, params: ParamBatch, h_out: torch.Tensor, h_y: torch.Tensor, *,
-                           chunks: Optional[int] = None, masks_fn=None, wait: bool = True):
+                           chunks: Optional[int] = None, masks_fn=None, wait: bool = True, upload: str = "auto"):
         """The end-to-end call for data that lives in (pinned) host memory: uint8 images ``h_src`` [B, Hs, Ws, 3] ->
         ``h_out`` uint8 [B, h, w, 3] and labels ``h_y`` int64 [B], all host tensors.  The batch is cut into ``chunks``
         pieces that flow through three streams -- host-to-device copy, generation (``ssad_generate``), device-to-host
         copy -- so the two PCIe directions and the kernels overlap.  Returns when the results are in host memory;
         with ``wait=False`` it returns at once with a ``torch.cuda.Event`` that completes when they are (a loader that
         keeps the next batch in flight: call again with other host buffers, then ``event.synchronize()`` this one).
-        ``masks_fn(d_src_chunk) -> packed masks`` supplies per-image masks (non-fixed classes: ``obj_mask_batch``)."""
+        ``masks_fn(d_src_chunk) -> packed masks`` supplies per-image masks (non-fixed classes: ``obj_mask_batch``).
+        ``upload``: "full" (= "auto") copies every image whole with the copy engine; "windows" fetches only what a
+        patch-mode call reads (the working window and the cut rectangle, ``ssad_upload_windows``: a kernel reads the pinned
+        host memory directly) -- 36 % fewer bytes at BASELINE config 2 and 2.30 ms instead of 3.15 ms for the upload on
+        its own, but with the results travelling the other way at the same time the kernel's reads drop to 30 GB/s and the
+        pair takes as long as the whole-image copy (3.29 vs 3.25 ms, tools/time_upload.py), so it is opt-in: for callers
+        whose results stay on the device.  Needs patch mode, no pre-warp, no per-image ``obj_mask``."""
         B = int(h_src.shape[0])
         W, H = self.cfg.work_size
         if chunks is None:
@@ -377,6 +383,14 @@ class BatchGenerator:
                 raise ValueError("label-3 records with per-image device masks: call params.resolve_lines(...) first")
             params.resolve_lines(self._window_mask_fn(rec, None, None))
             rec = np.ascontiguousarray(params.records)
+        Hs, Ws = int(h_src.shape[1]), int(h_src.shape[2])
+        win_ok = (masks_fn is None and self.cfg.patch_localization and not rec["warp_en"].any() and h_src.is_pinned()
+                  and h_src.is_contiguous() and h_src.data_ptr() % 16 == 0 and (Hs * Ws * 3) % 16 == 0)
+        if upload == "windows" and not win_ok:
+            raise ValueError("upload='windows' needs patch mode, pinned contiguous 16-byte aligned host images, no pre-warp and no masks_fn")
+        if upload not in ("auto", "full", "windows"):
+            raise ValueError("upload must be 'auto', 'full' or 'windows'")
+        use_win = upload == "windows"
         st["ev_rec"].synchronize()               # the previous call's upload has left the staging buffer
         st["h_rec"].numpy()[...] = rec.view(np.uint8).reshape(B, IMAGE_PARAMS_DTYPE.itemsize)
         with torch.cuda.stream(st["up"]):
@@ -385,7 +399,13 @@ class BatchGenerator:
         for c, (lo, hi) in enumerate(bounds):
             d_src, d_out, d_y = st["src"][lo:hi], st["out"][lo:hi], st["y"][lo:hi]
             with torch.cuda.stream(st["up"]):
-                d_src.copy_(h_src[lo:hi], non_blocking=True)
+                if use_win:
+                    N.check(self.lib.ssad_upload_windows(hi - lo, C.c_void_p(st["d_rec"][lo:hi].data_ptr()),
+                                                         C.c_void_p(h_src[lo:hi].data_ptr()), C.c_void_p(d_src.data_ptr()),
+                                                         Ws * 3, Hs * Ws * 3, Hs, Ws, H, W, int(hints[2]),
+                                                         C.c_void_p(st["up"].cuda_stream)), "ssad_upload_windows")
+                else:
+                    d_src.copy_(h_src[lo:hi], non_blocking=True)
                 st["ev_up"][c].record(st["up"])
             with torch.cuda.stream(st["run"]):
                 st["run"].wait_event(st["ev_up"][c])

@@ -221,6 +221,41 @@ def test_host_buffer_pipeline_matches_device_call(name, chunks):
     assert torch.equal(h_y, ref["y"].cpu())
 
 
+@pytest.mark.parametrize("name", ["patch_level", "patch_level_32", "lines_patch"])
+def test_host_buffer_pipeline_window_upload_matches_full_upload(name):
+    """generate_from_host(upload="windows"): only the working window and the cut rectangle of every image cross PCIe
+    (ssad_upload_windows reads the pinned host images directly).  Same bytes as the device-resident call -- also when
+    the device staging buffer holds OTHER images from an earlier call everywhere else (a read outside the uploaded
+    regions would show)."""
+    import gpu_utils as U
+    sc = S.build(name, 24)
+    other = S.build(name, 24, seed=5)
+    gen = U.make_generator(sc)
+    ref = U.run_cuda(sc, norm_dtype=None, debug=False, gen=gen)
+    W, H = sc.cfg.work_size
+    h_out = torch.zeros((24, H, W, 3), dtype=torch.uint8).pin_memory()
+    h_y = torch.zeros((24,), dtype=torch.int64).pin_memory()
+    # an earlier call leaves the other scenario's images in the staging buffer
+    gen.generate_from_host(torch.from_numpy(255 - other.images).pin_memory(), other.params, h_out, h_y, chunks=3, upload="full")
+    h_src = torch.from_numpy(sc.images).pin_memory()
+    for mode in ("windows", "full"):
+        h_out.zero_(); h_y.zero_()
+        gen.generate_from_host(h_src, sc.params, h_out, h_y, chunks=3, upload=mode)
+        assert torch.equal(h_out, ref["x_u8"].cpu()), mode
+        assert torch.equal(h_y, ref["y"].cpu()), mode
+
+
+def test_window_upload_is_refused_where_the_whole_image_is_needed():
+    import gpu_utils as U
+    sc = S.build("image_level_256", 12)          # pre-warp: gathers from the whole image
+    gen = U.make_generator(sc)
+    W, H = sc.cfg.work_size
+    h_out = torch.zeros((12, H, W, 3), dtype=torch.uint8).pin_memory()
+    h_y = torch.zeros((12,), dtype=torch.int64).pin_memory()
+    with pytest.raises(ValueError, match="windows"):
+        gen.generate_from_host(torch.from_numpy(sc.images).pin_memory(), sc.params, h_out, h_y, upload="windows")
+
+
 @pytest.mark.gpu
 def test_host_buffer_pipeline_two_batches_in_flight():
     """generate_from_host(wait=False): a second call is issued while the first batch is still on its way; both deliver
