@@ -4,21 +4,26 @@
 //   -> binary_fill_holes(3x3) -> binary_erosion(4x4) -> largest 8-connected component (degenerate: no foreground ->
 //   everything), bit-packed.
 //
-// Four kernels.
-//   canny32_kernel     float32, one CTA per 128x64 tile: the whole canny chain in fast arithmetic; a decision is taken
-//                      only when it clears the proven error of the float32 values, the few undecided pixels (near
-//                      ties) are listed -- or, when a 64x32 tile has too many, the tile.
+// Four kernels (+ ssad_obj_mask_static at the end of the file: the same call with its scratch in a static device array).
+//   canny32_kernel     float32, one CTA per 128x32 tile, four CTAs per SM: the whole canny chain in fast arithmetic
+//                      (L -> Gaussian axis 0 -> axis 1 / bleed-over -> Sobel, |gradient|^2 -> candidates listed ->
+//                      thresholds + non-maximum suppression one candidate per thread); a decision is taken only when
+//                      it clears the proven error of the float32 values, the few undecided pixels (near ties) are
+//                      listed -- or, when a 64x32 tile has too many, the tile.
 //   canny_resolve_kernel  float64, one warp per listed pixel: the reference's operation sequence on the pixel's window.
-//   canny_nms_kernel   float64, dense, the listed 64x32 tiles only (persistent CTAs walking the list): L -> separable Gaussian (scipy correlate1d order: centre tap,
-//                      then the symmetric pairs from the outermost inwards, every product and sum rounded on its own)
-//                      / bleed-over normalisation -> Sobel (reflect) -> magnitude -> bilinear non-maximum suppression
-//                      -> two bit planes (>= low, >= high) written with warp ballots.  FP64-pipe bound: ~125
-//                      non-fusable double operations per pixel (no FMA: the CPU libraries round every op).
-//   mask_planes_kernel one warp per image, one lane per 32-pixel word of a row (W <= 1024): every later step is a
-//                      reachability or a shift on bit planes.  Connectivity (hysteresis, hole filling, component
-//                      extraction) = alternating down / up sweeps; one row step floods a whole row at once with
-//                      the carry trick  reach = (M & ~(M + S)) | S  inside a word and a ballot + add carry chain
-//                      across the 32 words, until a sweep pair changes nothing.
+//   canny_nms_kernel   float64, dense, the listed 64x32 tiles only (persistent CTAs walking the list): L -> separable
+//                      Gaussian (scipy correlate1d order: centre tap, then the symmetric pairs from the outermost
+//                      inwards, every product and sum rounded on its own) / bleed-over normalisation -> Sobel (reflect)
+//                      -> magnitude -> bilinear non-maximum suppression -> two bit planes (>= low, >= high) written
+//                      with warp ballots.  FP64-pipe bound: ~125 non-fusable double operations per pixel (no FMA: the
+//                      CPU libraries round every op).
+//   mask_planes_kernel one CTA per image, one band of 64 rows per warp, one lane per 32-pixel word of a row
+//                      (W <= 1024): every later step is a reachability or a shift on bit planes.  Connectivity
+//                      (hysteresis, hole filling) = down / up sweeps inside a band to the band's fixed point, then
+//                      rounds over the band boundaries; one row step floods a whole row at once with the carry trick
+//                      reach = (M & ~(M + S)) | S  inside a word and a ballot + add carry chain across the 32 words.
+//                      Dilation + closing + hole-fill seeds are one streaming sweep; the largest component is a
+//                      union-find over pixel runs in shared memory (flood peel beyond 4096 runs).
 #include <cuda_runtime.h>
 #include <mutex>
 #include <cstdio>
