@@ -1,9 +1,10 @@
 // ssad_generate: the kernel pipeline (six kernels per chunk of the batch).
 //
-// v6 runs the whole of PretextTaskDataset.__getitem__ (datasets.py:209-394) for one image inside one cluster; ncu shows
-// that kernel issue-bound with 39 % of every CTA's life spent in its short serial phases (geometry, decisions, canvas,
-// tables) and a 1.7-wave tail.  Here each phase is its own grid, sized for what it does, and the two passes over the
-// pixels are pure streaming kernels -- no paste, mask or flag logic inside their loops:
+// Round 1's single-kernel design ran the whole of PretextTaskDataset.__getitem__ (datasets.py:209-394) for one image inside
+// one cluster; ncu showed that kernel issue-bound with 39 % of every CTA's life spent in its short serial phases
+// (geometry, decisions, canvas, tables) and a 1.7-wave tail (profiles/history/).  Here each phase is its own grid, sized
+// for what it does, and the two passes over the pixels are pure streaming kernels -- no paste, mask or flag logic inside
+// their loops:
 //
 //   plan     CTA / image      parameters -> centres -> container clamp -> paste boxes; rect2poly / rotated-scar coverage
 //                             bit rows; the jitter plan and the tables of the ops ahead of Contrast; the image joins the
