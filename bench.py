@@ -351,21 +351,27 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
         ab = ab - 3 * H * W + 6 * H * W
     # two resident input sets, alternated, so consecutive steps never touch the same lines
     # (one step already moves > L2: e.g. config 2 = 157 MB in + 100 MB out vs 126 MB L2)
+    # batches in flight: two; four for batches under 256 images (the reference's B = 96: one such batch is six short
+    # kernels in a row on a fraction of the SMs, a latency chain that more batches in flight hide)
+    inflight = args.inflight if args.inflight else (4 if batch < 256 else 2)
+    inflight = max(1, min(4, inflight))
+    nset = max(2, inflight)                  # input / output / workspace sets (one per batch in flight, two at least)
     srcs = [torch.from_numpy(images).to(dev)]
     srcs.append(torch.roll(srcs[0], 1, dims=0).contiguous())
+    srcs += [srcs[k & 1] for k in range(2, nset)]         # (sets beyond the second read the same two inputs)
     per_image_masks = cfg.is_non_fixed
-    mask_bufs, mask_ws = [None, None], None
+    mask_bufs, mask_ws = [None] * 4, None
     if per_image_masks:
-        mask_bufs = [obj_mask_batch(srcs[j]) for j in range(2)]
+        mask_bufs = [obj_mask_batch(srcs[j]) for j in range(nset)]
         mask_ws = [torch.empty((int(gen.lib.ssad_obj_mask_workspace(batch, images.shape[1], images.shape[2])) + 16,),
-                               dtype=torch.uint8, device=dev) for _ in range(2)]
+                               dtype=torch.uint8, device=dev) for _ in range(nset)]
     pdev = gen.upload_params(params)
-    outs_u8 = [torch.empty((batch, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)] if want_u8 else [None, None]
-    outs_n = [torch.empty((batch, 3, H, W), dtype=norm_dtype, device=dev) for _ in range(2)] if norm_dtype else [None, None]
-    y_outs = [torch.empty((batch,), dtype=torch.int64, device=dev) for _ in range(2)]
+    outs_u8 = [torch.empty((batch, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(nset)] if want_u8 else [None] * nset
+    outs_n = [torch.empty((batch, 3, H, W), dtype=norm_dtype, device=dev) for _ in range(nset)] if norm_dtype else [None] * nset
+    y_outs = [torch.empty((batch,), dtype=torch.int64, device=dev) for _ in range(nset)]
 
     plans = [gen.plan(srcs[j], params, masks=mask_bufs[j], want_u8=want_u8, norm_dtype=norm_dtype, params_dev=pdev,
-                      out_u8=outs_u8[j], out_norm=outs_n[j], y_out=y_outs[j]) for j in range(2)]
+                      out_u8=outs_u8[j], out_norm=outs_n[j], y_out=y_outs[j]) for j in range(nset)]
     om_launches = int(gen.lib.ssad_obj_mask_launches()) if per_image_masks else 0
     launches_per_step = int(gen.lib.ssad_generate_launches(plans[0].args[0], int(bool(args.graph)))) + om_launches
     if args.graph:
@@ -374,8 +380,8 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
 
     def step(i):
         if per_image_masks:                  # obj_mask of every image of the batch, then the generator (datasets.py:232-233)
-            obj_mask_batch(srcs[i & 1], out=mask_bufs[i & 1], workspace=mask_ws[i & 1])
-        gen.run(plans[i & 1])
+            obj_mask_batch(srcs[i % nset], out=mask_bufs[i % nset], workspace=mask_ws[i % nset])
+        gen.run(plans[i % nset])
 
     def barrier():
         if world > 1:
@@ -386,7 +392,7 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
     # one batch, with its own input set, outputs and workspace), the way a loader keeps a second batch in preparation
     # while the consumer takes the first.  --inflight 1 issues every step on one stream (also timed, `serial` below).
     cur = torch.cuda.current_stream(dev)
-    lanes = [torch.cuda.Stream(dev) for _ in range(max(1, min(2, args.inflight)))]
+    lanes = [torch.cuda.Stream(dev) for _ in range(inflight)]
 
     def timed(nsteps, use_lanes):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -396,7 +402,7 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
             for ln in lanes:
                 ln.wait_stream(cur)
             for i in range(nsteps):
-                with torch.cuda.stream(lanes[i & 1]):
+                with torch.cuda.stream(lanes[i % len(lanes)]):
                     step(i)
             for ln in lanes:
                 cur.wait_stream(ln)
@@ -591,7 +597,7 @@ def run_reference(args, rank: int):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": warm, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": config_block(config, name, batch, world, args.out, max(1, min(2, args.inflight)), bool(args.graph)),
+            "config": config_block(config, name, batch, world, args.out, max(1, min(4, args.inflight or (4 if batch < 256 else 2))), bool(args.graph)),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{sample} images/step of the workload, {cores} processes x 1 thread; the reference is "
                                        "pure Python and cannot travel to this box, so its algorithm runs as oracle/generator.py "
@@ -618,7 +624,8 @@ def main():
     ap.add_argument("--e2e-upload", default="auto", choices=["auto", "full", "windows"],
                     help="host-buffer call: whole images up (auto = full), or only the windows a patch-mode call reads")
     ap.add_argument("--e2e-chunks", type=int, default=None, help="pieces of the batch in flight in the host-buffer call")
-    ap.add_argument("--inflight", type=int, default=2, help="batches in flight: steps alternate between this many streams (1|2)")
+    ap.add_argument("--inflight", type=int, default=None, help="batches in flight: steps rotate over this many streams and buffer sets "
+                    "(1..4; default 2, 4 for batches under 256 images)")
     ap.add_argument("--graph", type=int, default=1, help="1: replay each step's ssad_generate call from a CUDA graph")
     ap.add_argument("--profile-steps", type=int, default=0, help="run this many steps of --config between cudaProfilerStart/Stop "
                     "and exit (for `ncu --profile-from-start off`: tools/traffic.py)")
@@ -710,7 +717,7 @@ def main():
             if "ms_per_step" not in r or k == "5":
                 pc[k] = r
                 continue
-            pc[k] = {"workload": r["name"], "batch_per_gpu": r["batch"], "value": r["value"], "ms_per_step": r["ms_per_step"],
+            pc[k] = {"workload": r["name"], "batch_per_gpu": r["batch"], "inflight": r["inflight"], "value": r["value"], "ms_per_step": r["ms_per_step"],
                      "steps": r["steps"], "serial_ms_per_step": r["serial_ms_per_step"],
                      "roofline": {k2: v for k2, v in roofline_of(r, peaks, traffic).items() if k2 in ("achieved", "frac", "traffic", "algorithmic_bytes_per_image")},
                      "e2e": r.get("e2e"), "verify": r.get("verify"), "gpu_launches": r["steps"] * r["launches_per_step"],
