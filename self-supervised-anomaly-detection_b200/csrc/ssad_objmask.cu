@@ -941,8 +941,9 @@ struct Plane {
 
 // Grow R (subset of M) to everything 8-connected to it through M.  COMPLEMENT: M = ~plane & rowmask.
 // The rows of the image are cut into one band per warp of the CTA.  A warp brings its band to a fixed point on its own --
-// sweeps down and up (one row step floods a whole row, see flood_row) until a sweep changes nothing -- with the
-// neighbouring bands' boundary rows as it read them; a round ends at a CTA barrier.  In the following rounds a band that
+// a sweep down and a sweep up (one row step floods a whole row, see flood_row), then sweeps over just the rows the
+// previous sweep changed until one changes nothing -- with the neighbouring bands' boundary rows as it read them; a
+// round ends at a CTA barrier.  In the following rounds a band that
 // is at its fixed point only looks at the two boundary rows again: unchanged -> nothing to do; changed -> changes can
 // only run inwards from that edge, so the sweep stops at the first row it leaves as it was, and the band iterates again
 // only if something did change.  Rounds repeat until no warp changed anything (then every boundary row read in that
@@ -952,12 +953,15 @@ template <bool COMPLEMENT>
 __device__ int reach(const Plane& Mp, const Plane& Rp, int H, int ylo, int yhi, uint32_t rowmask, int lane) {
     bool first = true, settled = false;
     uint32_t seen_top = 0u, seen_bot = 0u;            // the neighbours' boundary rows as last read
-    // one sweep over the band from its first (dir 0) or last (dir 1) row, `prev` = the row before it.  EDGE: the band is
-    // at its fixed point, stop at the first row that does not change.
-    auto sweep = [&](int dir, uint32_t prev, bool edge) -> bool {
-        const int step = dir == 0 ? 1 : -1, n = yhi - ylo + 1;
-        int y = dir == 0 ? ylo : yhi;
-        bool ch = false;
+    // One sweep in direction dir (0 down, 1 up) from row `from` to the band's end, `prev` = the row before `from` in
+    // sweep order.  It may stop at the first row it leaves unchanged once it is past row `need`: up to `need` a row's
+    // predecessor may have changed since the band was last closed in this direction, beyond it only this sweep's own
+    // changes run on.  [clo, chi] = the rows it changed (chi < 0: none).
+    auto sweep = [&](int dir, int from, uint32_t prev, int need, int& clo, int& chi) {
+        const int step = dir == 0 ? 1 : -1, n = dir == 0 ? yhi - from + 1 : from - ylo + 1;
+        clo = 0x7FFFFFFF; chi = -1;
+        if (n <= 0) return;
+        int y = from;
         uint32_t Mn = Mp.ld(y), Rn = Rp.ld(y);
         #pragma unroll 1
         for (int i = 0; i < n; ++i, y += step) {
@@ -966,16 +970,17 @@ __device__ int reach(const Plane& Mp, const Plane& Rp, int H, int ylo, int yhi, 
             if (i + 1 < n) { Mn = Mp.ld(y + step); Rn = Rp.ld(y + step); }      // next row is in flight during the step
             const uint32_t S = R | (M & spread3(prev, lane));
             uint32_t Rnew = R;
+            bool rowch = false;
             // (the very first sweep floods every row that holds a seed at all: R has not been spread inside its rows yet)
             if (__any_sync(FULL, first ? S != 0u : S != R)) {
                 Rnew = flood_row(M, S, lane);
-                if (Rnew != R) { Rp.st(y, Rnew); ch = true; }
-            } else if (edge) {
-                break;
+                if (Rnew != R) Rp.st(y, Rnew);
+                rowch = __any_sync(FULL, Rnew != R);
             }
+            if (rowch) { clo = min(clo, y); chi = max(chi, y); }
+            else if (dir == 0 ? y > need : y < need) break;
             prev = Rnew;
         }
-        return __any_sync(FULL, ch);
     };
     for (int rounds = 1;; ++rounds) {
         bool changed = false;
@@ -984,18 +989,27 @@ __device__ int reach(const Plane& Mp, const Plane& Rp, int H, int ylo, int yhi, 
             const bool same = __all_sync(FULL, top == seen_top && bot == seen_bot);
             seen_top = top; seen_bot = bot;
             bool work = !settled;
+            int clo, chi;
             if (settled && !same) {
-                const bool c0 = sweep(0, top, true), c1 = sweep(1, bot, true);
-                work = c0 || c1;
+                // the band is at its fixed point: changes can only run inwards from a boundary row that changed
+                sweep(0, ylo, top, ylo - 1, clo, chi);
+                work = chi >= 0;
+                sweep(1, yhi, bot, yhi + 1, clo, chi);
+                work = work || chi >= 0;
                 changed = work;
             }
             if (work) {
-                // to the band's own fixed point: a sweep that changes nothing right after one in the other direction
-                for (int k = 0;; ++k) {
-                    const bool ch = sweep(k & 1, (k & 1) ? bot : top, false);
-                    first = false;
-                    changed = changed || ch;
-                    if (!ch && k >= 1) break;
+                // to the band's own fixed point: one full sweep down and one up, then sweeps over the rows the previous
+                // sweep changed (and as far beyond as their own changes run) until one changes nothing
+                sweep(0, ylo, top, yhi, clo, chi);
+                first = false;
+                changed = changed || chi >= 0;
+                sweep(1, yhi, bot, ylo, clo, chi);
+                for (int dir = 0; chi >= 0; dir ^= 1) {
+                    changed = true;
+                    const int a = clo, b = chi;
+                    if (dir == 0) sweep(0, a + 1, Rp.ld(a), b, clo, chi);
+                    else sweep(1, b - 1, Rp.ld(b), a, clo, chi);
                 }
                 settled = true;
             }
