@@ -501,8 +501,9 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
         for i in range(3):
             e2e_step(i)
         barrier()
+        import gc
+        gc.collect()                             # (buffers of the previous configuration are released here, not in the timed region)
         host_s[0] = 0.0
-        pre.busy_s, pre.n = 0.0, 0
         t0 = time.perf_counter()
         for i in range(e2e_steps):
             e2e_step(i)
@@ -668,7 +669,7 @@ def main():
         for c in (1, 2, 3):
             if c == args.config:
                 continue
-            r = run_config(c, args, rt, max(steps, 200), 10, args.verify)
+            r = run_config(c, args, rt, max(steps, 200), 30, args.verify)
             per_config[str(c)] = r
         try:
             per_config["datamodule"] = datamodule_rate(rt)
