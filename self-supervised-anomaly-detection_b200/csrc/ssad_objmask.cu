@@ -451,11 +451,15 @@ canny32_kernel(const __grid_constant__ C32K K, int H, int W, const uint8_t* __re
         if (inside) {
             // every pixel of the tile and its halo is in the image: no bounds
             const uint8_t* const base = img + (size_t)(y0 - 8) * src_pitch + (size_t)(x0 - 8) * 3 + g * 12;
+            const uint8_t* row = base + (size_t)rr * src_pitch;             // (one 64-bit product, then constant steps)
+            const size_t down = (size_t)RS * src_pitch;
             #pragma unroll
             for (int k = 0; k < NK; ++k) {
-                const int r = min(rr + k * RS, SG_H - 1);
-                const uint32_t* q = reinterpret_cast<const uint32_t*>(base + (size_t)r * src_pitch);
+                // (rows past the halo -- last round only -- re-read the last row; they are not stored)
+                const uint8_t* rq = (k * RS + RS - 1 < SG_H || rr + k * RS < SG_H) ? row : base + (size_t)(SG_H - 1) * src_pitch;
+                const uint32_t* q = reinterpret_cast<const uint32_t*>(rq);
                 w[k][0] = __ldg(q); w[k][1] = __ldg(q + 1); w[k][2] = __ldg(q + 2);
+                row += down;
             }
         } else {
             const int x = x0 - 8 + 4 * g;
