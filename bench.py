@@ -521,6 +521,42 @@ def run_config(config: int, args, rt, steps: int, e2e_steps: int, verify_images:
                       "host_ms_per_call": 1e3 * host_s[0] / max(e2e_steps, 1),
                       "sampler_included": True,
                       "sampler_records_per_s": (pre.n / pre.busy_s) if pre.busy_s > 0 else None}
+        # ---- the same with the source set RESIDENT on the device (the DataModule's deployment, datasets.py:476-508: the
+        # decoded set is loaded once): per step only the records go up and the results come down; per-image masks are
+        # per SOURCE image and built once (obj_mask depends on the original only)
+        if not args.no_resident:
+            uniq_n = min(batch, 8 if config == 4 else 16)     # (make_workload cycles the batch through that many images)
+            uniq_dev = torch.from_numpy(np.ascontiguousarray(images[:uniq_n])).to(dev)
+            idx_sets = [np.arange(batch) % uniq_n, (np.arange(batch) + 1) % uniq_n]
+            src_masks = obj_mask_batch(uniq_dev) if per_image_masks else None
+            pre2 = ParamPrefetcher(cfg, batch, 199 + rank)
+            pending2 = [None, None]
+
+            def res_step(i):
+                j = i & 1
+                if pending2[j] is not None:
+                    pending2[j].synchronize()
+                pending2[j] = gen.generate_resident_to_host(uniq_dev, idx_sets[j], pre2.get(), h_outs[j], h_ys[j], masks=src_masks,
+                                                            chunks=args.e2e_chunks, wait=not deep)
+            for i in range(3):
+                res_step(i)
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(e2e_steps):
+                res_step(i)
+            barrier()
+            dt2 = time.perf_counter() - t0
+            pre2.close()
+            if world > 1:
+                t = torch.tensor([dt2], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dt2 = float(t.item())
+            res["e2e_resident"] = {"value": world * batch * e2e_steps / dt2, "unit": UNIT, "h2d_bytes_per_step": int(rec_bytes),
+                                   "d2h_bytes_per_step": int(h_out.numel() + h_y.numel() * 8), "steps": e2e_steps,
+                                   "resident_images": int(uniq_n), "sampler_included": True,
+                                   "what": "source set resident on the device (decoded once, as the DataModule keeps it), records up, "
+                                           "results down" + ("; one obj_mask per SOURCE image, built once" if per_image_masks else "")}
+            del uniq_dev, src_masks
         del h_src, h_out, h_outs, h_y, h_ys
     del srcs, outs_u8, outs_n, plans, gen, mask_bufs, mask_ws, pdev
     torch.cuda.empty_cache()
@@ -624,6 +660,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--e2e-upload", default="auto", choices=["auto", "full", "windows"],
                     help="host-buffer call: whole images up (auto = full), or only the windows a patch-mode call reads")
+    ap.add_argument("--no-resident", action="store_true", help="skip the e2e_resident leg")
     ap.add_argument("--e2e-chunks", type=int, default=None, help="pieces of the batch in flight in the host-buffer call")
     ap.add_argument("--inflight", type=int, default=None, help="batches in flight: steps rotate over this many streams and buffer sets "
                     "(1..4; default 2, 4 for batches under 256 images)")
@@ -702,6 +739,7 @@ def main():
         "config": config_block(head["config"], head["name"], head["batch"], world, head["out"], head["inflight"], bool(args.graph)),
         "roofline": roofline_of(head, peaks, traffic),
         "e2e": head.get("e2e"),
+        **({"e2e_resident": head["e2e_resident"]} if "e2e_resident" in head else {}),
         "gpu_launches": head["steps"] * head["launches_per_step"],
         "serial": {"ms_per_step": head["serial_ms_per_step"], "value": world * head["batch"] / (head["serial_ms_per_step"] * 1e-3),
                    "note": "the same K steps issued on ONE stream (a step starts when the previous one has finished)"},
@@ -721,7 +759,7 @@ def main():
             pc[k] = {"workload": r["name"], "batch_per_gpu": r["batch"], "inflight": r["inflight"], "value": r["value"], "ms_per_step": r["ms_per_step"],
                      "steps": r["steps"], "serial_ms_per_step": r["serial_ms_per_step"],
                      "roofline": {k2: v for k2, v in roofline_of(r, peaks, traffic).items() if k2 in ("achieved", "frac", "traffic", "algorithmic_bytes_per_image")},
-                     "e2e": r.get("e2e"), "verify": r.get("verify"), "gpu_launches": r["steps"] * r["launches_per_step"],
+                     "e2e": r.get("e2e"), "e2e_resident": r.get("e2e_resident"), "verify": r.get("verify"), "gpu_launches": r["steps"] * r["launches_per_step"],
                      "clocks": r["clocks"]}
         line["per_config"] = pc
     if world == 1 and not args.no_cpu:

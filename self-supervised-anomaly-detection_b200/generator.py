@@ -429,6 +429,67 @@ class BatchGenerator:
             done.synchronize()                   # the caller owns the results when the call returns
         return done
 
+    def generate_resident_to_host(self, src_set: torch.Tensor, src_index, params: ParamBatch, h_out: torch.Tensor,
+                                  h_y: torch.Tensor, *, masks: Optional[torch.Tensor] = None, chunks: Optional[int] = None,
+                                  wait: bool = True):
+        """The deployment the reference's DataModule has (datasets.py:476-508: the decoded set is loaded once): the
+        distinct source images ``src_set`` [N, Hs, Ws, 3] stay on the device, item i works on ``src_set[src_index[i]]``;
+        per step only the 192-byte records go up and the results ``h_out`` uint8 [B, h, w, 3] / ``h_y`` int64 [B] (pinned
+        host tensors) come down, pieces of the batch pipelined through a generation and a download stream.  ``masks``: per
+        SOURCE image (non-fixed classes: ``obj_mask_batch(src_set)``, computed once -- obj_mask depends on the original
+        only).  Returns a ``torch.cuda.Event`` (complete when the results are in host memory; ``wait=True`` waits)."""
+        B = len(params)
+        W, H = self.cfg.work_size
+        if chunks is None:
+            chunks = min(8, B // 64)
+        chunks = max(1, min(int(chunks), B))
+        st = self._host_pipe(B, (1, 1, 3), chunks)           # (no device staging of sources: a 1x1 placeholder)
+        src_index = np.asarray(src_index, dtype=np.int64)
+        if len(src_index) != B:
+            raise ValueError("params and src_index disagree on the batch size")
+        if self.cfg.is_non_fixed and masks is None and self.mask_bits is None:
+            raise ValueError("non-fixed classes need per-image masks (obj_mask, datasets.py:232-233)")
+        cur = torch.cuda.current_stream(self.device)
+        for s_ in (st["up"], st["run"], st["down"]):
+            s_.wait_stream(cur)
+        st["run"].wait_stream(st["down"])            # the staging outputs are shared with the previous call's downloads
+        rec = np.ascontiguousarray(params.records)
+        if rec.dtype != IMAGE_PARAMS_DTYPE:
+            raise ValueError("records have the wrong dtype")
+        rec = rec.copy()
+        rec["src_index"] = src_index.astype(np.uint32)
+        self.validate_records(rec, src_set.shape[1:3], n_src=int(src_set.shape[0]))
+        hints = self.batch_hints(rec)
+        if hints[5] and params.line_xy is None:
+            params.resolve_lines(self._window_mask_fn(rec, masks, src_index))
+            rec["line_n"] = params.records["line_n"]
+        st["ev_rec"].synchronize()
+        st["h_rec"].numpy()[...] = rec.view(np.uint8).reshape(B, IMAGE_PARAMS_DTYPE.itemsize)
+        with torch.cuda.stream(st["up"]):
+            st["d_rec"].copy_(st["h_rec"], non_blocking=True)
+            st["ev_rec"].record(st["up"])
+        st["run"].wait_event(st["ev_rec"])
+        bounds = [(B * c // chunks, B * (c + 1) // chunks) for c in range(chunks)]
+        for c, (lo, hi) in enumerate(bounds):
+            d_out, d_y = st["out"][lo:hi], st["y"][lo:hi]
+            with torch.cuda.stream(st["run"]):
+                pl = self.plan(src_set, params.slice(lo, hi), masks=masks, want_u8=True, norm_dtype=None,
+                               params_dev=st["d_rec"][lo:hi], out_u8=d_out, y_out=d_y, workspace=st["ws"][c],
+                               src_index=src_index[lo:hi], validated=True, hints=hints)
+                st["ws"][c] = pl.workspace
+                self.run(pl)
+                st["ev_run"][c].record(st["run"])
+            with torch.cuda.stream(st["down"]):
+                st["down"].wait_event(st["ev_run"][c])
+                h_out[lo:hi].copy_(d_out, non_blocking=True)
+                h_y[lo:hi].copy_(d_y, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record(st["down"])
+        cur.wait_stream(st["up"]); cur.wait_stream(st["run"])
+        if wait:
+            done.synchronize()
+        return done
+
     def _host_pipe(self, B: int, src_shape: tuple, chunks: int) -> dict:
         key = (B, src_shape, chunks)
         st = getattr(self, "_pipe", None)

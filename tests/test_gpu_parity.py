@@ -310,6 +310,31 @@ def test_indexed_sources_match_gathered_batch(name):
     assert torch.equal(out2["x_u8"][:12], ref["x_u8"]) and torch.equal(out2["x_u8"][276:288], ref["x_u8"])
 
 
+@pytest.mark.parametrize("chunks", [1, 3])
+@pytest.mark.parametrize("name", ["image_level_256", "patch_level", "texture", "non_fixed", "lines_image"])
+def test_resident_sources_to_host_match_device_call(name, chunks):
+    """generate_resident_to_host: the source set stays on the device, per call only the records go up and the results
+    come down (the DataModule's deployment) -- same bytes as the device call on the gathered batch, twice in a row."""
+    import gpu_utils as U
+    sc = S.build(name, 24)
+    gen = U.make_generator(sc)
+    ref = U.run_cuda(sc, norm_dtype=None, debug=False, gen=gen)
+    perm = np.random.default_rng(4).permutation(24)
+    resident = torch.from_numpy(sc.images[perm]).cuda()
+    inv = np.argsort(perm)
+    masks = U.per_image_masks(sc)
+    if masks is not None:
+        masks = masks[torch.as_tensor(perm).cuda()].contiguous()
+    W, H = sc.cfg.work_size
+    h_out = torch.zeros((24, H, W, 3), dtype=torch.uint8).pin_memory()
+    h_y = torch.zeros((24,), dtype=torch.int64).pin_memory()
+    for _ in range(2):
+        h_out.zero_(); h_y.zero_()
+        gen.generate_resident_to_host(resident, inv, sc.params, h_out, h_y, masks=masks, chunks=chunks)
+        assert torch.equal(h_out, ref["x_u8"].cpu())
+        assert torch.equal(h_y, ref["y"].cpu())
+
+
 def test_two_host_threads_with_their_own_contexts():
     """ssad_context_create: two host threads drive the same device at once, each through its own context (its own helper
     streams); both get the bytes of a single-threaded call."""
