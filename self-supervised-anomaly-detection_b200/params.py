@@ -175,9 +175,12 @@ def random_affine_fixed(w: int, h: int, angle: np.ndarray, scale: np.ndarray) ->
     [cos, sin, 0, -sin, cos, 0] / scale before the translation terms.)"""
     angle = np.asarray(angle, dtype=np.float64)
     scale = np.asarray(scale, dtype=np.float64)
-    rot = [math.radians(float(a)) for a in angle]
-    cs = np.array([math.cos(r) for r in rot], dtype=np.float64)
-    sn = np.array([math.sin(r) for r in rot], dtype=np.float64)
+    # libm's cos / sin through math.* (NumPy's vector versions may differ in the last place); math.radians(x) is the one
+    # IEEE product x * (pi / 180), so that part is an array op
+    rot = (angle * (math.pi / 180.0)).tolist()
+    n = len(rot)
+    cs = np.fromiter(map(math.cos, rot), dtype=np.float64, count=n)
+    sn = np.fromiter(map(math.sin, rot), dtype=np.float64, count=n)
     cx, cy = w * 0.5, h * 0.5
     m0, m1, m3, m4 = cs / scale, sn / scale, (-sn) / scale, cs / scale
     m2 = 0.0 / scale
